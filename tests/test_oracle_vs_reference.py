@@ -1,0 +1,46 @@
+"""CPU, build container only: the standalone oracle against the reference's OWN classes run live
+(oracle/ref_harness.py imports /root/reference).  Skipped where the reference tree is absent."""
+import pytest
+import torch
+
+from helpers import make_rays, rel_err
+from oracle.ref_import import reference_available
+
+pytestmark = pytest.mark.skipif(not reference_available(), reason="/root/reference not present on this box")
+
+
+@pytest.mark.parametrize("training", [False, True])
+def test_oracle_equals_reference_live(training, spec, params_factory):
+    from oracle.nerfacto_oracle import OracleEmitter
+    from oracle.ref_harness import ReferenceEmitter
+    P = params_factory(0, 1e3)
+    R = ReferenceEmitter(P, spec)
+    O = OracleEmitter(P, spec)
+    R.train(training)
+    O.train(training)
+    N = 300
+    o, v, g = make_rays(N, seed=11)
+    jit = [torch.rand(N, 1, generator=g) for _ in range(3)] if training else None
+    _, a = R.render(o, v, near=0.2, camera_idx=2, jitter=jit, return_aux=True)
+    _, b = O.render(o, v, near=0.2, camera_idx=2, jitter=jit, return_aux=True)
+    assert torch.equal(a["inds1"], b["inds1"]) and torch.equal(a["inds2"], b["inds2"])
+    for k in ["rgb", "weights0", "weights1", "weights2", "sdist1", "sdist2", "accumulation"]:
+        assert torch.equal(a[k], b[k]), k          # same op order -> same bits on the same CPU
+    do, dv = torch.randn(3, N, generator=g), torch.randn(3, N, generator=g)
+    assert rel_err(O.jvp(o, v, do, dv, near=0.2, camera_idx=2, jitter=jit),
+                   R.jvp(o, v, do, dv, near=0.2, camera_idx=2, jitter=jit)) < 1e-6
+    gout = torch.randn(N, 3, generator=g)
+    go_r, gv_r, gr, _ = R.vjp(o, v, gout, near=0.2, camera_idx=2, jitter=jit)
+    go_o, gv_o, gq, _ = O.vjp(o, v, gout, near=0.2, camera_idx=2, jitter=jit)
+    assert rel_err(go_o, go_r) < 1e-5 and rel_err(gv_o, gv_r) < 1e-5
+    for k in gr:
+        assert rel_err(gq[k], gr[k], floor=1e-30) < 1e-4, k
+
+
+def test_grid_scalings_match_reference(spec):
+    from oracle.ref_import import import_reference
+    ns = import_reference()
+    for g in [spec.main_grid, *spec.prop_grids]:
+        enc = ns.encodings.HashEncoding(num_levels=g.num_levels, min_res=g.base_res, max_res=g.max_res,
+                                        log2_hashmap_size=4, implementation="torch")
+        assert [float(x) for x in enc.scalings] == g.scalings()
