@@ -1,0 +1,193 @@
+/*
+ * nemit.h - C ABI of libnerfemitter.so: the B200 (sm_100a) NeRF-emitter evaluation path.
+ *
+ * Drop-in boundary for gerwang/nerf-emitter's emitter query.  Every entry point
+ * cites the reference interface it replaces (paths relative to the reference checkout;
+ * NS = nerfstudio/, DS = differentiable-sdf-rendering/python/).
+ *
+ * Conventions
+ *   - plain pointers and sizes; all data pointers are DEVICE pointers unless named *_host;
+ *   - every call is asynchronous on the given cudaStream_t (passed as void*), no hidden host sync;
+ *   - return value: 0 = ok, <0 = error (see NEMIT_E_*); nemit_last_error() gives the message;
+ *   - the library BORROWS parameter / gradient memory (torch owns it); gradients are ACCUMULATED
+ *     (+=) like torch's .backward() over chunks (NS/pipelines/mitsuba_sdf.py:1180-1190);
+ *   - rays come in as struct-of-arrays (3,N) fp32 exactly as the dr.CustomOp receives them
+ *     (DS/emitters/nerf.py:12-17, nerf_emitter_op.py:41-42) and radiance leaves as (N,3) row-major
+ *     (nerf_emitter_op.py:35-36), so no transposes are needed on either side.
+ */
+#ifndef NEMIT_H_
+#define NEMIT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NEMIT_OK 0
+#define NEMIT_E_INVALID (-1)   /* bad argument / unsupported shape */
+#define NEMIT_E_CUDA (-2)      /* CUDA runtime error */
+#define NEMIT_E_UNBOUND (-3)   /* parameters (or gradients) not bound */
+#define NEMIT_E_WORKSPACE (-4) /* workspace too small */
+
+#define NEMIT_MAX_LEVELS 16
+
+/* One multiresolution hash grid: NS/field_components/encodings.py:264-312.  `scalings` are the
+ * per-level floor(min_res * g^l) values the host computed exactly as encodings.py:281-283 does
+ * (main grid ends at 2047, not 2048).  Table layout: (num_levels << log2_table_size, 2) fp32. */
+typedef struct NemitGrid {
+  int32_t num_levels;
+  int32_t log2_table_size;
+  float scalings[NEMIT_MAX_LEVELS];
+} NemitGrid;
+
+/* Model constants: NS/models/nerfacto.py:58-157 as overridden by sdf-nerfacto
+ * (NS/configs/method_configs.py:314-326). */
+typedef struct NemitConfig {
+  NemitGrid main_grid;          /* 16 levels, T=2^19 */
+  NemitGrid prop_grid[2];       /* 5 levels, T=2^17 */
+  int32_t num_prop_samples[2];  /* 256, 96   (NS/models/nerfacto.py:85-88) */
+  int32_t num_nerf_samples;     /* 48 */
+  int32_t hidden_dim;           /* 64 */
+  int32_t geo_feat_dim;         /* 15 */
+  int32_t appearance_dim;       /* 32 */
+  int32_t prop_hidden_dim;      /* 16 */
+  int32_t num_images;           /* rows of the appearance embedding */
+  float near_plane;             /* 0.05, used in training mode only (scene_colliders.py:217-222) */
+  float far_plane;              /* 1000 */
+  float scene_scale;            /* DS/emitters/nerf_op.py:76-89 */
+  float aabb[6];                /* min xyz, max xyz of the scene box */
+  float rgb_bias;               /* SafeExp bias, -5 (NS/fields/nerfacto_field.py:40-57) */
+  int32_t disable_inside_aabb;  /* 1 during emitter queries (NS/pipelines/mitsuba_sdf.py:922) */
+  int32_t cpu_sum_width;        /* ATen CPU torch.sum vector width to reproduce (8); 0 = fp64 sum */
+  float interlevel_mult;        /* 1.0   (NS/models/nerfacto.py:106) */
+  float distortion_mult;        /* 7e-3  (NS/configs/method_configs.py:320) */
+  /* sampler tables computed by the host with torch.linspace so they are bit-identical to
+   * NS/model_components/ray_samplers.py:104 and :323-331 */
+  const float* lin0_host;       /* num_prop_samples[0]+1 values of linspace(0,1,S0+1) */
+  const float* u1_host;         /* num_prop_samples[1]+1 values of linspace(0,1-1/nb,nb)       */
+  const float* u2_host;         /* num_nerf_samples+1 values                                   */
+} NemitConfig;
+
+/* Parameter pointers, named as in the reference state_dict (SURVEY.md 8b "Parameter ownership").
+ * The same struct carries the gradient accumulators for nemit_bind_grads. */
+typedef struct NemitParams {
+  float* main_table;            /* field.mlp_base_grid.hash_table            (16*2^19, 2) */
+  float* base_w0; float* base_b0; /* field.mlp_base_mlp.layers.0  (64,32),(64) */
+  float* base_w1; float* base_b1; /* field.mlp_base_mlp.layers.1  (16,64),(16) */
+  float* head_w0; float* head_b0; /* field.mlp_head.layers.0      (64,63),(64) */
+  float* head_w1; float* head_b1; /* field.mlp_head.layers.1      (64,64),(64) */
+  float* head_w2; float* head_b2; /* field.mlp_head.layers.2      (3,64),(3)   */
+  float* appearance;            /* field.embedding_appearance.embedding.weight (num_images,32) */
+  float* prop_table[2];         /* proposal_networks.i.encoding.hash_table   (5*2^17, 2) */
+  float* prop_w0[2]; float* prop_b0[2]; /* proposal_networks.i.mlp_base.1.layers.0 (16,10),(16) */
+  float* prop_w1[2]; float* prop_b1[2]; /* proposal_networks.i.mlp_base.1.layers.1 (1,16),(1)   */
+} NemitParams;
+
+/* Per-call ray batch: what NeRFEmitterOp.eval/forward/backward get from Mitsuba
+ * (DS/emitters/nerf_emitter_op.py:18-21, 38-117). */
+typedef struct NemitRays {
+  const float* o;        /* (3,N) origins in Mitsuba unit-cube coordinates */
+  const float* v;        /* (3,N) directions */
+  const float* near_per_ray; /* (N) or NULL -> near_scalar; o' = o + near*v (nerf_emitter_op.py:28,43) */
+  float near_scalar;
+  int64_t n;
+  int32_t camera_idx;    /* appearance row in training mode (nerfacto_field.py:272-285) */
+  int32_t training;      /* 1: model.train() semantics (near plane 0.05, embedding row, no clamp) */
+  const float* jitter;   /* (N,3) per-ray U[0,1) for the three single-jitter samplers, or NULL =
+                            deterministic bins (ray_samplers.py:107-117, 323-333). The host draws
+                            them from the samplers' own generators. */
+  float anneal;          /* ProposalNetworkSampler._anneal (ray_samplers.py:609); 1.0 = no-op */
+} NemitRays;
+
+/* Optional per-level outputs of the proposal loop, for parity tests and for
+ * ProposalNetworkSampler's return value (ray_samplers.py:584-626). Any pointer may be NULL. */
+typedef struct NemitLevelsOut {
+  float* weights0;   /* (N,S0) */
+  float* weights1;   /* (N,S1) */
+  float* s_edges1;   /* (N,S1+1) spacing-domain bin edges of level 1 */
+  float* s_edges2;   /* (N,S2+1) */
+  float* t_edges2;   /* (N,S2+1) euclidean bin edges of the final samples */
+  int32_t* inds1;    /* (N,S1+1) searchsorted(cdf,u,right) of PDF stage 1 */
+  int32_t* inds2;    /* (N,S2+1) */
+  float* weights2;   /* (N,S2) final weights (filled by nemit_forward only) */
+} NemitLevelsOut;
+
+typedef struct NemitHandle NemitHandle;
+
+const char* nemit_last_error(void);
+int nemit_version(void);
+
+/* lifetime: one handle per device (SURVEY.md 8b "Threading / streams") */
+int nemit_create(const NemitConfig* cfg, int device, NemitHandle** out);
+int nemit_destroy(NemitHandle* h);
+
+/* borrow parameter / gradient pointers (never copied, never freed) */
+int nemit_bind_params(NemitHandle* h, const NemitParams* p);
+int nemit_bind_grads(NemitHandle* h, const NemitParams* g);
+
+/* bytes of scratch the calls below need for a batch of n rays (chunked internally) */
+size_t nemit_workspace_bytes(const NemitHandle* h, int64_t n);
+
+/* replaces NeRFEmitterOp.ns_render_ray -> Model.get_rgb_for_camera_ray_bundle ->
+ * SdfNerfactoModel.get_rgb (nerf_emitter_op.py:38-58, NS/models/base_model.py:290-313,
+ * NS/models/sdf_nerfacto.py:64-83).  rgb (N,3); accumulation (N) optional. */
+int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, float* accumulation,
+                  const NemitLevelsOut* levels_or_null, void* workspace, size_t workspace_bytes,
+                  void* stream);
+
+/* proposal loop only: ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) */
+int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const NemitLevelsOut* out,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* replaces NeRFEmitterOp.ns_forward_ray -> forward_grad_for_camera_ray_bundle ->
+ * SdfNerfactoModel.forward_grad (nerf_emitter_op.py:60-90, base_model.py:315-344,
+ * sdf_nerfacto.py:85-113).  d_o, d_v (3,N) tangents; d_rgb (N,3), NaN tangents zeroed. */
+int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o, const float* d_v,
+              float* d_rgb, void* workspace, size_t workspace_bytes, void* stream);
+
+/* replaces NeRFEmitterOp.ns_backward_ray -> backward_for_camera_ray_bundle ->
+ * get_backward_outputs + get_reg_loss_dict (nerf_emitter_op.py:92-117,
+ * NS/pipelines/mitsuba_sdf.py:1144-1219, sdf_nerfacto.py:115-187).
+ * grad_rgb (N,3); grad_o, grad_v (3,N) are OVERWRITTEN (already include the -near*grad_v
+ * change of variables, nerf_emitter_op.py:112); parameter grads are accumulated into the bound
+ * buffers.  chunk_rays = rays per backward chunk over which the regulariser means are taken
+ * (backward_num_rays_per_chunk); loss_scale = GradScaler scale applied to parameter grads only.
+ * proposal_requires_grad = the sampler's `updated` flag (ray_samplers.py:598,613-618). */
+int nemit_backward(NemitHandle* h, const NemitRays* rays, const float* grad_rgb,
+                   int64_t chunk_rays, float loss_scale, int32_t proposal_requires_grad,
+                   float* grad_o, float* grad_v, void* workspace, size_t workspace_bytes,
+                   void* stream);
+
+/* component drop-in: HashEncoding.forward (NS/field_components/encodings.py:341-382).
+ * x (n,3) in [0,1]; out (n, 2*num_levels). which: 0 = main grid, 1/2 = proposal grids. */
+int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, int64_t n, float* out,
+                      void* stream);
+
+/* vMF-mixture emitter: VonMisesFisherEmitter.sample_direction / pdf_direction
+ * (DS/emitters/vMF.py:24-81).  lobes: position (K,3), weight (K) unnormalised, std (K).
+ * p (N,3) shading points in emitter-local coordinates, u (N,2); d (N,3), pdf (N). */
+typedef struct NemitVmfLobes {
+  const float* position;
+  const float* weight;
+  const float* std;
+  int32_t num_lobes;
+} NemitVmfLobes;
+int nemit_vmf_sample(const NemitVmfLobes* lobes, const float* p, const float* u, int64_t n,
+                     float* d, float* pdf, void* stream);
+int nemit_vmf_pdf(const NemitVmfLobes* lobes, const float* p, const float* d, int64_t n,
+                  float* pdf, void* stream);
+
+/* end-to-end entry with HOST (pinned) ray and radiance buffers: H2D copy, forward, D2H copy,
+ * all queued on `stream`; the device staging lives in the workspace. */
+int nemit_forward_host(NemitHandle* h, const NemitRays* rays_host, float* rgb_host,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* number of kernels the library has launched on this handle since creation (bench evidence) */
+int64_t nemit_launch_count(const NemitHandle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NEMIT_H_ */

@@ -1,0 +1,342 @@
+// api.cu - the C ABI of libnerfemitter.so (include/nemit.h): handle, argument checks, chunking,
+// workspace carving, kernel launches.  No torch types, no allocation of parameter memory.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "kernels.h"
+#include "vmf.h"
+
+using namespace nemit;
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, const char* a = "", long long b = 0) {
+  char buf[512];
+  snprintf(buf, sizeof(buf), fmt, a, b);
+  g_err = buf;
+  return code;
+}
+static int cuda_fail(cudaError_t e, const char* where) {
+  return fail(NEMIT_E_CUDA, "CUDA error in %s: ", where), g_err += cudaGetErrorString(e), NEMIT_E_CUDA;
+}
+
+struct NemitHandle {
+  int device;
+  ModelDev M;
+  NemitConfig cfg;
+  float* tables_dev;        // lin0 | u1 | u2 copies of the host sampler tables
+  const float* lin0;
+  const float* u1;
+  const float* u2;
+  bool params_bound, grads_bound;
+  NemitParams P, G;
+  int64_t launches;
+};
+
+static const int64_t kChunkRays = 1 << 18;
+
+extern "C" const char* nemit_last_error(void) { return g_err.c_str(); }
+extern "C" int nemit_version(void) { return 100; }
+
+static bool grid_ok(const NemitGrid& g, int levels) {
+  return g.num_levels == levels && g.log2_table_size >= 1 && g.log2_table_size <= 26;
+}
+static void grid_to_dev(const NemitGrid& g, GridDev& d) {
+  d.num_levels = g.num_levels;
+  d.table_size = 1u << g.log2_table_size;
+  d.table_mask = d.table_size - 1u;
+  for (int i = 0; i < NEMIT_MAX_LEVELS; ++i) d.scal[i] = i < g.num_levels ? g.scalings[i] : 0.f;
+}
+
+extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** out) {
+  if (!cfg || !out) return fail(NEMIT_E_INVALID, "nemit_create: null argument%s");
+  if (!grid_ok(cfg->main_grid, kMainLevels) || !grid_ok(cfg->prop_grid[0], kPropLevels) ||
+      !grid_ok(cfg->prop_grid[1], kPropLevels))
+    return fail(NEMIT_E_INVALID, "nemit_create: this build supports a 16-level main grid and 5-level proposal grids%s");
+  if (cfg->num_prop_samples[0] != kS0 || cfg->num_prop_samples[1] != kS1 || cfg->num_nerf_samples != kS2)
+    return fail(NEMIT_E_INVALID, "nemit_create: this build supports 256/96/48 samples per ray%s");
+  if (cfg->hidden_dim != kHidden || cfg->geo_feat_dim != kGeo || cfg->appearance_dim != kApp ||
+      cfg->prop_hidden_dim != kPropHidden)
+    return fail(NEMIT_E_INVALID, "nemit_create: this build supports hidden 64 / geo 15 / appearance 32 / proposal hidden 16%s");
+  if (cfg->num_images < 1) return fail(NEMIT_E_INVALID, "nemit_create: num_images must be >= 1%s");
+  if (!cfg->lin0_host || !cfg->u1_host || !cfg->u2_host)
+    return fail(NEMIT_E_INVALID, "nemit_create: sampler tables missing%s");
+  if (cfg->cpu_sum_width != 0 && cfg->cpu_sum_width != 8 && cfg->cpu_sum_width != 16)
+    return fail(NEMIT_E_INVALID, "nemit_create: cpu_sum_width must be 0, 8 or 16%s");
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+  if (device < 0 || device >= ndev) return fail(NEMIT_E_INVALID, "nemit_create: no such CUDA device%s");
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+  NemitHandle* h = new (std::nothrow) NemitHandle();
+  if (!h) return fail(NEMIT_E_INVALID, "nemit_create: out of host memory%s");
+  memset(h, 0, sizeof(*h));
+  h->device = device;
+  h->cfg = *cfg;
+  h->cfg.lin0_host = h->cfg.u1_host = h->cfg.u2_host = nullptr;
+  grid_to_dev(cfg->main_grid, h->M.main_grid);
+  grid_to_dev(cfg->prop_grid[0], h->M.prop_grid[0]);
+  grid_to_dev(cfg->prop_grid[1], h->M.prop_grid[1]);
+  for (int k = 0; k < 3; ++k) { h->M.aabb_min[k] = cfg->aabb[k]; h->M.aabb_max[k] = cfg->aabb[3 + k]; }
+  h->M.scene_scale = cfg->scene_scale;
+  h->M.near_plane = cfg->near_plane;
+  h->M.far_plane = cfg->far_plane;
+  h->M.rgb_bias = cfg->rgb_bias;
+  h->M.disable_inside_aabb = cfg->disable_inside_aabb;
+  h->M.cpu_sum_width = cfg->cpu_sum_width;
+  h->M.num_images = cfg->num_images;
+  h->M.interlevel_mult = cfg->interlevel_mult;
+  h->M.distortion_mult = cfg->distortion_mult;
+  const int n0 = kS0 + 1, n1 = kS1 + 1, n2 = kS2 + 1;
+  if ((e = cudaMalloc(&h->tables_dev, sizeof(float) * (n0 + n1 + n2))) != cudaSuccess) {
+    delete h;
+    return cuda_fail(e, "cudaMalloc(sampler tables)");
+  }
+  cudaMemcpy(h->tables_dev, cfg->lin0_host, sizeof(float) * n0, cudaMemcpyHostToDevice);
+  cudaMemcpy(h->tables_dev + n0, cfg->u1_host, sizeof(float) * n1, cudaMemcpyHostToDevice);
+  e = cudaMemcpy(h->tables_dev + n0 + n1, cfg->u2_host, sizeof(float) * n2, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { cudaFree(h->tables_dev); delete h; return cuda_fail(e, "cudaMemcpy(sampler tables)"); }
+  h->lin0 = h->tables_dev;
+  h->u1 = h->tables_dev + n0;
+  h->u2 = h->tables_dev + n0 + n1;
+  *out = h;
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_destroy(NemitHandle* h) {
+  if (!h) return NEMIT_OK;
+  cudaSetDevice(h->device);
+  cudaFree(h->tables_dev);
+  delete h;
+  return NEMIT_OK;
+}
+
+static bool params_complete(const NemitParams* p) {
+  const float* const* q = reinterpret_cast<const float* const*>(p);
+  for (size_t i = 0; i < sizeof(NemitParams) / sizeof(float*); ++i)
+    if (!q[i]) return false;
+  return true;
+}
+
+extern "C" int nemit_bind_params(NemitHandle* h, const NemitParams* p) {
+  if (!h || !p) return fail(NEMIT_E_INVALID, "nemit_bind_params: null argument%s");
+  if (!params_complete(p)) return fail(NEMIT_E_INVALID, "nemit_bind_params: a parameter pointer is null%s");
+  h->P = *p;
+  h->params_bound = true;
+  return NEMIT_OK;
+}
+extern "C" int nemit_bind_grads(NemitHandle* h, const NemitParams* g) {
+  if (!h || !g) return fail(NEMIT_E_INVALID, "nemit_bind_grads: null argument%s");
+  if (!params_complete(g)) return fail(NEMIT_E_INVALID, "nemit_bind_grads: a gradient pointer is null%s");
+  h->G = *g;
+  h->grads_bound = true;
+  return NEMIT_OK;
+}
+extern "C" int64_t nemit_launch_count(const NemitHandle* h) { return h ? h->launches : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// workspace
+// ---------------------------------------------------------------------------------------------
+static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct WsLayout {
+  size_t t_edges2, s_edges2, host_stage, bwd, total;
+};
+static WsLayout ws_layout(int64_t n) {
+  int64_t c = n < kChunkRays ? n : kChunkRays;
+  if (c < 1) c = 1;
+  WsLayout L;
+  size_t off = 0;
+  L.t_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
+  L.s_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
+  L.bwd = off;      off += align_up(backward_chunk_bytes(c));
+  L.host_stage = off; off += align_up(sizeof(float) * (size_t)(n < 1 ? 1 : n) * 13);   // o,v (6) near (1) jitter (3) rgb (3)
+  L.total = off;
+  return L;
+}
+
+extern "C" size_t nemit_workspace_bytes(const NemitHandle* h, int64_t n) {
+  (void)h;
+  return ws_layout(n).total;
+}
+
+static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who) {
+  if (!h || !r) return fail(NEMIT_E_INVALID, "%s: null argument", who);
+  if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "%s: parameters not bound (nemit_bind_params)", who);
+  if (r->n < 0) return fail(NEMIT_E_INVALID, "%s: negative ray count", who);
+  if (r->n > 0 && (!r->o || !r->v)) return fail(NEMIT_E_INVALID, "%s: null ray pointers", who);
+  if (r->training && (r->camera_idx < 0 || r->camera_idx >= h->cfg.num_images))
+    return fail(NEMIT_E_INVALID, "%s: camera_idx outside the appearance embedding", who);
+  if (!(r->anneal > 0.f)) return fail(NEMIT_E_INVALID, "%s: anneal must be > 0", who);
+  return NEMIT_OK;
+}
+
+static void fill_ray_args(RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
+  A.o = r->o; A.v = r->v; A.near_per_ray = r->near_per_ray; A.near_scalar = r->near_scalar;
+  A.n_total = r->n; A.ray_offset = off; A.n = n; A.training = r->training; A.camera_idx = r->camera_idx;
+  A.jitter = r->jitter; A.anneal = r->anneal;
+}
+
+static void fill_sample_args(const NemitHandle* h, SampleArgs& S, const NemitRays* r, int64_t off, int64_t n) {
+  memset(&S, 0, sizeof(S));
+  fill_ray_args(S, r, off, n);
+  for (int i = 0; i < 2; ++i) {
+    S.prop_table[i] = reinterpret_cast<const float2*>(h->P.prop_table[i]);
+    S.prop_w0[i] = h->P.prop_w0[i]; S.prop_b0[i] = h->P.prop_b0[i];
+    S.prop_w1[i] = h->P.prop_w1[i]; S.prop_b1[i] = h->P.prop_b1[i];
+  }
+  S.lin0 = h->lin0; S.u1 = h->u1; S.u2 = h->u2;
+}
+
+static void fill_field_params(const NemitParams& P, FieldParams& F) {
+  F.main_table = reinterpret_cast<const float2*>(P.main_table);
+  F.base_w0 = P.base_w0; F.base_b0 = P.base_b0; F.base_w1 = P.base_w1; F.base_b1 = P.base_b1;
+  F.head_w0 = P.head_w0; F.head_b0 = P.head_b0; F.head_w1 = P.head_w1; F.head_b1 = P.head_b1;
+  F.head_w2 = P.head_w2; F.head_b2 = P.head_b2; F.appearance = P.appearance;
+}
+
+static void offset_levels(SampleArgs& S, const NemitLevelsOut* L, int64_t off) {
+  if (!L) return;
+  if (L->weights0) S.weights0 = L->weights0 + off * kS0;
+  if (L->weights1) S.weights1 = L->weights1 + off * kS1;
+  if (L->s_edges1) S.s_edges1 = L->s_edges1 + off * (kS1 + 1);
+  if (L->s_edges2) S.s_edges2 = L->s_edges2 + off * (kS2 + 1);
+  if (L->t_edges2) S.t_edges2 = L->t_edges2 + off * (kS2 + 1);
+  if (L->inds1) S.inds1 = L->inds1 + off * (kS1 + 1);
+  if (L->inds2) S.inds2 = L->inds2 + off * (kS2 + 1);
+}
+
+extern "C" int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const NemitLevelsOut* out,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
+  (void)workspace; (void)workspace_bytes;
+  int rc = check_rays(h, rays, "nemit_sample_levels");
+  if (rc) return rc;
+  if (!out) return fail(NEMIT_E_INVALID, "nemit_sample_levels: null outputs%s");
+  cudaSetDevice(h->device);
+  for (int64_t off = 0; off < rays->n; off += kChunkRays) {
+    int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
+    SampleArgs S;
+    fill_sample_args(h, S, rays, off, n);
+    offset_levels(S, out, off);
+    cudaError_t e = launch_sample_levels(h->M, S, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    h->launches++;
+  }
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, float* accumulation,
+                             const NemitLevelsOut* levels, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_rays(h, rays, "nemit_forward");
+  if (rc) return rc;
+  if (rays->n == 0) return NEMIT_OK;
+  if (!rgb) return fail(NEMIT_E_INVALID, "nemit_forward: null rgb output%s");
+  WsLayout L = ws_layout(rays->n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(NEMIT_E_WORKSPACE, "nemit_forward: workspace too small%s (need %lld bytes)", "", (long long)L.total);
+  cudaSetDevice(h->device);
+  char* ws = static_cast<char*>(workspace);
+  for (int64_t off = 0; off < rays->n; off += kChunkRays) {
+    int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
+    SampleArgs S;
+    fill_sample_args(h, S, rays, off, n);
+    offset_levels(S, levels, off);
+    float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
+    float* user_t = S.t_edges2;
+    S.t_edges2 = t_edges;
+    cudaError_t e = launch_sample_levels(h->M, S, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    h->launches++;
+    if (user_t) {
+      e = cudaMemcpyAsync(user_t, t_edges, sizeof(float) * n * (kS2 + 1), cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
+      if (e != cudaSuccess) return cuda_fail(e, "copy t_edges2");
+    }
+    FieldArgs F;
+    memset(&F, 0, sizeof(F));
+    fill_ray_args(F, rays, off, n);
+    fill_field_params(h->P, F.P);
+    F.t_edges2 = t_edges;
+    F.rgb = rgb + off * 3;
+    F.accumulation = accumulation ? accumulation + off : nullptr;
+    F.weights2 = (levels && levels->weights2) ? levels->weights2 + off * kS2 : nullptr;
+    e = launch_field_forward(h->M, F, (cudaStream_t)stream);
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
+    h->launches++;
+  }
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, int64_t n, float* out, void* stream) {
+  if (!h || (n > 0 && (!x || !out))) return fail(NEMIT_E_INVALID, "nemit_hash_encode: null argument%s");
+  if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_hash_encode: parameters not bound%s");
+  if (which < 0 || which > 2) return fail(NEMIT_E_INVALID, "nemit_hash_encode: which must be 0, 1 or 2%s");
+  cudaSetDevice(h->device);
+  const GridDev& G = which == 0 ? h->M.main_grid : h->M.prop_grid[which - 1];
+  const float* t = which == 0 ? h->P.main_table : h->P.prop_table[which - 1];
+  cudaError_t e = launch_hash_encode(G, reinterpret_cast<const float2*>(t), x, n, out, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_hash_encode");
+  h->launches++;
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_forward_host(NemitHandle* h, const NemitRays* rh, float* rgb_host, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  int rc = check_rays(h, rh, "nemit_forward_host");
+  if (rc) return rc;
+  if (rh->n == 0) return NEMIT_OK;
+  if (!rgb_host) return fail(NEMIT_E_INVALID, "nemit_forward_host: null rgb output%s");
+  WsLayout L = ws_layout(rh->n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(NEMIT_E_WORKSPACE, "nemit_forward_host: workspace too small%s (need %lld bytes)", "", (long long)L.total);
+  cudaSetDevice(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n = rh->n;
+  float* stage = reinterpret_cast<float*>(static_cast<char*>(workspace) + L.host_stage);
+  float *d_o = stage, *d_v = stage + 3 * n, *d_near = stage + 6 * n, *d_jit = stage + 7 * n, *d_rgb = stage + 10 * n;
+  cudaError_t e;
+  if ((e = cudaMemcpyAsync(d_o, rh->o, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D o");
+  if ((e = cudaMemcpyAsync(d_v, rh->v, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D v");
+  NemitRays rd = *rh;
+  rd.o = d_o; rd.v = d_v;
+  if (rh->near_per_ray) {
+    if ((e = cudaMemcpyAsync(d_near, rh->near_per_ray, sizeof(float) * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D near");
+    rd.near_per_ray = d_near;
+  }
+  if (rh->jitter) {
+    if ((e = cudaMemcpyAsync(d_jit, rh->jitter, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D jitter");
+    rd.jitter = d_jit;
+  }
+  rc = nemit_forward(h, &rd, d_rgb, nullptr, nullptr, workspace, workspace_bytes, stream);
+  if (rc) return rc;
+  if ((e = cudaMemcpyAsync(rgb_host, d_rgb, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuda_fail(e, "D2H rgb");
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// vMF mixture (DS/emitters/vMF.py)
+// ---------------------------------------------------------------------------------------------
+static int check_lobes(const NemitVmfLobes* l, const char* who) {
+  if (!l || !l->position || !l->weight || !l->std) return fail(NEMIT_E_INVALID, "%s: null lobe table", who);
+  if (l->num_lobes < 1 || l->num_lobes > 1024) return fail(NEMIT_E_INVALID, "%s: num_lobes must be in [1,1024]", who);
+  return NEMIT_OK;
+}
+extern "C" int nemit_vmf_sample(const NemitVmfLobes* lobes, const float* p, const float* u, int64_t n, float* d,
+                                float* pdf, void* stream) {
+  int rc = check_lobes(lobes, "nemit_vmf_sample");
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!p || !u || !d || !pdf))) return fail(NEMIT_E_INVALID, "nemit_vmf_sample: bad sample arguments%s");
+  cudaError_t e = launch_vmf_sample(lobes->position, lobes->weight, lobes->std, lobes->num_lobes, p, u, n, d, pdf,
+                                    (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_sample");
+}
+extern "C" int nemit_vmf_pdf(const NemitVmfLobes* lobes, const float* p, const float* d, int64_t n, float* pdf,
+                             void* stream) {
+  int rc = check_lobes(lobes, "nemit_vmf_pdf");
+  if (rc) return rc;
+  if (n < 0 || (n > 0 && (!p || !d || !pdf))) return fail(NEMIT_E_INVALID, "nemit_vmf_pdf: bad sample arguments%s");
+  cudaError_t e = launch_vmf_pdf(lobes->position, lobes->weight, lobes->std, lobes->num_lobes, p, d, n, pdf,
+                                 (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_pdf");
+}

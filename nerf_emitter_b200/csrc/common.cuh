@@ -1,0 +1,218 @@
+// common.cuh - shared device helpers of libnerfemitter (sm_100a).
+//
+// Arithmetic that feeds the PDF resampling (spacing maps, sample positions, contraction, hash
+// coordinates) is written with explicit round-to-nearest intrinsics (__fmul_rn / __fadd_rn /
+// __fdiv_rn): nvcc must not contract a*b+c into an FMA there, because the parity gate asks for
+// searchsorted indices that are bit-equal to the reference's torch-CPU arithmetic, which rounds
+// after every operation.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/nemit.h"
+
+#define NEMIT_PRIME_Y 2654435761u
+#define NEMIT_PRIME_Z 805459861u
+
+namespace nemit {
+
+constexpr int kS0 = 256;         // proposal samples level 0
+constexpr int kS1 = 96;          // proposal samples level 1
+constexpr int kS2 = 48;          // nerf samples
+constexpr int kPropLevels = 5;
+constexpr int kPropEnc = 10;     // 5 levels x 2 features
+constexpr int kPropHidden = 16;
+constexpr int kMainLevels = 16;
+constexpr int kMainEnc = 32;
+constexpr int kHidden = 64;
+constexpr int kGeo = 15;
+constexpr int kApp = 32;
+constexpr int kHeadIn = 63;      // 16 SH + 15 geo + 32 appearance
+
+struct GridDev {
+  int num_levels;
+  uint32_t table_mask;           // T-1 (T is a power of two)
+  uint32_t table_size;
+  float scal[NEMIT_MAX_LEVELS];
+};
+
+// Everything a kernel needs that is constant for a handle; passed by value (__grid_constant__).
+struct ModelDev {
+  GridDev main_grid;
+  GridDev prop_grid[2];
+  float aabb_min[3], aabb_max[3];
+  float scene_scale;
+  float near_plane, far_plane;
+  float rgb_bias;
+  int disable_inside_aabb;
+  int cpu_sum_width;
+  int num_images;
+  float interlevel_mult, distortion_mult;
+};
+
+// ---------------------------------------------------------------------------------------------
+// exact (non-contracted) fp32 helpers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+
+// NS/model_components/ray_samplers.py:250  spacing_fn
+__device__ __forceinline__ float spacing_fwd(float x) {
+  return x < 1.f ? div_rn(x, 2.f) : sub_rn(1.f, div_rn(1.f, mul_rn(2.f, x)));
+}
+// ray_samplers.py:251  spacing_fn_inv
+__device__ __forceinline__ float spacing_inv(float s) {
+  return s < 0.5f ? mul_rn(2.f, s) : div_rn(1.f, sub_rn(2.f, mul_rn(2.f, s)));
+}
+// ray_samplers.py:121-122  spacing_to_euclidean_fn: f_inv(x*s_far + (1-x)*s_near)
+__device__ __forceinline__ float s_to_t(float s, float s_near, float s_far) {
+  return spacing_inv(add_rn(mul_rn(s, s_far), mul_rn(sub_rn(1.f, s), s_near)));
+}
+
+// Mitsuba unit cube -> NeRF coordinates (DS/emitters/nerf_op.py:76-89, NS/utils/mi_gl_conversion.py:4-9,40-42):
+// o_mi' = o + near*v ; x = (o_mi'*2-1)*scale ; (x,y,z) -> (z,x,y).
+__device__ __forceinline__ void load_ray(const float* __restrict__ o, const float* __restrict__ v,
+                                         const float* __restrict__ near_per_ray, float near_scalar,
+                                         int64_t n, int64_t r, float scene_scale, float oo[3], float dd[3]) {
+  float nr = near_per_ray ? near_per_ray[r] : near_scalar;
+  float vm[3] = {v[r], v[n + r], v[2 * n + r]};
+  float om[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    float x = add_rn(o[k * n + r], mul_rn(nr, vm[k]));
+    om[k] = mul_rn(sub_rn(mul_rn(x, 2.f), 1.f), scene_scale);
+  }
+  // matmul with the permutation matrix adds exact zeros; the + 0 translation is exact as well
+  oo[0] = om[2]; oo[1] = om[0]; oo[2] = om[1];
+  dd[0] = vm[2]; dd[1] = vm[0]; dd[2] = vm[1];
+}
+
+// NS/cameras/rays.py:49-58: pos = o + d*(t0+t1)/2 (evaluated as ((d*(t0+t1))/2) + o)
+__device__ __forceinline__ float sample_pos(float o, float d, float tsum) {
+  return add_rn(o, mul_rn(mul_rn(d, tsum), 0.5f));
+}
+
+// SceneContraction(order=inf) + (x+2)/4 + selector (NS/field_components/spatial_distortions.py:67-70,
+// NS/fields/density_fields.py:96-106, NS/data/scene_box.py:36-37). Returns selector; p is zeroed when
+// the selector is false (density_fields.py:106).
+__device__ __forceinline__ bool contract_normalise(const float x[3], const ModelDev& M, float p[3]) {
+  float mag = fmaxf(fabsf(x[0]), fmaxf(fabsf(x[1]), fabsf(x[2])));
+  bool sel = true;
+  if (mag < 1.f) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) p[k] = x[k];
+  } else {
+    float f = sub_rn(2.f, div_rn(1.f, mag));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) p[k] = mul_rn(f, div_rn(x[k], mag));
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    p[k] = div_rn(add_rn(p[k], 2.f), 4.f);
+    sel = sel && (p[k] > 0.f) && (p[k] < 1.f);
+  }
+  if (M.disable_inside_aabb) {
+    bool inside = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) inside = inside && (x[k] > M.aabb_min[k]) && (x[k] < M.aabb_max[k]);
+    sel = sel && !inside;
+  }
+  if (!sel) { p[0] = 0.f; p[1] = 0.f; p[2] = 0.f; }
+  return sel;
+}
+
+// NS/field_components/encodings.py:322-339: (x*1) ^ (y*2654435761) ^ (z*805459861) mod T. The
+// reference multiplies in int64; for T a power of two <= 2^32 the low bits equal the uint32 product.
+__device__ __forceinline__ uint32_t hash3(uint32_t x, uint32_t y, uint32_t z, uint32_t mask) {
+  return (x ^ (y * NEMIT_PRIME_Y) ^ (z * NEMIT_PRIME_Z)) & mask;
+}
+
+// One level of the torch-path hash grid (encodings.py:341-382): 8 gathers + trilinear blend in the
+// reference's order (ceil corner weighted by the offset, floor by 1-offset; x, then y, then z).
+struct LevelCell {
+  uint32_t idx[8];   // order: (cx,cy,cz) (fx,cy,cz) (cx,fy,cz) (fx,fy,cz) (cx,cy,fz) (fx,cy,fz) (cx,fy,fz) (fx,fy,fz)
+  float fx, fy, fz;
+};
+
+__device__ __forceinline__ void level_cell(const float p[3], float scale, uint32_t mask, uint32_t level_off,
+                                           LevelCell& c) {
+  float xs = mul_rn(p[0], scale), ys = mul_rn(p[1], scale), zs = mul_rn(p[2], scale);
+  float xf = floorf(xs), yf = floorf(ys), zf = floorf(zs);
+  uint32_t x0 = (uint32_t)(int)xf, y0 = (uint32_t)(int)yf, z0 = (uint32_t)(int)zf;
+  uint32_t x1 = (uint32_t)(int)ceilf(xs), y1 = (uint32_t)(int)ceilf(ys), z1 = (uint32_t)(int)ceilf(zs);
+  c.fx = sub_rn(xs, xf); c.fy = sub_rn(ys, yf); c.fz = sub_rn(zs, zf);
+  uint32_t hx0 = x0, hx1 = x1;
+  uint32_t hy0 = y0 * NEMIT_PRIME_Y, hy1 = y1 * NEMIT_PRIME_Y;
+  uint32_t hz0 = z0 * NEMIT_PRIME_Z, hz1 = z1 * NEMIT_PRIME_Z;
+  c.idx[0] = ((hx1 ^ hy1 ^ hz1) & mask) + level_off;
+  c.idx[1] = ((hx0 ^ hy1 ^ hz1) & mask) + level_off;
+  c.idx[2] = ((hx1 ^ hy0 ^ hz1) & mask) + level_off;
+  c.idx[3] = ((hx0 ^ hy0 ^ hz1) & mask) + level_off;
+  c.idx[4] = ((hx1 ^ hy1 ^ hz0) & mask) + level_off;
+  c.idx[5] = ((hx0 ^ hy1 ^ hz0) & mask) + level_off;
+  c.idx[6] = ((hx1 ^ hy0 ^ hz0) & mask) + level_off;
+  c.idx[7] = ((hx0 ^ hy0 ^ hz0) & mask) + level_off;
+}
+
+__device__ __forceinline__ float lerp_ref(float a_hi, float b_lo, float f) {
+  // a*f + b*(1-f), each product and the sum rounded (torch evaluates them as separate ops)
+  return add_rn(mul_rn(a_hi, f), mul_rn(b_lo, sub_rn(1.f, f)));
+}
+
+__device__ __forceinline__ float2 blend_cell(const float2 v[8], const LevelCell& c) {
+  float2 r;
+  {
+    float a = lerp_ref(v[0].x, v[1].x, c.fx), b = lerp_ref(v[2].x, v[3].x, c.fx);
+    float cc = lerp_ref(v[4].x, v[5].x, c.fx), d = lerp_ref(v[6].x, v[7].x, c.fx);
+    r.x = lerp_ref(lerp_ref(a, b, c.fy), lerp_ref(cc, d, c.fy), c.fz);
+  }
+  {
+    float a = lerp_ref(v[0].y, v[1].y, c.fx), b = lerp_ref(v[2].y, v[3].y, c.fx);
+    float cc = lerp_ref(v[4].y, v[5].y, c.fx), d = lerp_ref(v[6].y, v[7].y, c.fx);
+    r.y = lerp_ref(lerp_ref(a, b, c.fy), lerp_ref(cc, d, c.fy), c.fz);
+  }
+  return r;
+}
+
+__device__ __forceinline__ float2 ldg_f2(const float2* __restrict__ t, uint32_t i) { return __ldg(t + i); }
+
+// torch.nan_to_num defaults: nan -> 0, +inf -> FLT_MAX, -inf -> -FLT_MAX
+__device__ __forceinline__ float nan_to_num(float x) {
+  if (isnan(x)) return 0.f;
+  if (isinf(x)) return x > 0.f ? 3.4028234663852886e38f : -3.4028234663852886e38f;
+  return x;
+}
+
+__device__ __forceinline__ double warp_incl_scan(double v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    double t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// weights of one level from the per-sample delta*sigma held in registers (sample i = k*32 + lane).
+// Exclusive prefix accumulated in float64 and rounded to float32 per prefix, as ATen's CPU cumsum does.
+template <int K>
+__device__ __forceinline__ void weights_from_ds(const float (&ds)[K], float (&w)[K], int lane) {
+  double carry = 0.0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double inc = warp_incl_scan((double)ds[k], lane);
+    double exc = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) exc = 0.0;
+    float prefix = (float)(carry + exc);
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+    float alpha = sub_rn(1.f, expf(-ds[k]));
+    w[k] = nan_to_num(mul_rn(alpha, expf(-prefix)));
+  }
+}
+
+}  // namespace nemit

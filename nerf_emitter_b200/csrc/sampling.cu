@@ -1,0 +1,85 @@
+// sampling.cu - k_sample_levels: the proposal loop of one ray per warp.
+// Output: the 49 spacing / euclidean edges of the final 48 samples (+ optional per-level outputs).
+#include "sampling.cuh"
+#include "kernels.h"
+
+namespace nemit {
+
+constexpr int kWarpsPerCta = 8;
+
+struct SampleSmem {
+  PropMlpSmem mlp[2];
+  WarpScratch warp[kWarpsPerCta];
+};
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ SampleArgs A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  SampleSmem* sm = reinterpret_cast<SampleSmem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  for (int i = 0; i < 2; ++i)
+    load_prop_mlp(&sm->mlp[i], A.prop_w0[i], A.prop_b0[i], A.prop_w1[i], A.prop_b1[i], tid, blockDim.x);
+  __syncthreads();
+  WarpScratch* sc = &sm->warp[wid];
+
+  for (int64_t r = (int64_t)blockIdx.x * kWarpsPerCta + wid; r < A.n; r += (int64_t)gridDim.x * kWarpsPerCta) {
+    RayCtx R;
+    load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r, M.scene_scale, R.o, R.d);
+    const float near = A.training ? M.near_plane : 0.f;      // NearFarCollider, scene_colliders.py:217-222
+    R.s_near = spacing_fwd(mul_rn(1.f, near));
+    R.s_far = spacing_fwd(mul_rn(1.f, M.far_plane));
+    const float* jit = A.jitter ? A.jitter + (A.ray_offset + r) * 3 : nullptr;
+    const float j0 = jit ? jit[0] : -1.f, j1 = jit ? jit[1] : -1.f, j2 = jit ? jit[2] : -1.f;
+
+    // ---- level 0: 256 piecewise-spaced bins ------------------------------------------------
+    initial_edges(sc, A.lin0, j0, lane);
+    float w0[kS0 / 32];
+    proposal_level_weights<kS0>(sc, R, A.prop_table[0], M.prop_grid[0], &sm->mlp[0], M, lane, w0);
+    if (A.weights0) {
+#pragma unroll
+      for (int k = 0; k < kS0 / 32; ++k) A.weights0[r * kS0 + k * 32 + lane] = w0[k];
+    }
+    pdf_resample_warp<kS0>(sc, w0, kS1, A.u1, j1, A.anneal, M.cpu_sum_width, lane,
+                           A.inds1 ? A.inds1 + r * (kS1 + 1) : nullptr);
+    // ---- level 1: 96 bins ------------------------------------------------------------------
+    for (int i = lane; i <= kS1; i += 32) {
+      float e = sc->s_new[i];
+      sc->s_edge[i] = e;
+      if (A.s_edges1) A.s_edges1[r * (kS1 + 1) + i] = e;
+    }
+    __syncwarp();
+    float w1[kS1 / 32];
+    proposal_level_weights<kS1>(sc, R, A.prop_table[1], M.prop_grid[1], &sm->mlp[1], M, lane, w1);
+    if (A.weights1) {
+#pragma unroll
+      for (int k = 0; k < kS1 / 32; ++k) A.weights1[r * kS1 + k * 32 + lane] = w1[k];
+    }
+    pdf_resample_warp<kS1>(sc, w1, kS2, A.u2, j2, A.anneal, M.cpu_sum_width, lane,
+                           A.inds2 ? A.inds2 + r * (kS2 + 1) : nullptr);
+    // ---- level 2 edges ---------------------------------------------------------------------
+    for (int i = lane; i <= kS2; i += 32) {
+      float s = sc->s_new[i];
+      if (A.s_edges2) A.s_edges2[r * (kS2 + 1) + i] = s;
+      if (A.t_edges2) A.t_edges2[r * (kS2 + 1) + i] = s_to_t(s, R.s_near, R.s_far);
+    }
+    __syncwarp();
+  }
+}
+
+cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream) {
+  if (A.n <= 0) return cudaSuccess;
+  static bool attr_set = false;
+  size_t smem = sizeof(SampleSmem);
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k_sample_levels, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  int64_t ctas = (A.n + kWarpsPerCta - 1) / kWarpsPerCta;
+  const int64_t max_ctas = 148 * 8 * 16;
+  if (ctas > max_ctas) ctas = max_ctas;
+  k_sample_levels<<<(unsigned)ctas, kWarpsPerCta * 32, smem, stream>>>(M, A);
+  return cudaGetLastError();
+}
+
+}  // namespace nemit

@@ -1,0 +1,214 @@
+// sampling.cuh - warp-cooperative per-ray proposal loop (levels 0 and 1) shared by the forward and
+// backward kernels.  One warp owns one ray; lane L owns samples L, L+32, L+64, ... so that
+// neighbouring lanes look up neighbouring points of the same ray (same / adjacent hash cells on the
+// coarse levels -> the 8-byte gathers of a warp coalesce into few 32-byte sectors).
+//
+// Follows ProposalNetworkSampler.generate_ray_samples (NS/model_components/ray_samplers.py:584-626),
+// UniformLinDispPiecewiseSampler (:231-254, :82-134), PDFSampler (:282-380),
+// HashMLPDensityField.get_density (NS/fields/density_fields.py:95-122) and RaySamples.get_weights
+// (NS/cameras/rays.py:128-150).
+#pragma once
+#include "common.cuh"
+
+namespace nemit {
+
+// proposal MLP in shared memory: row j = {W0[j][0..9], b0[j], w1[j]} (12 floats, 16 rows) + b1
+struct PropMlpSmem {
+  float row[kPropHidden][12];
+  float b1;
+  float pad[3];
+};
+
+__device__ __forceinline__ void load_prop_mlp(PropMlpSmem* dst, const float* __restrict__ w0,
+                                              const float* __restrict__ b0, const float* __restrict__ w1,
+                                              const float* __restrict__ b1, int tid, int nthreads) {
+  for (int i = tid; i < kPropHidden * 12; i += nthreads) {
+    int j = i / 12, k = i % 12;
+    float v;
+    if (k < kPropEnc) v = w0[j * kPropEnc + k];
+    else if (k == kPropEnc) v = b0[j];
+    else v = w1[j];
+    dst->row[j][k] = v;
+  }
+  if (tid == 0) dst->b1 = b1[0];
+}
+
+// hash-encode one point on a 5-level proposal grid
+__device__ __forceinline__ void prop_encode(const float p[3], const float2* __restrict__ table, const GridDev& G,
+                                            float enc[kPropEnc]) {
+  LevelCell cell[kPropLevels];
+  float2 v[kPropLevels][8];
+#pragma unroll
+  for (int l = 0; l < kPropLevels; ++l) {
+    level_cell(p, G.scal[l], G.table_mask, (uint32_t)l * G.table_size, cell[l]);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v[l][c] = ldg_f2(table, cell[l].idx[c]);
+  }
+#pragma unroll
+  for (int l = 0; l < kPropLevels; ++l) {
+    float2 r = blend_cell(v[l], cell[l]);
+    enc[2 * l] = r.x;
+    enc[2 * l + 1] = r.y;
+  }
+}
+
+// raw (pre-activation) density of the proposal MLP; optionally returns the hidden pre-activations
+__device__ __forceinline__ float prop_mlp_raw(const float enc[kPropEnc], const PropMlpSmem* W) {
+  float raw = W->b1;
+#pragma unroll
+  for (int j = 0; j < kPropHidden; ++j) {
+    const float4* r4 = reinterpret_cast<const float4*>(W->row[j]);
+    float4 a = r4[0], b = r4[1], c = r4[2];
+    float h = c.z;  // b0[j]
+    h = fmaf(a.x, enc[0], h); h = fmaf(a.y, enc[1], h); h = fmaf(a.z, enc[2], h); h = fmaf(a.w, enc[3], h);
+    h = fmaf(b.x, enc[4], h); h = fmaf(b.y, enc[5], h); h = fmaf(b.z, enc[6], h); h = fmaf(b.w, enc[7], h);
+    h = fmaf(c.x, enc[8], h); h = fmaf(c.y, enc[9], h);
+    raw = fmaf(c.w, fmaxf(h, 0.f), raw);
+  }
+  return raw;
+}
+
+// density at a sample position (NeRF coordinates): contraction -> hash -> MLP -> trunc_exp * selector
+__device__ __forceinline__ float prop_density(const float x[3], const float2* __restrict__ table, const GridDev& G,
+                                              const PropMlpSmem* W, const ModelDev& M) {
+  float p[3];
+  if (!contract_normalise(x, M, p)) return 0.f;   // reference evaluates at p=0 and multiplies by 0
+  float enc[kPropEnc];
+  prop_encode(p, table, G, enc);
+  return expf(prop_mlp_raw(enc, W));
+}
+
+// per-warp scratch of the proposal loop
+struct WarpScratch {
+  float s_edge[kS0 + 4];   // spacing edges of the current level (S+1 used)
+  float buf[kS0 + 4];      // padded weights, then cdf (S+1 used)
+  float s_new[kS1 + 4];    // edges produced by the PDF stage (M+1 used)
+};
+
+// ATen's CPU float sum over a contiguous row (aten/src/ATen/native/cpu/SumKernel.cpp, row_sum with
+// ilp_factor 4 over Vectorized<float> of width V): reproduced so that pdf = w / sum(w) has the same
+// bits as torch.sum on the reference's CPU path.  `w` in shared memory, n values.  All lanes return
+// the sum.  V == 0 selects a float64 sum rounded once.
+__device__ __forceinline__ float row_sum_like_aten(const float* w, int n, int V, int lane) {
+  if (V <= 0) {
+    double acc = 0.0;
+    for (int i = lane; i < n; i += 32) acc += (double)w[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    return (float)acc;
+  }
+  const int nv = n / V;          // whole vectors
+  const int n_ilp = nv / 4;
+  float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
+  if (lane < V) {
+    for (int i = 0; i < n_ilp; ++i) {
+      p0 = add_rn(p0, w[(i * 4 + 0) * V + lane]);
+      p1 = add_rn(p1, w[(i * 4 + 1) * V + lane]);
+      p2 = add_rn(p2, w[(i * 4 + 2) * V + lane]);
+      p3 = add_rn(p3, w[(i * 4 + 3) * V + lane]);
+    }
+    for (int i = n_ilp * 4; i < nv; ++i) p0 = add_rn(p0, w[i * V + lane]);
+    p0 = add_rn(add_rn(add_rn(p0, p1), p2), p3);
+  }
+  float acc = 0.f;
+  for (int k = nv * V; k < n; ++k) acc = add_rn(acc, w[k]);   // scalar tail first
+  for (int l = 0; l < V; ++l) acc = add_rn(acc, __shfl_sync(0xffffffffu, p0, l));
+  return acc;
+}
+
+// PDFSampler.generate_ray_samples for one ray: S existing bins (edges in sc->s_edge, weights in
+// registers), M new samples -> M+1 new edges into sc->s_new.  u_base = linspace(0,1-1/nb,nb) from the
+// host.  jit < 0 means deterministic.  inds_out (M+1) optional.
+template <int S>
+__device__ __forceinline__ void pdf_resample_warp(WarpScratch* sc, const float (&w)[S / 32], int M,
+                                                  const float* __restrict__ u_base, float jit, float anneal,
+                                                  int sum_width, int lane, int32_t* inds_out) {
+  constexpr int K = S / 32;
+  const int nb = M + 1;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    float x = w[k];
+    if (anneal != 1.f) x = powf(x, anneal);
+    sc->buf[k * 32 + lane] = add_rn(x, 0.01f);
+  }
+  __syncwarp();
+  float tot = row_sum_like_aten(sc->buf, S, sum_width, lane);
+  float fill = fmaxf(sub_rn(1e-5f, tot), 0.f);
+  float fill_each = div_rn(fill, (float)S);
+  tot = add_rn(tot, fill);
+  float pdf[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) pdf[k] = div_rn(add_rn(sc->buf[k * 32 + lane], fill_each), tot);
+  __syncwarp();
+  double carry = 0.0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double inc = warp_incl_scan((double)pdf[k], lane);
+    sc->buf[k * 32 + lane + 1] = fminf(1.f, (float)(carry + inc));
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) sc->buf[0] = 0.f;
+  __syncwarp();
+  const float half_step = (float)(1.0 / (2.0 * (double)nb));
+  for (int k = lane; k <= M; k += 32) {
+    float u = (jit >= 0.f) ? add_rn(u_base[k], div_rn(jit, (float)nb)) : add_rn(u_base[k], half_step);
+    int lo = 0, hi = S + 1;          // searchsorted(cdf, u, side="right") over S+1 entries
+    while (lo < hi) {
+      int mid = (lo + hi) >> 1;
+      if (sc->buf[mid] <= u) lo = mid + 1; else hi = mid;
+    }
+    if (inds_out) inds_out[k] = lo;
+    int i0 = min(max(lo - 1, 0), S), i1 = min(max(lo, 0), S);
+    float c0 = sc->buf[i0], c1 = sc->buf[i1];
+    float e0 = sc->s_edge[i0], e1 = sc->s_edge[i1];
+    float t = div_rn(sub_rn(u, c0), sub_rn(c1, c0));
+    t = isnan(t) ? 0.f : t;                        // nan_to_num(.., 0) then clip
+    t = fminf(fmaxf(t, 0.f), 1.f);
+    sc->s_new[k] = add_rn(e0, mul_rn(t, sub_rn(e1, e0)));
+  }
+  __syncwarp();
+}
+
+struct RayCtx {
+  float o[3], d[3];
+  float s_near, s_far;
+};
+
+// One proposal level: density at the S bin midpoints, weights. Edges must be in sc->s_edge[0..S].
+template <int S>
+__device__ __forceinline__ void proposal_level_weights(const WarpScratch* sc, const RayCtx& R,
+                                                       const float2* __restrict__ table, const GridDev& G,
+                                                       const PropMlpSmem* W, const ModelDev& M, int lane,
+                                                       float (&w)[S / 32]) {
+  constexpr int K = S / 32;
+  float ds[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    int i = k * 32 + lane;
+    float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far);
+    float t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
+    float tsum = add_rn(t0, t1);
+    float x[3] = {sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
+                  sample_pos(R.o[2], R.d[2], tsum)};
+    float sigma = prop_density(x, table, G, W, M);
+    ds[k] = mul_rn(sub_rn(t1, t0), sigma);
+  }
+  weights_from_ds<K>(ds, w, lane);
+}
+
+// initial edges (ray_samplers.py:104-117): lin0 = linspace(0,1,S0+1) from the host; with jitter the
+// edges move inside [midpoint below, midpoint above].
+__device__ __forceinline__ void initial_edges(WarpScratch* sc, const float* __restrict__ lin0, float jit, int lane) {
+  for (int i = lane; i <= kS0; i += 32) {
+    float e = lin0[i];
+    if (jit >= 0.f) {
+      float lo = (i == 0) ? lin0[0] : div_rn(add_rn(lin0[i], lin0[i - 1]), 2.f);
+      float hi = (i == kS0) ? lin0[kS0] : div_rn(add_rn(lin0[i + 1], lin0[i]), 2.f);
+      e = add_rn(lo, mul_rn(sub_rn(hi, lo), jit));
+    }
+    sc->s_edge[i] = e;
+  }
+  __syncwarp();
+}
+
+}  // namespace nemit

@@ -1,0 +1,284 @@
+"""Host side of the emitter path: owns a libnerfemitter handle and mirrors the three modes of the
+reference's ``NeRFEmitterOp`` (DS/emitters/nerf_emitter_op.py:38-117) on torch CUDA tensors.
+
+Parameters stay ordinary torch tensors named as in the reference ``state_dict``; the
+library borrows their device pointers.  There is no fallback: every call goes through the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from . import lib as L
+from .params import EmitterModelSpec, all_param_names, param_shapes, prop_param_names
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _check(t: torch.Tensor, shape, name, dtype=torch.float32):
+    if t.dtype != dtype or not t.is_cuda or not t.is_contiguous() or tuple(t.shape) != tuple(shape):
+        raise ValueError("%s must be a contiguous CUDA %s tensor of shape %s, got %s %s %s" % (
+            name, dtype, tuple(shape), t.dtype, tuple(t.shape), t.device))
+
+
+def sampler_tables(spec: EmitterModelSpec):
+    """The samplers' linspace tables, computed by torch on the CPU so that they are bit-identical to
+    NS/model_components/ray_samplers.py:104 and :323-331."""
+    s0, s1 = spec.num_proposal_samples
+    s2 = spec.num_nerf_samples
+    lin0 = torch.linspace(0.0, 1.0, s0 + 1)
+    u1 = torch.linspace(0.0, 1.0 - (1.0 / (s1 + 1)), steps=s1 + 1)
+    u2 = torch.linspace(0.0, 1.0 - (1.0 / (s2 + 1)), steps=s2 + 1)
+    return lin0.contiguous(), u1.contiguous(), u2.contiguous()
+
+
+class NerfEmitter:
+    """B200 evaluation of the nerfacto emitter: ``render`` / ``jvp`` / ``backward`` take Mitsuba-space
+    rays as (3,N) fp32 CUDA tensors exactly like the dr.CustomOp and return (N,3) radiance."""
+
+    def __init__(self, params: Dict[str, torch.Tensor], spec: Optional[EmitterModelSpec] = None,
+                 device: Optional[torch.device] = None, scene_scale: float = 1.0,
+                 disable_inside_aabb: bool = True, interlevel_mult: float = 1.0, distortion_mult: float = 7e-3,
+                 cpu_sum_width: int = 8):
+        self.lib = L.load()
+        self.spec = spec = spec or EmitterModelSpec()
+        if device is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.NemitError("NerfEmitter needs a CUDA device; there is no CPU path")
+        self.scene_scale = float(scene_scale)
+        self.training = False
+        self.anneal = 1.0
+        cfg = L.NemitConfig()
+        for g, dst in [(spec.main_grid, cfg.main_grid), (spec.prop_grids[0], cfg.prop_grid[0]),
+                       (spec.prop_grids[1], cfg.prop_grid[1])]:
+            dst.num_levels = g.num_levels
+            dst.log2_table_size = g.log2_hashmap_size
+            for i, s in enumerate(g.scalings()):
+                dst.scalings[i] = s
+        cfg.num_prop_samples[0], cfg.num_prop_samples[1] = spec.num_proposal_samples
+        cfg.num_nerf_samples = spec.num_nerf_samples
+        cfg.hidden_dim, cfg.geo_feat_dim, cfg.appearance_dim = spec.hidden_dim, spec.geo_feat_dim, spec.appearance_dim
+        cfg.prop_hidden_dim, cfg.num_images = spec.prop_hidden, spec.num_images
+        cfg.near_plane, cfg.far_plane, cfg.scene_scale = spec.near_plane, spec.far_plane, scene_scale
+        for i, v in enumerate([-scene_scale] * 3 + [scene_scale] * 3):
+            cfg.aabb[i] = v
+        cfg.rgb_bias = spec.rgb_bias
+        cfg.disable_inside_aabb = int(disable_inside_aabb)
+        cfg.cpu_sum_width = cpu_sum_width
+        cfg.interlevel_mult, cfg.distortion_mult = interlevel_mult, distortion_mult
+        self._tables = sampler_tables(spec)
+        cfg.lin0_host = C.cast(self._tables[0].data_ptr(), L.c_float_p)
+        cfg.u1_host = C.cast(self._tables[1].data_ptr(), L.c_float_p)
+        cfg.u2_host = C.cast(self._tables[2].data_ptr(), L.c_float_p)
+        self._h = C.c_void_p()
+        L.check(self.lib.nemit_create(C.byref(cfg), self.device.index or 0, C.byref(self._h)), "nemit_create")
+        self._ws = None
+        self.params: Dict[str, torch.Tensor] = {}
+        self.grads: Dict[str, torch.Tensor] = {}
+        self.bind_params(params)
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            self.lib.nemit_destroy(h)
+            self._h = C.c_void_p()
+
+    # -- parameters ------------------------------------------------------------------------
+    def _pack(self, tensors: Dict[str, torch.Tensor]) -> L.NemitParams:
+        shapes = param_shapes(self.spec)
+        for n in all_param_names():
+            if n not in tensors:
+                raise KeyError("missing parameter %s" % n)
+            _check(tensors[n], shapes[n], n)
+        P = L.NemitParams()
+        main = ["field.mlp_base_grid.hash_table",
+                "field.mlp_base_mlp.layers.0.weight", "field.mlp_base_mlp.layers.0.bias",
+                "field.mlp_base_mlp.layers.1.weight", "field.mlp_base_mlp.layers.1.bias",
+                "field.mlp_head.layers.0.weight", "field.mlp_head.layers.0.bias",
+                "field.mlp_head.layers.1.weight", "field.mlp_head.layers.1.bias",
+                "field.mlp_head.layers.2.weight", "field.mlp_head.layers.2.bias",
+                "field.embedding_appearance.embedding.weight"]
+        for f, n in zip(L.PARAM_FIELDS, main):
+            setattr(P, f, tensors[n].data_ptr())
+        for i in range(2):
+            names = prop_param_names(i)
+            P.prop_table[i] = tensors[names[0]].data_ptr()
+            P.prop_w0[i] = tensors[names[1]].data_ptr()
+            P.prop_b0[i] = tensors[names[2]].data_ptr()
+            P.prop_w1[i] = tensors[names[3]].data_ptr()
+            P.prop_b1[i] = tensors[names[4]].data_ptr()
+        return P
+
+    def bind_params(self, params: Dict[str, torch.Tensor]):
+        """Borrow the parameter tensors (moved to the device once if they are not there yet)."""
+        self.params = {k: v.detach().to(self.device, torch.float32).contiguous() for k, v in params.items()}
+        self._P = self._pack(self.params)
+        L.check(self.lib.nemit_bind_params(self._h, C.byref(self._P)), "nemit_bind_params")
+
+    def bind_grads(self, grads: Optional[Dict[str, torch.Tensor]] = None):
+        """Bind gradient accumulators (``param.grad`` tensors). Created zero-filled if not given."""
+        if grads is None:
+            grads = {k: torch.zeros_like(v) for k, v in self.params.items()}
+        self.grads = grads
+        self._G = self._pack(self.grads)
+        L.check(self.lib.nemit_bind_grads(self._h, C.byref(self._G)), "nemit_bind_grads")
+        return grads
+
+    def zero_grads(self):
+        for g in self.grads.values():
+            g.zero_()
+
+    def train(self, mode: bool = True):
+        self.training = bool(mode)
+        return self
+
+    def eval(self):
+        return self.train(False)
+
+    # -- plumbing --------------------------------------------------------------------------
+    def _workspace(self, n: int) -> torch.Tensor:
+        need = int(self.lib.nemit_workspace_bytes(self._h, n))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _rays(self, o3n, v3n, near, camera_idx, jitter) -> L.NemitRays:
+        n = o3n.shape[1]
+        _check(o3n, (3, n), "o")
+        _check(v3n, (3, n), "v")
+        R = L.NemitRays()
+        R.o, R.v, R.n = o3n.data_ptr(), v3n.data_ptr(), n
+        self._keep = [o3n, v3n]
+        if isinstance(near, torch.Tensor):
+            near = near.reshape(-1).to(self.device, torch.float32).contiguous()
+            _check(near, (n,), "near")
+            R.near_per_ray = near.data_ptr()
+            self._keep.append(near)
+        else:
+            R.near_per_ray = None
+            R.near_scalar = float(near)
+        R.camera_idx = int(camera_idx)
+        R.training = int(self.training)
+        if jitter is not None and self.training:
+            if isinstance(jitter, (list, tuple)):
+                jitter = torch.cat([j.reshape(n, 1) for j in jitter], dim=1)
+            jitter = jitter.to(self.device, torch.float32).contiguous()
+            _check(jitter, (n, 3), "jitter")
+            R.jitter = jitter.data_ptr()
+            self._keep.append(jitter)
+        else:
+            R.jitter = None
+        R.anneal = float(self.anneal)
+        return R
+
+    def _levels_out(self, n: int, want_weights2: bool):
+        s0, s1 = self.spec.num_proposal_samples
+        s2 = self.spec.num_nerf_samples
+        f = dict(device=self.device, dtype=torch.float32)
+        out = dict(weights0=torch.empty(n, s0, **f), weights1=torch.empty(n, s1, **f),
+                   s_edges1=torch.empty(n, s1 + 1, **f), s_edges2=torch.empty(n, s2 + 1, **f),
+                   t_edges2=torch.empty(n, s2 + 1, **f),
+                   inds1=torch.empty(n, s1 + 1, device=self.device, dtype=torch.int32),
+                   inds2=torch.empty(n, s2 + 1, device=self.device, dtype=torch.int32))
+        if want_weights2:
+            out["weights2"] = torch.empty(n, s2, **f)
+        LO = L.NemitLevelsOut()
+        for k, t in out.items():
+            setattr(LO, k, t.data_ptr())
+        return out, LO
+
+    # -- the three modes -------------------------------------------------------------------
+    def render(self, o3n: torch.Tensor, v3n: torch.Tensor, near=0.0, camera_idx: int = 0, jitter=None,
+               return_aux: bool = False):
+        """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> rgb (N,3)."""
+        n = o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        rgb = torch.empty(n, 3, device=self.device, dtype=torch.float32)
+        ws = self._workspace(n)
+        if not return_aux:
+            L.check(self.lib.nemit_forward(self._h, C.byref(R), _ptr(rgb), None, None, _ptr(ws), ws.numel(),
+                                           self._stream()), "nemit_forward")
+            return rgb
+        acc = torch.empty(n, device=self.device, dtype=torch.float32)
+        aux, LO = self._levels_out(n, True)
+        L.check(self.lib.nemit_forward(self._h, C.byref(R), _ptr(rgb), _ptr(acc), C.byref(LO), _ptr(ws), ws.numel(),
+                                       self._stream()), "nemit_forward")
+        aux["rgb"] = rgb
+        aux["accumulation"] = acc
+        return rgb, aux
+
+    def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None):
+        """ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) for emitter rays."""
+        n = o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        aux, LO = self._levels_out(n, False)
+        ws = self._workspace(n)
+        L.check(self.lib.nemit_sample_levels(self._h, C.byref(R), C.byref(LO), _ptr(ws), ws.numel(), self._stream()),
+                "nemit_sample_levels")
+        return aux
+
+    def jvp(self, o3n, v3n, do3n, dv3n, near=0.0, camera_idx: int = 0, jitter=None):
+        """NeRFEmitterOp.ns_forward_ray (nerf_emitter_op.py:60-90): tangents (3,N) -> d_rgb (N,3)."""
+        n = o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        _check(do3n, (3, n), "d_o")
+        _check(dv3n, (3, n), "d_v")
+        out = torch.empty(n, 3, device=self.device, dtype=torch.float32)
+        ws = self._workspace(n)
+        L.check(self.lib.nemit_jvp(self._h, C.byref(R), _ptr(do3n), _ptr(dv3n), _ptr(out), _ptr(ws), ws.numel(),
+                                   self._stream()), "nemit_jvp")
+        return out
+
+    def backward(self, o3n, v3n, grad_rgb, near=0.0, camera_idx: int = 0, jitter=None,
+                 chunk_rays: Optional[int] = None, loss_scale: float = 1.0, proposal_requires_grad: bool = True):
+        """NeRFEmitterOp.ns_backward_ray (nerf_emitter_op.py:92-117): returns (grad_o, grad_v) as (3,N);
+        parameter gradients are accumulated into the bound ``grads``."""
+        if not self.grads:
+            self.bind_grads()
+        n = o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        _check(grad_rgb, (n, 3), "grad_rgb")
+        go = torch.empty(3, n, device=self.device, dtype=torch.float32)
+        gv = torch.empty(3, n, device=self.device, dtype=torch.float32)
+        ws = self._workspace(n)
+        L.check(self.lib.nemit_backward(self._h, C.byref(R), _ptr(grad_rgb), int(chunk_rays or n), float(loss_scale),
+                                        int(proposal_requires_grad), _ptr(go), _ptr(gv), _ptr(ws), ws.numel(),
+                                        self._stream()), "nemit_backward")
+        return go, gv
+
+    def render_host(self, o_host: torch.Tensor, v_host: torch.Tensor, rgb_host: torch.Tensor, near: float = 0.0,
+                    camera_idx: int = 0):
+        """End-to-end call with pinned HOST buffers (nemit_forward_host): H2D, forward, D2H on the stream."""
+        n = o_host.shape[1]
+        for t, nm in [(o_host, "o_host"), (v_host, "v_host"), (rgb_host, "rgb_host")]:
+            if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("%s must be a contiguous fp32 host tensor" % nm)
+        R = L.NemitRays()
+        R.o, R.v, R.n = o_host.data_ptr(), v_host.data_ptr(), n
+        R.near_per_ray, R.near_scalar, R.camera_idx, R.training = None, float(near), int(camera_idx), int(self.training)
+        R.jitter, R.anneal = None, float(self.anneal)
+        ws = self._workspace(n)
+        L.check(self.lib.nemit_forward_host(self._h, C.byref(R), C.c_void_p(rgb_host.data_ptr()), _ptr(ws), ws.numel(),
+                                            self._stream()), "nemit_forward_host")
+        return rgb_host
+
+    def hash_encode(self, x: torch.Tensor, which: int = 0) -> torch.Tensor:
+        """HashEncoding.forward (NS/field_components/encodings.py:341-382) on (n,3) points in [0,1]."""
+        n = x.shape[0]
+        _check(x, (n, 3), "x")
+        g = self.spec.main_grid if which == 0 else self.spec.prop_grids[which - 1]
+        out = torch.empty(n, g.num_levels * g.features_per_level, device=self.device, dtype=torch.float32)
+        L.check(self.lib.nemit_hash_encode(self._h, which, _ptr(x), n, _ptr(out), self._stream()), "nemit_hash_encode")
+        return out
+
+    def launch_count(self) -> int:
+        return int(self.lib.nemit_launch_count(self._h))

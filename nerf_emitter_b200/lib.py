@@ -1,0 +1,116 @@
+"""ctypes binding of libnerfemitter.so (include/nemit.h).  Fails loudly when the library is missing:
+there is no CPU or torch fallback for the emitter path."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libnerfemitter.so")
+MAX_LEVELS = 16
+
+c_float_p = C.POINTER(C.c_float)
+c_int32_p = C.POINTER(C.c_int32)
+
+
+class NemitGrid(C.Structure):
+    _fields_ = [("num_levels", C.c_int32), ("log2_table_size", C.c_int32), ("scalings", C.c_float * MAX_LEVELS)]
+
+
+class NemitConfig(C.Structure):
+    _fields_ = [
+        ("main_grid", NemitGrid), ("prop_grid", NemitGrid * 2),
+        ("num_prop_samples", C.c_int32 * 2), ("num_nerf_samples", C.c_int32),
+        ("hidden_dim", C.c_int32), ("geo_feat_dim", C.c_int32), ("appearance_dim", C.c_int32),
+        ("prop_hidden_dim", C.c_int32), ("num_images", C.c_int32),
+        ("near_plane", C.c_float), ("far_plane", C.c_float), ("scene_scale", C.c_float),
+        ("aabb", C.c_float * 6), ("rgb_bias", C.c_float),
+        ("disable_inside_aabb", C.c_int32), ("cpu_sum_width", C.c_int32),
+        ("interlevel_mult", C.c_float), ("distortion_mult", C.c_float),
+        ("lin0_host", c_float_p), ("u1_host", c_float_p), ("u2_host", c_float_p),
+    ]
+
+
+PARAM_FIELDS = [
+    "main_table", "base_w0", "base_b0", "base_w1", "base_b1", "head_w0", "head_b0", "head_w1", "head_b1",
+    "head_w2", "head_b2", "appearance",
+]
+
+
+class NemitParams(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in PARAM_FIELDS] + [
+        ("prop_table", C.c_void_p * 2), ("prop_w0", C.c_void_p * 2), ("prop_b0", C.c_void_p * 2),
+        ("prop_w1", C.c_void_p * 2), ("prop_b1", C.c_void_p * 2)]
+
+
+class NemitRays(C.Structure):
+    _fields_ = [("o", C.c_void_p), ("v", C.c_void_p), ("near_per_ray", C.c_void_p), ("near_scalar", C.c_float),
+                ("n", C.c_int64), ("camera_idx", C.c_int32), ("training", C.c_int32), ("jitter", C.c_void_p),
+                ("anneal", C.c_float)]
+
+
+class NemitLevelsOut(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in
+                ["weights0", "weights1", "s_edges1", "s_edges2", "t_edges2", "inds1", "inds2", "weights2"]]
+
+
+class NemitVmfLobes(C.Structure):
+    _fields_ = [("position", C.c_void_p), ("weight", C.c_void_p), ("std", C.c_void_p), ("num_lobes", C.c_int32)]
+
+
+# every symbol include/nemit.h declares: (restype, argtypes)
+_H = C.c_void_p
+SYMBOLS = {
+    "nemit_last_error": (C.c_char_p, []),
+    "nemit_version": (C.c_int, []),
+    "nemit_create": (C.c_int, [C.POINTER(NemitConfig), C.c_int, C.POINTER(_H)]),
+    "nemit_destroy": (C.c_int, [_H]),
+    "nemit_bind_params": (C.c_int, [_H, C.POINTER(NemitParams)]),
+    "nemit_bind_grads": (C.c_int, [_H, C.POINTER(NemitParams)]),
+    "nemit_workspace_bytes": (C.c_size_t, [_H, C.c_int64]),
+    "nemit_forward": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.POINTER(NemitLevelsOut),
+                                C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_sample_levels": (C.c_int, [_H, C.POINTER(NemitRays), C.POINTER(NemitLevelsOut), C.c_void_p, C.c_size_t,
+                                      C.c_void_p]),
+    "nemit_jvp": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                            C.c_void_p]),
+    "nemit_backward": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_void_p,
+                                 C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_hash_encode": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "nemit_vmf_sample": (C.c_int, [C.POINTER(NemitVmfLobes), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]),
+    "nemit_vmf_pdf": (C.c_int, [C.POINTER(NemitVmfLobes), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                C.c_void_p]),
+    "nemit_forward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_launch_count": (C.c_int64, [_H]),
+}
+
+_LIB = None
+
+
+class NemitError(RuntimeError):
+    pass
+
+
+def load():
+    """Loads the shared library (once). Raises if it has not been built: no fallback exists."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise NemitError(
+            "libnerfemitter.so is not built (%s). Run `python -c 'import __graft_entry__ as g; g.build()'` "
+            "or `make -C nerf_emitter_b200/csrc`. There is no CPU/torch fallback for this path." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the export is missing
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().nemit_last_error()
+        raise NemitError("%s failed (%d): %s" % (what, rc, msg.decode() if msg else "?"))
