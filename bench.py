@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py - emitter rays/sec on N B200s (driver contract; see DESIGN.md "Measurement").
+
+A step = one pass of the emitter hot path over one batch of synthetic rays resident in HBM:
+`nemit_forward` (+ `nemit_backward` once built) on `--rays` rays per GPU (default 2^20, BASELINE config 2
+shape: 1 M rays, random-init weights, deterministic unjittered rays).  Rays shard over ranks with replicated
+weights (weak scaling); no data-path collective in the forward, one gradient all-reduce in the backward.
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+ALG_BYTES_SAMPLING = (256 * 5 + 96 * 5) * 8 * 8      # prop gathers per ray: 112 640 B
+ALG_BYTES_FIELD = 48 * 16 * 8 * 8                    # main-grid gathers per ray: 49 152 B
+RAY_IO_BYTES = 24 + 12
+
+
+def make_rays(n, seed, device):
+    g = torch.Generator().manual_seed(seed)
+    o = torch.rand(3, n, generator=g)
+    v = torch.randn(3, n, generator=g)
+    v = v / v.norm(dim=0, keepdim=True)
+    return o.to(device), v.to(device)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.samples.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for s in self.samples:
+            try:
+                sm.append(float(s[1]))
+                mx.append(float(s[2]))
+            except Exception:
+                continue
+            for name, val in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], s[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def cpu_reference_rate(n_rays, repeats, mode="fwd"):
+    """The reference's torch-CPU algorithm (oracle port) on the host cores: rays/s on a bounded sample."""
+    from nerf_emitter_b200 import EmitterModelSpec, make_params
+    from oracle.nerfacto_oracle import OracleEmitter
+    torch.set_num_threads(os.cpu_count() or 1)
+    spec = EmitterModelSpec()
+    P = make_params(spec, seed=0, table_scale=1e3)
+    O = OracleEmitter(P, spec)
+    o, v = make_rays(n_rays, 1, "cpu")
+    g = torch.randn(n_rays, 3)
+
+    def one():
+        O.train(False)
+        O.render(o, v)
+        if mode == "fwd+bwd":
+            O.train(True)
+            O.vjp(o, v, g)
+    one()
+    best = 1e30
+    for _ in range(repeats):
+        t = time.perf_counter()
+        one()
+        best = min(best, time.perf_counter() - t)
+    return n_rays / best, best
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    n = args.ref_rays
+    times = []
+    from nerf_emitter_b200 import EmitterModelSpec, make_params
+    from oracle.nerfacto_oracle import OracleEmitter
+    torch.set_num_threads(os.cpu_count() or 1)
+    spec = EmitterModelSpec()
+    O = OracleEmitter(make_params(spec, seed=0, table_scale=1e3), spec)
+    o, v = make_rays(n, 1, "cpu")
+    g = torch.randn(n, 3)
+
+    def step():
+        O.train(False)
+        O.render(o, v)
+        if args.mode == "fwd+bwd":
+            O.train(True)
+            O.vjp(o, v, g)
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = n / dt
+    line = {"impl": "reference", "metric": METRIC[args.mode], "value": val, "unit": "rays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, n),
+            "cpu_baseline": {"value": val, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": "%d rays per step of the same workload (oracle/nerfacto_oracle.py, torch CPU fp32)" % n},
+            "e2e": {"value": val, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+METRIC = {"fwd": "NeRF-emitter rays/sec fwd (nerfacto 256/96/48 samples)",
+          "fwd+bwd": "NeRF-emitter rays/sec fwd+bwd (nerfacto 256/96/48 samples)"}
+
+
+def workload_config(args, rays_per_gpu):
+    return {"workload": "nerfacto emitter query, %d deterministic rays per GPU, 256/96/48 samples, random-init stress "
+                        "weights (hash tables U(-1,1)), eval-mode forward%s" % (
+                            rays_per_gpu, " + training-mode backward (param + ray grads, interlevel+distortion)"
+                            if args.mode == "fwd+bwd" else ""),
+            "mode": args.mode, "rays_per_gpu": rays_per_gpu, "mlp_precision": args.precision,
+            "l2_policy": "inputs+tables (%.0f MiB/step touched) exceed L2; no explicit flush" % (
+                (rays_per_gpu * (36 + 49 * 4 * 2) + 74 * 2 ** 20) / 2 ** 20),
+            "parallelism": "ray-sharded x%d, weights replicated" % args.gpus}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU per step")
+    ap.add_argument("--ref-rays", type=int, default=4096, help="rays per step of the CPU reference arm")
+    ap.add_argument("--mode", default=None, choices=["fwd", "fwd+bwd"])
+    ap.add_argument("--precision", default="fp32")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    from nerf_emitter_b200 import lib as L
+    if args.mode is None:
+        args.mode = "fwd+bwd" if backward_available() else "fwd"
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    from nerf_emitter_b200 import EmitterModelSpec, NerfEmitter, make_params
+    spec = EmitterModelSpec()
+    P = make_params(spec, seed=0, table_scale=1e3)
+    E = NerfEmitter(P, spec, device=dev)
+    n = args.rays
+    o, v = make_rays(n, 1 + rank, dev)
+    gout = torch.randn(n, 3, device=dev)
+    if args.mode == "fwd+bwd":
+        E.bind_grads()
+        flat_grads = None
+
+    def step():
+        E.train(False)
+        rgb = E.render(o, v)
+        if args.mode == "fwd+bwd":
+            E.train(True)
+            E.backward(o, v, gout, chunk_rays=16384)
+            if world > 1:
+                for gname in E.grads:
+                    dist.all_reduce(E.grads[gname])
+        return rgb
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    launches0 = E.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    barrier()
+    ev[0].record()
+    for _ in range(args.steps):
+        step()
+    ev[1].record()
+    barrier()
+    ms = ev[0].elapsed_time(ev[1])
+    launches = E.launch_count() - launches0
+    clk = clocks.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = n * world / (ms_per_step * 1e-3)
+
+    # per-kernel timing for the roofline (forward kernels timed alone on this stream, same inputs)
+    roof = kernel_roofline(E, o, v, n)
+
+    # e2e: pinned host rays in, host radiance out, through nemit_forward_host
+    oh = o.cpu().pin_memory()
+    vh = v.cpu().pin_memory()
+    rh = torch.empty(n, 3).pin_memory()
+    E.train(False)
+    for _ in range(2):
+        E.render_host(oh, vh, rh)
+    barrier()
+    ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev2[0].record()
+    e2e_steps = max(3, args.steps // 2)
+    for _ in range(e2e_steps):
+        E.render_host(oh, vh, rh)
+    ev2[1].record()
+    barrier()
+    t2 = torch.tensor([ev2[0].elapsed_time(ev2[1])], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+    e2e_val = n * world / (float(t2.item()) / e2e_steps * 1e-3)
+
+    if rank == 0:
+        line = {"metric": METRIC[args.mode], "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
+                "clocks": clk, "gpu_launches": int(launches),
+                "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 12 * n,
+                        "note": "forward only through nemit_forward_host (pinned host rays in, host radiance out)"},
+                "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            rate, best = cpu_reference_rate(args.ref_rays, 3, args.mode)
+            line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+                                    "sample": "%d rays of the same workload, best of 3 (%.2f s each), oracle/nerfacto_oracle.py "
+                                              "torch CPU fp32" % (args.ref_rays, best)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def backward_available():
+    try:
+        src = open(os.path.join(ROOT, "nerf_emitter_b200", "csrc", "backward.cu")).read()
+        return "k_field_backward" in src
+    except OSError:
+        return False
+
+
+def kernel_roofline(E, o, v, n):
+    """Times the two forward kernels separately (sample_levels alone; forward = both) with CUDA events."""
+    hbm, src = measured_peaks()
+    E.train(False)
+
+    def timed(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+    t_s = timed(lambda: E.sample_levels(o, v, edges_only=True))
+    t_f = timed(lambda: E.render(o, v))
+    t_field = max(t_f - t_s, 1e-6)
+    launches_per_call = max(1, (n + (1 << 18) - 1) >> 18)
+    dom, t_dom, alg = ("k_sample_levels", t_s, ALG_BYTES_SAMPLING) if t_s >= t_field else ("k_field_forward", t_field, ALG_BYTES_FIELD)
+    achieved = alg * n / (t_dom * 1e-3) / 1e9
+    return {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "peak_source": src, "unit": "GB/s",
+            "frac": achieved / hbm, "traffic": None,
+            "algorithmic_bytes_per_ray": alg, "launches_per_step": launches_per_call,
+            "ms_k_sample_levels": t_s, "ms_k_field_forward": t_field,
+            "note": "achieved = algorithmic 8-byte-gather bytes of the dominant kernel / its CUDA-event time; "
+                    "tables (74 MiB) are L2-resident so DRAM traffic is far below this"}
+
+
+if __name__ == "__main__":
+    main()

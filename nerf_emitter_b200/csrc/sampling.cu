@@ -22,40 +22,38 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
   __syncthreads();
   WarpScratch* sc = &sm->warp[wid];
 
+#pragma unroll 1
   for (int64_t r = (int64_t)blockIdx.x * kWarpsPerCta + wid; r < A.n; r += (int64_t)gridDim.x * kWarpsPerCta) {
     RayCtx R;
     load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r, M.scene_scale, R.o, R.d);
     const float near = A.training ? M.near_plane : 0.f;      // NearFarCollider, scene_colliders.py:217-222
-    R.s_near = spacing_fwd(mul_rn(1.f, near));
-    R.s_far = spacing_fwd(mul_rn(1.f, M.far_plane));
+    R.s_near = spacing_fwd(near);
+    R.s_far = spacing_fwd(M.far_plane);
     const float* jit = A.jitter ? A.jitter + (A.ray_offset + r) * 3 : nullptr;
-    const float j0 = jit ? jit[0] : -1.f, j1 = jit ? jit[1] : -1.f, j2 = jit ? jit[2] : -1.f;
+    initial_edges(sc, A.lin0, jit ? jit[0] : -1.f, lane);
 
-    // ---- level 0: 256 piecewise-spaced bins ------------------------------------------------
-    initial_edges(sc, A.lin0, j0, lane);
-    float w0[kS0 / 32];
-    proposal_level_weights<kS0>(sc, R, A.prop_table[0], M.prop_grid[0], &sm->mlp[0], M, lane, w0);
-    if (A.weights0) {
-#pragma unroll
-      for (int k = 0; k < kS0 / 32; ++k) A.weights0[r * kS0 + k * 32 + lane] = w0[k];
+    // levels 0 and 1 run through ONE copy of the code (instruction-cache footprint, see sampling.cuh)
+#pragma unroll 1
+    for (int lvl = 0; lvl < 2; ++lvl) {
+      const int S = lvl == 0 ? kS0 : kS1;          // bins at this level
+      const int Mn = lvl == 0 ? kS1 : kS2;         // samples of the next level
+      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane);
+      float* w_out = lvl == 0 ? A.weights0 : A.weights1;
+      if (w_out) {
+        for (int i = lane; i < S; i += 32) w_out[r * S + i] = sc->buf[i];
+      }
+      int32_t* inds = lvl == 0 ? A.inds1 : A.inds2;
+      pdf_resample_warp(sc, S, Mn, lvl == 0 ? A.u1 : A.u2, jit ? jit[lvl + 1] : -1.f, A.anneal, M.cpu_sum_width,
+                        lane, inds ? inds + r * (Mn + 1) : nullptr);
+      if (lvl == 0) {
+        for (int i = lane; i <= kS1; i += 32) {
+          float e = sc->s_new[i];
+          sc->s_edge[i] = e;
+          if (A.s_edges1) A.s_edges1[r * (kS1 + 1) + i] = e;
+        }
+        __syncwarp();
+      }
     }
-    pdf_resample_warp<kS0>(sc, w0, kS1, A.u1, j1, A.anneal, M.cpu_sum_width, lane,
-                           A.inds1 ? A.inds1 + r * (kS1 + 1) : nullptr);
-    // ---- level 1: 96 bins ------------------------------------------------------------------
-    for (int i = lane; i <= kS1; i += 32) {
-      float e = sc->s_new[i];
-      sc->s_edge[i] = e;
-      if (A.s_edges1) A.s_edges1[r * (kS1 + 1) + i] = e;
-    }
-    __syncwarp();
-    float w1[kS1 / 32];
-    proposal_level_weights<kS1>(sc, R, A.prop_table[1], M.prop_grid[1], &sm->mlp[1], M, lane, w1);
-    if (A.weights1) {
-#pragma unroll
-      for (int k = 0; k < kS1 / 32; ++k) A.weights1[r * kS1 + k * 32 + lane] = w1[k];
-    }
-    pdf_resample_warp<kS1>(sc, w1, kS2, A.u2, j2, A.anneal, M.cpu_sum_width, lane,
-                           A.inds2 ? A.inds2 + r * (kS2 + 1) : nullptr);
     // ---- level 2 edges ---------------------------------------------------------------------
     for (int i = lane; i <= kS2; i += 32) {
       float s = sc->s_new[i];

@@ -3,6 +3,11 @@
 // neighbouring lanes look up neighbouring points of the same ray (same / adjacent hash cells on the
 // coarse levels -> the 8-byte gathers of a warp coalesce into few 32-byte sectors).
 //
+// Code-size note (ncu, round 1): the first version unrolled the 8 samples per lane and instantiated
+// the level twice; 18 k SASS instructions, 91 % of warp stalls were instruction-cache misses
+// (stall_no_inst).  The loops over samples are therefore NOT unrolled and both levels run through one
+// copy of the code with per-level parameters; per-sample values live in the warp's shared scratch.
+//
 // Follows ProposalNetworkSampler.generate_ray_samples (NS/model_components/ray_samplers.py:584-626),
 // UniformLinDispPiecewiseSampler (:231-254, :82-134), PDFSampler (:282-380),
 // HashMLPDensityField.get_density (NS/fields/density_fields.py:95-122) and RaySamples.get_weights
@@ -33,7 +38,7 @@ __device__ __forceinline__ void load_prop_mlp(PropMlpSmem* dst, const float* __r
   if (tid == 0) dst->b1 = b1[0];
 }
 
-// hash-encode one point on a 5-level proposal grid
+// hash-encode one point on a 5-level proposal grid: all 40 gathers are issued before the first blend
 __device__ __forceinline__ void prop_encode(const float p[3], const float2* __restrict__ table, const GridDev& G,
                                             float enc[kPropEnc]) {
   LevelCell cell[kPropLevels];
@@ -52,10 +57,10 @@ __device__ __forceinline__ void prop_encode(const float p[3], const float2* __re
   }
 }
 
-// raw (pre-activation) density of the proposal MLP; optionally returns the hidden pre-activations
+// raw (pre-activation) density of the proposal MLP
 __device__ __forceinline__ float prop_mlp_raw(const float enc[kPropEnc], const PropMlpSmem* W) {
   float raw = W->b1;
-#pragma unroll
+#pragma unroll 4
   for (int j = 0; j < kPropHidden; ++j) {
     const float4* r4 = reinterpret_cast<const float4*>(W->row[j]);
     float4 a = r4[0], b = r4[1], c = r4[2];
@@ -69,9 +74,9 @@ __device__ __forceinline__ float prop_mlp_raw(const float enc[kPropEnc], const P
 }
 
 // density at a sample position (NeRF coordinates): contraction -> hash -> MLP -> trunc_exp * selector
-__device__ __forceinline__ float prop_density(const float x[3], const float2* __restrict__ table, const GridDev& G,
-                                              const PropMlpSmem* W, const ModelDev& M) {
-  float p[3];
+__device__ __noinline__ float prop_density(float x0, float x1, float x2, const float2* __restrict__ table,
+                                           const GridDev& G, const PropMlpSmem* W, const ModelDev& M) {
+  float x[3] = {x0, x1, x2}, p[3];
   if (!contract_normalise(x, M, p)) return 0.f;   // reference evaluates at p=0 and multiplies by 0
   float enc[kPropEnc];
   prop_encode(p, table, G, enc);
@@ -81,7 +86,8 @@ __device__ __forceinline__ float prop_density(const float x[3], const float2* __
 // per-warp scratch of the proposal loop
 struct WarpScratch {
   float s_edge[kS0 + 4];   // spacing edges of the current level (S+1 used)
-  float buf[kS0 + 4];      // padded weights, then cdf (S+1 used)
+  float buf[kS0 + 4];      // delta*sigma -> weights -> padded weights
+  float cdf[kS0 + 4];      // S+1 used
   float s_new[kS1 + 4];    // edges produced by the PDF stage (M+1 used)
 };
 
@@ -101,65 +107,102 @@ __device__ __forceinline__ float row_sum_like_aten(const float* w, int n, int V,
   const int n_ilp = nv / 4;
   float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
   if (lane < V) {
+#pragma unroll 1
     for (int i = 0; i < n_ilp; ++i) {
       p0 = add_rn(p0, w[(i * 4 + 0) * V + lane]);
       p1 = add_rn(p1, w[(i * 4 + 1) * V + lane]);
       p2 = add_rn(p2, w[(i * 4 + 2) * V + lane]);
       p3 = add_rn(p3, w[(i * 4 + 3) * V + lane]);
     }
+#pragma unroll 1
     for (int i = n_ilp * 4; i < nv; ++i) p0 = add_rn(p0, w[i * V + lane]);
     p0 = add_rn(add_rn(add_rn(p0, p1), p2), p3);
   }
   float acc = 0.f;
+#pragma unroll 1
   for (int k = nv * V; k < n; ++k) acc = add_rn(acc, w[k]);   // scalar tail first
+#pragma unroll 1
   for (int l = 0; l < V; ++l) acc = add_rn(acc, __shfl_sync(0xffffffffu, p0, l));
   return acc;
 }
 
+struct RayCtx {
+  float o[3], d[3];
+  float s_near, s_far;
+};
+
+// One proposal level: density at the S bin midpoints -> weights (in sc->buf[0..S)).
+// Edges must be in sc->s_edge[0..S].  S is a multiple of 32.
+__device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const RayCtx& R, int S,
+                                                       const float2* __restrict__ table, const GridDev& G,
+                                                       const PropMlpSmem* W, const ModelDev& M, int lane) {
+#pragma unroll 1
+  for (int i = lane; i < S; i += 32) {
+    float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far);
+    float t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
+    float tsum = add_rn(t0, t1);
+    float sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
+                               sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
+    sc->buf[i] = mul_rn(sub_rn(t1, t0), sigma);
+  }
+  __syncwarp();
+  // exclusive prefix accumulated in float64 and rounded to float32 per prefix (ATen's CPU cumsum)
+  double carry = 0.0;
+#pragma unroll 1
+  for (int i = lane; i < S; i += 32) {
+    float ds = sc->buf[i];
+    double inc = warp_incl_scan((double)ds, lane);
+    double exc = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) exc = 0.0;
+    float prefix = (float)(carry + exc);
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+    float alpha = sub_rn(1.f, expf(-ds));
+    sc->buf[i] = nan_to_num(mul_rn(alpha, expf(-prefix)));
+  }
+  __syncwarp();
+}
+
 // PDFSampler.generate_ray_samples for one ray: S existing bins (edges in sc->s_edge, weights in
-// registers), M new samples -> M+1 new edges into sc->s_new.  u_base = linspace(0,1-1/nb,nb) from the
+// sc->buf), M new samples -> M+1 new edges into sc->s_new.  u_base = linspace(0,1-1/nb,nb) from the
 // host.  jit < 0 means deterministic.  inds_out (M+1) optional.
-template <int S>
-__device__ __forceinline__ void pdf_resample_warp(WarpScratch* sc, const float (&w)[S / 32], int M,
-                                                  const float* __restrict__ u_base, float jit, float anneal,
-                                                  int sum_width, int lane, int32_t* inds_out) {
-  constexpr int K = S / 32;
+__device__ __forceinline__ void pdf_resample_warp(WarpScratch* sc, int S, int M, const float* __restrict__ u_base,
+                                                  float jit, float anneal, int sum_width, int lane,
+                                                  int32_t* inds_out) {
   const int nb = M + 1;
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    float x = w[k];
+#pragma unroll 1
+  for (int i = lane; i < S; i += 32) {
+    float x = sc->buf[i];
     if (anneal != 1.f) x = powf(x, anneal);
-    sc->buf[k * 32 + lane] = add_rn(x, 0.01f);
+    sc->buf[i] = add_rn(x, 0.01f);
   }
   __syncwarp();
   float tot = row_sum_like_aten(sc->buf, S, sum_width, lane);
-  float fill = fmaxf(sub_rn(1e-5f, tot), 0.f);
-  float fill_each = div_rn(fill, (float)S);
+  const float fill = fmaxf(sub_rn(1e-5f, tot), 0.f);
+  const float fill_each = div_rn(fill, (float)S);
   tot = add_rn(tot, fill);
-  float pdf[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) pdf[k] = div_rn(add_rn(sc->buf[k * 32 + lane], fill_each), tot);
-  __syncwarp();
+  // cdf = [0, min(1, cumsum(pdf))]: float64 accumulate, each prefix rounded to float32
   double carry = 0.0;
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    double inc = warp_incl_scan((double)pdf[k], lane);
-    sc->buf[k * 32 + lane + 1] = fminf(1.f, (float)(carry + inc));
+#pragma unroll 1
+  for (int i = lane; i < S; i += 32) {
+    float pdf = div_rn(add_rn(sc->buf[i], fill_each), tot);
+    double inc = warp_incl_scan((double)pdf, lane);
+    sc->cdf[i + 1] = fminf(1.f, (float)(carry + inc));
     carry += __shfl_sync(0xffffffffu, inc, 31);
   }
-  if (lane == 0) sc->buf[0] = 0.f;
+  if (lane == 0) sc->cdf[0] = 0.f;
   __syncwarp();
   const float half_step = (float)(1.0 / (2.0 * (double)nb));
+#pragma unroll 1
   for (int k = lane; k <= M; k += 32) {
     float u = (jit >= 0.f) ? add_rn(u_base[k], div_rn(jit, (float)nb)) : add_rn(u_base[k], half_step);
     int lo = 0, hi = S + 1;          // searchsorted(cdf, u, side="right") over S+1 entries
     while (lo < hi) {
       int mid = (lo + hi) >> 1;
-      if (sc->buf[mid] <= u) lo = mid + 1; else hi = mid;
+      if (sc->cdf[mid] <= u) lo = mid + 1; else hi = mid;
     }
     if (inds_out) inds_out[k] = lo;
     int i0 = min(max(lo - 1, 0), S), i1 = min(max(lo, 0), S);
-    float c0 = sc->buf[i0], c1 = sc->buf[i1];
+    float c0 = sc->cdf[i0], c1 = sc->cdf[i1];
     float e0 = sc->s_edge[i0], e1 = sc->s_edge[i1];
     float t = div_rn(sub_rn(u, c0), sub_rn(c1, c0));
     t = isnan(t) ? 0.f : t;                        // nan_to_num(.., 0) then clip
@@ -169,36 +212,10 @@ __device__ __forceinline__ void pdf_resample_warp(WarpScratch* sc, const float (
   __syncwarp();
 }
 
-struct RayCtx {
-  float o[3], d[3];
-  float s_near, s_far;
-};
-
-// One proposal level: density at the S bin midpoints, weights. Edges must be in sc->s_edge[0..S].
-template <int S>
-__device__ __forceinline__ void proposal_level_weights(const WarpScratch* sc, const RayCtx& R,
-                                                       const float2* __restrict__ table, const GridDev& G,
-                                                       const PropMlpSmem* W, const ModelDev& M, int lane,
-                                                       float (&w)[S / 32]) {
-  constexpr int K = S / 32;
-  float ds[K];
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    int i = k * 32 + lane;
-    float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far);
-    float t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
-    float tsum = add_rn(t0, t1);
-    float x[3] = {sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
-                  sample_pos(R.o[2], R.d[2], tsum)};
-    float sigma = prop_density(x, table, G, W, M);
-    ds[k] = mul_rn(sub_rn(t1, t0), sigma);
-  }
-  weights_from_ds<K>(ds, w, lane);
-}
-
 // initial edges (ray_samplers.py:104-117): lin0 = linspace(0,1,S0+1) from the host; with jitter the
 // edges move inside [midpoint below, midpoint above].
 __device__ __forceinline__ void initial_edges(WarpScratch* sc, const float* __restrict__ lin0, float jit, int lane) {
+#pragma unroll 1
   for (int i = lane; i <= kS0; i += 32) {
     float e = lin0[i];
     if (jit >= 0.f) {

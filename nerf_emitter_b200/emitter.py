@@ -216,11 +216,17 @@ class NerfEmitter:
         aux["accumulation"] = acc
         return rgb, aux
 
-    def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None):
-        """ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) for emitter rays."""
+    def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None, edges_only: bool = False):
+        """ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) for emitter rays.
+        edges_only: write just the final 49 euclidean edges (what the field kernel consumes)."""
         n = o3n.shape[1]
         R = self._rays(o3n, v3n, near, camera_idx, jitter)
-        aux, LO = self._levels_out(n, False)
+        if edges_only:
+            aux = dict(t_edges2=torch.empty(n, self.spec.num_nerf_samples + 1, device=self.device))
+            LO = L.NemitLevelsOut()
+            LO.t_edges2 = aux["t_edges2"].data_ptr()
+        else:
+            aux, LO = self._levels_out(n, False)
         ws = self._workspace(n)
         L.check(self.lib.nemit_sample_levels(self._h, C.byref(R), C.byref(LO), _ptr(ws), ws.numel(), self._stream()),
                 "nemit_sample_levels")

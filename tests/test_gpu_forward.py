@@ -23,10 +23,30 @@ def emitters(spec, params_factory):
     return get
 
 
-def _near_tie_mismatches(inds_gpu, inds_ref, cdf_ref, nb, jitter=None):
-    """Every index mismatch must be a near-tie |u - cdf[idx]| <= 4 ulp-ish of the cdf."""
-    bad = (inds_gpu != inds_ref)
-    return int(bad.sum())
+def _check_indices(tag, inds_gpu, inds_ref, cdf_ref, jitter_col=None, tie_tol=2e-6):
+    """searchsorted indices must equal the reference's EXCEPT at ties: the deterministic sampler puts
+    u_k = (2k+1)/(2 nb) exactly on cdf entries whenever the weights sum to ~1 and leading bins are empty
+    (cdf_i = i*0.01/1.96 = i/196 while u_k = (4k+2)/196), so the reference's own index there is decided by
+    the last bit of sum(w).  A mismatch is accepted only if it is off by one AND the cdf entry that
+    decides it is within tie_tol of u; the count is printed."""
+    a = np.asarray(inds_gpu).astype(np.int64)
+    b = np.asarray(inds_ref).astype(np.int64)
+    cdf = np.asarray(cdf_ref)
+    nb = a.shape[1]
+    u = np.linspace(0.0, 1.0 - 1.0 / nb, nb, dtype=np.float32)[None, :].repeat(a.shape[0], 0)
+    if jitter_col is None:
+        u = u + np.float32(1.0 / (2 * nb))
+    else:
+        u = u + (np.asarray(jitter_col, dtype=np.float32).reshape(-1, 1) / np.float32(nb))
+    bad = a != b
+    n_bad = int(bad.sum())
+    print("%s: %d / %d index mismatches (all must be ties)" % (tag, n_bad, a.size))
+    if n_bad:
+        assert np.abs(a - b)[bad].max() == 1, tag
+        r, k = np.nonzero(bad)
+        boundary = cdf[r, np.minimum(a, b)[r, k]]
+        assert np.abs(boundary - u[r, k]).max() <= tie_tol, (tag, float(np.abs(boundary - u[r, k]).max()))
+    return n_bad
 
 
 @pytest.mark.parametrize("case", GOLDEN_CASES)
@@ -38,10 +58,9 @@ def test_forward_matches_reference_golden(case, spec, emitters):
     rgb, aux = E.render(I["o"].cuda(), I["v"].cuda(), near=I["near"], camera_idx=I["camera_idx"],
                         jitter=I["jitter"], return_aux=True)
     torch.cuda.synchronize()
-    m1 = int((aux["inds1"].cpu().numpy() != G["inds1"]).sum())
-    m2 = int((aux["inds2"].cpu().numpy() != G["inds2"]).sum())
-    print("%s: index mismatches stage1 %d/%d stage2 %d/%d" % (case, m1, G["inds1"].size, m2, G["inds2"].size))
-    assert m1 <= max(1, G["inds1"].size // 2000) and m2 <= max(1, G["inds2"].size // 2000)
+    jit = G["jitter"] if I["training"] else None
+    _check_indices(case + " stage1", aux["inds1"].cpu().numpy(), G["inds1"], G["cdf1"], None if jit is None else jit[:, 1])
+    _check_indices(case + " stage2", aux["inds2"].cpu().numpy(), G["inds2"], G["cdf2"], None if jit is None else jit[:, 2])
     for k, gk in [("weights0", "weights0"), ("weights1", "weights1"), ("weights2", "weights2"),
                   ("s_edges1", "sdist1"), ("s_edges2", "sdist2"), ("rgb", "rgb"), ("accumulation", "accumulation")]:
         ref = G[gk].reshape(aux[k].shape)
@@ -64,10 +83,10 @@ def test_forward_matches_oracle_4096(training, spec, params_factory, emitters):
     rgb_ref, a = O.render(o, v, near=near[:, None], camera_idx=3, jitter=jit, return_aux=True)
     rgb, b = E.render(o.cuda(), v.cuda(), near=near.cuda(), camera_idx=3, jitter=jit, return_aux=True)
     torch.cuda.synchronize()
-    m1 = int((b["inds1"].cpu() != a["inds1"]).sum())
-    m2 = int((b["inds2"].cpu() != a["inds2"]).sum())
-    print("4096 rays training=%s: index mismatches %d/%d, %d/%d" % (training, m1, a["inds1"].numel(), m2, a["inds2"].numel()))
-    assert m1 <= a["inds1"].numel() // 2000 and m2 <= a["inds2"].numel() // 2000
+    _check_indices("4096 stage1", b["inds1"].cpu().numpy(), a["inds1"].numpy(), a["cdf1"].numpy(),
+                   None if jit is None else jit[1].numpy())
+    _check_indices("4096 stage2", b["inds2"].cpu().numpy(), a["inds2"].numpy(), a["cdf2"].numpy(),
+                   None if jit is None else jit[2].numpy())
     for k, rk in [("weights0", "weights0"), ("weights1", "weights1"), ("weights2", "weights2"),
                   ("s_edges1", "sdist1"), ("s_edges2", "sdist2"), ("rgb", "rgb")]:
         assert rel_err(b[k].cpu(), a[rk]) < TOL, (k, rel_err(b[k].cpu(), a[rk]))

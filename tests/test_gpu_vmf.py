@@ -26,7 +26,7 @@ def test_vmf_sample_and_pdf_match_oracle():
     ok = ~far
     assert float((pdf.cpu()[ok] - pdf_ref[ok]).abs().max() / pdf_ref[ok].abs().max()) < 1e-3
     pdf2 = V.pdf_direction(p.cuda(), d)
-    assert torch.allclose(pdf2, pdf, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(pdf2, pdf, rtol=1e-3, atol=1e-6)   # kappa up to ~1e3 amplifies the 1e-7 renormalisation of d
     pdf3 = V.pdf_direction(p.cuda(), (d_ref * 2.5).cuda())       # un-normalised input directions
     assert float((pdf3.cpu() - pdf_ref).abs().max() / pdf_ref.abs().max()) < 1e-3
 
