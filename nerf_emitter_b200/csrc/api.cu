@@ -143,7 +143,20 @@ static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
   size_t t_edges2, s_edges2, host_stage, bwd, total;
+  size_t g_sigma, g_rgbs, weights2, ray_grad;   // inside the backward block
 };
+static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
+  size_t off = base;
+  if (L) L->g_sigma = off;
+  off += align_up(sizeof(float) * (size_t)c * kS2);
+  if (L) L->g_rgbs = off;
+  off += align_up(sizeof(float) * (size_t)c * kS2 * 3);
+  if (L) L->weights2 = off;
+  off += align_up(sizeof(float) * (size_t)c * kS2);
+  if (L) L->ray_grad = off;
+  off += align_up(sizeof(float) * (size_t)c * 6);
+  return off - base;
+}
 static WsLayout ws_layout(int64_t n) {
   int64_t c = n < kChunkRays ? n : kChunkRays;
   if (c < 1) c = 1;
@@ -151,7 +164,7 @@ static WsLayout ws_layout(int64_t n) {
   size_t off = 0;
   L.t_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
   L.s_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
-  L.bwd = off;      off += align_up(backward_chunk_bytes(c));
+  L.bwd = off;      off += backward_chunk_bytes(c, &L, off);
   L.host_stage = off; off += align_up(sizeof(float) * (size_t)(n < 1 ? 1 : n) * 13);   // o,v (6) near (1) jitter (3) rgb (3)
   L.total = off;
   return L;
@@ -311,6 +324,119 @@ extern "C" int nemit_forward_host(NemitHandle* h, const NemitRays* rh, float* rg
   rc = nemit_forward(h, &rd, d_rgb, nullptr, nullptr, workspace, workspace_bytes, stream);
   if (rc) return rc;
   if ((e = cudaMemcpyAsync(rgb_host, d_rgb, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuda_fail(e, "D2H rgb");
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// forward-mode and reverse-mode entries
+// ---------------------------------------------------------------------------------------------
+extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o, const float* d_v, float* d_rgb,
+                         void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_rays(h, rays, "nemit_jvp");
+  if (rc) return rc;
+  if (rays->n == 0) return NEMIT_OK;
+  if (!d_o || !d_v || !d_rgb) return fail(NEMIT_E_INVALID, "nemit_jvp: null tangent pointers%s");
+  WsLayout L = ws_layout(rays->n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(NEMIT_E_WORKSPACE, "nemit_jvp: workspace too small%s (need %lld bytes)", "", (long long)L.total);
+  cudaSetDevice(h->device);
+  char* ws = static_cast<char*>(workspace);
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int64_t off = 0; off < rays->n; off += kChunkRays) {
+    int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
+    SampleArgs S;
+    fill_sample_args(h, S, rays, off, n);
+    S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
+    cudaError_t e = launch_sample_levels(h->M, S, st);
+    if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    h->launches++;
+    FieldArgs F;
+    memset(&F, 0, sizeof(F));
+    fill_ray_args(F, rays, off, n);
+    fill_field_params(h->P, F.P);
+    F.t_edges2 = S.t_edges2;
+    F.d_o = d_o; F.d_v = d_v;
+    F.d_rgb = d_rgb + off * 3;
+    e = launch_field_jvp(h->M, F, st);
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_jvp");
+    h->launches++;
+  }
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float* grad_rgb, int64_t chunk_rays,
+                              float loss_scale, int32_t proposal_requires_grad, float* grad_o, float* grad_v,
+                              void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_rays(h, rays, "nemit_backward");
+  if (rc) return rc;
+  if (!h->grads_bound) return fail(NEMIT_E_UNBOUND, "nemit_backward: gradient buffers not bound (nemit_bind_grads)%s");
+  if (rays->n == 0) return NEMIT_OK;
+  if (!grad_rgb || !grad_o || !grad_v) return fail(NEMIT_E_INVALID, "nemit_backward: null gradient pointers%s");
+  if (chunk_rays <= 0) chunk_rays = rays->n;
+  WsLayout L = ws_layout(rays->n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(NEMIT_E_WORKSPACE, "nemit_backward: workspace too small%s (need %lld bytes)", "", (long long)L.total);
+  cudaSetDevice(h->device);
+  char* ws = static_cast<char*>(workspace);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  for (int64_t off = 0; off < rays->n; off += kChunkRays) {
+    int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
+    float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
+    float* s_edges = reinterpret_cast<float*>(ws + L.s_edges2);
+    float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
+    float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
+    float* weights2 = reinterpret_cast<float*>(ws + L.weights2);
+    float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
+    SampleArgs S;
+    fill_sample_args(h, S, rays, off, n);
+    S.t_edges2 = t_edges;
+    S.s_edges2 = s_edges;
+    if ((e = launch_sample_levels(h->M, S, st)) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    h->launches++;
+    // pass 1: forward of the 48-sample stage + composite adjoint
+    FieldArgs F;
+    memset(&F, 0, sizeof(F));
+    fill_ray_args(F, rays, off, n);
+    fill_field_params(h->P, F.P);
+    F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
+    F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
+    if ((e = launch_field_adjoint_seed(h->M, F, st)) != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
+    h->launches++;
+    // pass 2: MLP / hash-grid backward
+    if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
+    FieldBwdArgs B;
+    memset(&B, 0, sizeof(B));
+    fill_ray_args(B, rays, off, n);
+    fill_field_params(h->P, B.P);
+    B.G.main_table = reinterpret_cast<float2*>(h->G.main_table);
+    B.G.base_w0 = h->G.base_w0; B.G.base_b0 = h->G.base_b0; B.G.base_w1 = h->G.base_w1; B.G.base_b1 = h->G.base_b1;
+    B.G.head_w0 = h->G.head_w0; B.G.head_b0 = h->G.head_b0; B.G.head_w1 = h->G.head_w1; B.G.head_b1 = h->G.head_b1;
+    B.G.head_w2 = h->G.head_w2; B.G.head_b2 = h->G.head_b2; B.G.appearance = h->G.appearance;
+    B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = loss_scale;
+    if ((e = launch_field_backward(h->M, B, st)) != cudaSuccess) return cuda_fail(e, "k_field_backward");
+    h->launches++;
+    // pass 3: interlevel loss -> proposal networks (only when the sampler says they carry autograd)
+    if (proposal_requires_grad && h->M.interlevel_mult != 0.f) {
+      PropBwdArgs Q;
+      memset(&Q, 0, sizeof(Q));
+      fill_sample_args(h, Q, rays, off, n);
+      for (int i = 0; i < 2; ++i) {
+        Q.g_table[i] = reinterpret_cast<float2*>(h->G.prop_table[i]);
+        Q.g_w0[i] = h->G.prop_w0[i]; Q.g_b0[i] = h->G.prop_b0[i];
+        Q.g_w1[i] = h->G.prop_w1[i]; Q.g_b1[i] = h->G.prop_b1[i];
+      }
+      Q.weights2 = weights2; Q.s_edges2_in = s_edges; Q.reg_chunk = chunk_rays; Q.loss_scale = loss_scale;
+      if ((e = launch_prop_backward(h->M, Q, st)) != cudaSuccess) return cuda_fail(e, "k_prop_backward");
+      h->launches++;
+    }
+    FinalizeArgs Z;
+    memset(&Z, 0, sizeof(Z));
+    fill_ray_args(Z, rays, off, n);
+    Z.ray_grad = ray_grad; Z.grad_o = grad_o; Z.grad_v = grad_v;
+    if ((e = launch_finalize_ray_grads(h->M, Z, st)) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
+    h->launches++;
+  }
   return NEMIT_OK;
 }
 

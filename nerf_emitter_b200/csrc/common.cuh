@@ -215,4 +215,100 @@ __device__ __forceinline__ void weights_from_ds(const float (&ds)[K], float (&w)
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// derivatives (jvp / backward kernels)
+// ---------------------------------------------------------------------------------------------
+// d(blend_cell)/d(offset): the reference's a*f + b*(1-f) differentiates to (a - b) per axis.
+__device__ __forceinline__ void blend_cell_grad(const float2 v[8], const LevelCell& c, float2& gx, float2& gy, float2& gz) {
+  const float fx = c.fx, fy = c.fy, fz = c.fz, ux = 1.f - fx, uy = 1.f - fy, uz = 1.f - fz;
+#define NEMIT_BCG(F)                                                                              \
+  {                                                                                               \
+    float a = v[0].F * fx + v[1].F * ux, b = v[2].F * fx + v[3].F * ux;                           \
+    float cc = v[4].F * fx + v[5].F * ux, d = v[6].F * fx + v[7].F * ux;                          \
+    gz.F = (a * fy + b * uy) - (cc * fy + d * uy);                                                \
+    gy.F = fz * (a - b) + uz * (cc - d);                                                          \
+    gx.F = fz * (fy * (v[0].F - v[1].F) + uy * (v[2].F - v[3].F)) +                               \
+           uz * (fy * (v[4].F - v[5].F) + uy * (v[6].F - v[7].F));                                \
+  }
+  NEMIT_BCG(x)
+  NEMIT_BCG(y)
+#undef NEMIT_BCG
+}
+
+// trilinear corner weights in the LevelCell corner order
+__device__ __forceinline__ void corner_weights(const LevelCell& c, float w[8]) {
+  const float fx = c.fx, fy = c.fy, fz = c.fz, ux = 1.f - fx, uy = 1.f - fy, uz = 1.f - fz;
+  w[0] = fx * fy * fz; w[1] = ux * fy * fz; w[2] = fx * uy * fz; w[3] = ux * uy * fz;
+  w[4] = fx * fy * uz; w[5] = ux * fy * uz; w[6] = fx * uy * uz; w[7] = ux * uy * uz;
+}
+
+// Contraction + (x+2)/4 + selector: vector-Jacobian product g_p -> g_x (spatial_distortions.py:67-70).
+// x' = x (m<1) else f(m) x, f = (2-1/m)/m, m = |x_j| the max component.
+__device__ __forceinline__ void contract_vjp(const float x[3], bool sel, const float gp[3], float gx[3]) {
+  if (!sel) { gx[0] = gx[1] = gx[2] = 0.f; return; }
+  float a0 = fabsf(x[0]), a1 = fabsf(x[1]), a2 = fabsf(x[2]);
+  float m = fmaxf(a0, fmaxf(a1, a2));
+  if (m < 1.f) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) gx[k] = 0.25f * gp[k];
+    return;
+  }
+  int j = (a0 >= a1 && a0 >= a2) ? 0 : (a1 >= a2 ? 1 : 2);
+  float inv = 1.f / m;
+  float f = (2.f - inv) * inv;
+  float fp = 2.f * inv * inv * (inv - 1.f);
+  float dot = gp[0] * x[0] + gp[1] * x[1] + gp[2] * x[2];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) gx[k] = 0.25f * f * gp[k];
+  gx[j] += 0.25f * dot * fp * (x[j] < 0.f ? -1.f : 1.f);
+}
+
+// forward-mode counterpart: tangent of p given the tangent of x
+__device__ __forceinline__ void contract_jvp(const float x[3], bool sel, const float dx[3], float dp[3]) {
+  if (!sel) { dp[0] = dp[1] = dp[2] = 0.f; return; }
+  float a0 = fabsf(x[0]), a1 = fabsf(x[1]), a2 = fabsf(x[2]);
+  float m = fmaxf(a0, fmaxf(a1, a2));
+  if (m < 1.f) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) dp[k] = 0.25f * dx[k];
+    return;
+  }
+  int j = (a0 >= a1 && a0 >= a2) ? 0 : (a1 >= a2 ? 1 : 2);
+  float inv = 1.f / m;
+  float f = (2.f - inv) * inv;
+  float fp = 2.f * inv * inv * (inv - 1.f);
+  float dm = (x[j] < 0.f ? -1.f : 1.f) * dx[j];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) dp[k] = 0.25f * (f * dx[k] + x[k] * fp * dm);
+}
+
+__device__ __forceinline__ float warp_incl_scan_f(float v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    float t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
+}
+
+// like weights_from_ds but also returns the transmittance T and e = exp(-ds) (alpha = 1 - e)
+template <int K>
+__device__ __forceinline__ void weights_full(const float (&ds)[K], float (&w)[K], float (&T)[K], float (&e)[K], int lane) {
+  double carry = 0.0;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double inc = warp_incl_scan((double)ds[k], lane);
+    double exc = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) exc = 0.0;
+    float prefix = (float)(carry + exc);
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+    e[k] = expf(-ds[k]);
+    T[k] = expf(-prefix);
+    w[k] = nan_to_num(mul_rn(sub_rn(1.f, e[k]), T[k]));
+  }
+}
+
+// float2 reduction into a gradient table (red.global.add.v2.f32 on sm_90+)
+__device__ __forceinline__ void atomic_add_f2(float2* addr, float2 v) { atomicAdd(addr, v); }
+
 }  // namespace nemit

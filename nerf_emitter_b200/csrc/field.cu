@@ -17,8 +17,13 @@ struct FieldSmem {
   float ray_o[kRaysPerGroup * 3];
   float ray_d[kRaysPerGroup * 3];
   float app_tmp[kApp];
+  float s_edge[kRaysPerGroup * (kS2 + 1)];   // adjoint-seed mode only
 };
 
+// MODE 0: forward (rgb, accumulation, weights).  MODE 1: first pass of the backward - same forward,
+// then the per-ray composite adjoint (RGB renderer, get_weights, distortion loss, t^2 gradient
+// scaling) writes dL/dsigma and dL/drgb_sample for k_field_backward.
+template <int MODE>
 __global__ void __launch_bounds__(128)
 k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -42,6 +47,7 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
     for (int i = tid; i < kRaysPerGroup * (kS2 + 1); i += 128) {
       int rr = i / (kS2 + 1);
       sm->t_edge[i] = rr < rays_here ? A.t_edges2[r0 * (kS2 + 1) + i] : 0.f;
+      if (MODE == 1) sm->s_edge[i] = rr < rays_here ? A.s_edges2[r0 * (kS2 + 1) + i] : 0.f;
     }
     __syncthreads();
 
@@ -95,6 +101,11 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
 
     // composite: warp w handles rays w and w+4; lane handles samples lane and lane+32
     for (int rr = wid; rr < rays_here; rr += 4) {
+      if (MODE == 1) {
+        composite_adjoint_ray(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)], &sm->sigma[rr * kS2],
+                              &sm->rgb[rr * kS2 * 3], r0 + rr, lane);
+        continue;
+      }
       float ds[2], w[2];
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
@@ -134,19 +145,26 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
   }
 }
 
-cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+template <int MODE>
+static cudaError_t launch_field_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static bool attr_set = false;
   size_t smem = sizeof(FieldSmem);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_field_forward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_field_forward<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   int64_t ctas = groups < 148 * 2 ? groups : 148 * 2;     // persistent: 2 CTAs per SM (smem-limited)
-  k_field_forward<<<(unsigned)ctas, 128, smem, stream>>>(M, A);
+  k_field_forward<MODE><<<(unsigned)ctas, 128, smem, stream>>>(M, A);
   return cudaGetLastError();
+}
+cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+  return launch_field_mode<0>(M, A, stream);
+}
+cudaError_t launch_field_adjoint_seed(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+  return launch_field_mode<1>(M, A, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

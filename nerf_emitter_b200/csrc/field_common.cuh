@@ -155,4 +155,186 @@ __device__ __forceinline__ void load_field_weights(FieldWeightsSmem* S, const Fi
   __syncthreads();
 }
 
+// Reverse-mode adjoint of RGBRenderer + get_weights + distortion loss for ONE ray, one warp
+// (NS/model_components/renderers.py:71-121,203-234; NS/cameras/rays.py:128-150;
+// NS/model_components/losses.py:134-153,558-577; objective NS/pipelines/mitsuba_sdf.py:1170-1177).
+// t_edge / s_edge: the ray's 49 euclidean / spacing edges; sigma (48) and rgb (48x3) in shared memory
+// (sigma is overwritten with the weights).  Writes dL/dsigma, dL/drgb_sample (t^2 scaling applied)
+// and the final weights of global ray r (chunk-local index).
+__device__ __forceinline__ void composite_adjoint_ray(const ModelDev& M, const FieldArgs& A, const float* t_edge,
+                                                      const float* s_edge, float* sigma, const float* rgb,
+                                                      int64_t r, int lane) {
+  const bool eval = !A.training;
+  float ds[2], w[2], T[2], e[2], delta[2], scale[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    int si = k * 32 + lane;
+    ds[k] = 0.f; delta[k] = 0.f; scale[k] = 0.f;
+    if (si < kS2) {
+      float t0 = t_edge[si], t1 = t_edge[si + 1];
+      delta[k] = sub_rn(t1, t0);
+      ds[k] = mul_rn(delta[k], sigma[si]);
+      float tm = (t0 + t1) * 0.5f;
+      scale[k] = fminf(fmaxf(tm * tm, 0.f), 1.f);
+    }
+  }
+  weights_full<2>(ds, w, T, e, lane);
+  __syncwarp();
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    int si = k * 32 + lane;
+    if (si < kS2) sigma[si] = w[k];           // weights visible to all lanes (distortion term)
+  }
+  __syncwarp();
+  float c[2][3], fin[2][3];
+  float cr = 0.f, cg = 0.f, cb = 0.f, acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    int si = k * 32 + lane;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) { c[k][ch] = 0.f; fin[k][ch] = 1.f; }
+    if (si < kS2) {
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) {
+        float v = rgb[si * 3 + ch];
+        if (eval) { fin[k][ch] = (isnan(v) || isinf(v)) ? 0.f : 1.f; v = nan_to_num(v); }
+        c[k][ch] = v;
+      }
+      cr = fmaf(w[k], c[k][0], cr); cg = fmaf(w[k], c[k][1], cg); cb = fmaf(w[k], c[k][2], cb);
+      acc += w[k];
+      if (A.weights2) A.weights2[r * kS2 + si] = w[k];
+    }
+  }
+  cr = warp_sum(cr); cg = warp_sum(cg); cb = warp_sum(cb); acc = warp_sum(acc);
+  float last[3];
+#pragma unroll
+  for (int ch = 0; ch < 3; ++ch) {
+    float v = rgb[(kS2 - 1) * 3 + ch];
+    last[ch] = eval ? nan_to_num(v) : v;
+  }
+  const float bg = 1.f - acc;
+  const int64_t rg = A.ray_offset + r;
+  float gb[3] = {A.grad_rgb[rg * 3 + 0], A.grad_rgb[rg * 3 + 1], A.grad_rgb[rg * 3 + 2]};
+  if (eval) {   // clamp(min=0) passes the gradient where the composite is >= 0
+    if (!(cr + last[0] * bg >= 0.f)) gb[0] = 0.f;
+    if (!(cg + last[1] * bg >= 0.f)) gb[1] = 0.f;
+    if (!(cb + last[2] * bg >= 0.f)) gb[2] = 0.f;
+  }
+  // regulariser means are per backward chunk (get_reg_loss_dict is evaluated per chunk)
+  const int64_t chunk = A.reg_chunk > 0 ? A.reg_chunk : A.n_total;
+  const int64_t c0 = (rg / chunk) * chunk;
+  const float cnt = (float)min(chunk, A.n_total - c0);
+  const float dm = M.distortion_mult / cnt;
+  float gw[2], gww[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    int si = k * 32 + lane;
+    gw[k] = 0.f; gww[k] = 0.f;
+    if (si < kS2) {
+      float ui = (s_edge[si] + s_edge[si + 1]) * 0.5f;
+      float inter = 0.f;
+#pragma unroll 4
+      for (int j = 0; j < kS2; ++j) {
+        float uj = (s_edge[j] + s_edge[j + 1]) * 0.5f;
+        inter = fmaf(sigma[j], fabsf(ui - uj), inter);
+      }
+      float dist = 2.f * inter + 2.f * w[k] * (s_edge[si + 1] - s_edge[si]) * (1.f / 3.f);
+      gw[k] = gb[0] * (c[k][0] - last[0]) + gb[1] * (c[k][1] - last[1]) + gb[2] * (c[k][2] - last[2]) + dm * dist;
+      gww[k] = gw[k] * w[k];
+    }
+  }
+  // suffix sums of gw*w over later samples
+  float inc0 = warp_incl_scan_f(gww[0], lane);
+  float tot0 = __shfl_sync(0xffffffffu, inc0, 31);
+  float inc1 = warp_incl_scan_f(gww[1], lane) + tot0;
+  float total = __shfl_sync(0xffffffffu, inc1, 31);
+  float suffix[2] = {total - inc0, total - inc1};
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    int si = k * 32 + lane;
+    if (si < kS2) {
+      float gds = gw[k] * T[k] * e[k] - suffix[k];
+      A.g_sigma[r * kS2 + si] = gds * delta[k] * scale[k];
+      float wl = w[k] + (si == kS2 - 1 ? bg : 0.f);
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) A.g_rgbs[(r * kS2 + si) * 3 + ch] = gb[ch] * wl * fin[k][ch] * scale[k];
+    }
+  }
+  __syncwarp();
+}
+
+// Tangent GEMM: Yd[n][m] = (MASK ? Yp[n][m] > 0 : 1) * sum_k Wt[k][n] * Xd[k][m]  (no bias; ReLU mask from
+// the primal tile Yp).  Same thread mapping as tile_gemm.
+template <int K, int N, bool MASK>
+__device__ __forceinline__ void tile_gemm_tangent(const float* __restrict__ Xd, const float* __restrict__ Wt,
+                                                  const float* __restrict__ Yp, float* __restrict__ Yd, int tid) {
+  constexpr int TN = N / 8;
+  static_assert(N % 8 == 0 && (TN == 8 || TN == 2), "tile shape");
+  const int tm = tid & 15, tn = tid >> 4;
+  float acc[8][TN];
+#pragma unroll
+  for (int j = 0; j < TN; ++j)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i][j] = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < K; ++k) {
+    const float4 a0 = *reinterpret_cast<const float4*>(Xd + k * kTileM + tm * 8);
+    const float4 a1 = *reinterpret_cast<const float4*>(Xd + k * kTileM + tm * 8 + 4);
+    float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    float w[TN];
+    if constexpr (TN == 8) {
+      const float4 w0 = *reinterpret_cast<const float4*>(Wt + k * N + tn * 8);
+      const float4 w1 = *reinterpret_cast<const float4*>(Wt + k * N + tn * 8 + 4);
+      w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w; w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+    } else {
+      const float2 w0 = *reinterpret_cast<const float2*>(Wt + k * N + tn * 2);
+      w[0] = w0.x; w[1] = w0.y;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+  }
+#pragma unroll
+  for (int j = 0; j < TN; ++j) {
+    float o[8];
+    const int off = (tn * TN + j) * kTileM + tm * 8;
+    if (MASK) {
+      const float4 y0 = *reinterpret_cast<const float4*>(Yp + off);
+      const float4 y1 = *reinterpret_cast<const float4*>(Yp + off + 4);
+      const float y[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = y[i] > 0.f ? acc[i][j] : 0.f;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = acc[i][j];
+    }
+    *reinterpret_cast<float4*>(Yd + off) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(Yd + off + 4) = make_float4(o[4], o[5], o[6], o[7]);
+  }
+}
+
+// tangent of sh16 for direction tangent (dx, dy, dz)
+__device__ __forceinline__ void sh16_tangent(float x, float y, float z, float dx, float dy, float dz, float t[16]) {
+  const float k1 = 0.4886025119029199f, k2 = 1.0925484305920792f;
+  float xx = x * x, yy = y * y, zz = z * z;
+  float dxx = 2.f * x * dx, dyy = 2.f * y * dy, dzz = 2.f * z * dz;
+  t[0] = 0.f;
+  t[1] = k1 * dy;
+  t[2] = k1 * dz;
+  t[3] = k1 * dx;
+  t[4] = k2 * (dx * y + x * dy);
+  t[5] = k2 * (dy * z + y * dz);
+  t[6] = 0.9461746957575601f * dzz;
+  t[7] = k2 * (dx * z + x * dz);
+  t[8] = 0.5462742152960396f * (dxx - dyy);
+  t[9] = 0.5900435899266435f * (dy * (3.f * xx - yy) + y * (3.f * dxx - dyy));
+  t[10] = 2.890611442640554f * (dx * y * z + x * dy * z + x * y * dz);
+  t[11] = 0.4570457994644658f * (dy * (5.f * zz - 1.f) + y * 5.f * dzz);
+  t[12] = 0.3731763325901154f * (dz * (5.f * zz - 3.f) + z * 5.f * dzz);
+  t[13] = 0.4570457994644658f * (dx * (5.f * zz - 1.f) + x * 5.f * dzz);
+  t[14] = 1.445305721320277f * (dz * (xx - yy) + z * (dxx - dyy));
+  t[15] = 0.5900435899266435f * (dx * (xx - 3.f * yy) + x * (dxx - 3.f * dyy));
+}
+
 }  // namespace nemit

@@ -58,10 +58,57 @@ struct FieldArgs : RayArgs {
   const float* d_o;        // (3, n_total)
   const float* d_v;
   float* d_rgb;            // (n, 3)
+  // adjoint-seed mode (first pass of the backward): composite adjoint per ray
+  const float* s_edges2;   // (n, 49) chunk-local spacing edges (distortion loss)
+  const float* grad_rgb;   // (n_total, 3)
+  float* g_sigma;          // (n, 48)  dL/dsigma (post-selector density), gradient scaling applied
+  float* g_rgbs;           // (n, 48, 3) dL/drgb_sample, gradient scaling applied
+  int64_t reg_chunk;       // rays per backward chunk over which the regulariser means are taken
+};
+
+// gradient accumulators in the torch parameter layouts (atomically accumulated)
+struct FieldGrads {
+  float2* main_table;
+  float* base_w0; float* base_b0;
+  float* base_w1; float* base_b1;
+  float* head_w0; float* head_b0;
+  float* head_w1; float* head_b1;
+  float* head_w2; float* head_b2;
+  float* appearance;
+};
+
+struct FieldBwdArgs : RayArgs {
+  FieldParams P;
+  FieldGrads G;
+  const float* t_edges2;   // (n, 49)
+  const float* g_sigma;    // (n, 48)
+  const float* g_rgbs;     // (n, 48, 3)
+  float* ray_grad;         // (n, 6) zero-initialised accumulators: d/d(o_nerf), d/d(d_nerf)
+  float loss_scale;        // applied to parameter gradients only
+};
+
+struct PropBwdArgs : SampleArgs {
+  float2* g_table[2];
+  float* g_w0[2]; float* g_b0[2]; float* g_w1[2]; float* g_b1[2];
+  const float* weights2;   // (n, 48) final weights (detached in the interlevel loss)
+  const float* s_edges2_in;// (n, 49)
+  int64_t reg_chunk;
+  float loss_scale;
+};
+
+struct FinalizeArgs : RayArgs {
+  const float* ray_grad;   // (n, 6)
+  float* grad_o;           // (3, n_total)
+  float* grad_v;
 };
 
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
+cudaError_t launch_field_adjoint_seed(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
+cudaError_t launch_field_jvp(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
+cudaError_t launch_field_backward(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
+cudaError_t launch_prop_backward(const ModelDev& M, const PropBwdArgs& A, cudaStream_t stream);
+cudaError_t launch_finalize_ray_grads(const ModelDev& M, const FinalizeArgs& A, cudaStream_t stream);
 cudaError_t launch_hash_encode(const GridDev& G, const float2* table, const float* x, int64_t n, float* out,
                                cudaStream_t stream);
 

@@ -74,7 +74,7 @@ __device__ __forceinline__ float prop_mlp_raw(const float enc[kPropEnc], const P
 }
 
 // density at a sample position (NeRF coordinates): contraction -> hash -> MLP -> trunc_exp * selector
-__device__ __noinline__ float prop_density(float x0, float x1, float x2, const float2* __restrict__ table,
+static __device__ __noinline__ float prop_density(float x0, float x1, float x2, const float2* __restrict__ table,
                                            const GridDev& G, const PropMlpSmem* W, const ModelDev& M) {
   float x[3] = {x0, x1, x2}, p[3];
   if (!contract_normalise(x, M, p)) return 0.f;   // reference evaluates at p=0 and multiplies by 0
@@ -135,7 +135,8 @@ struct RayCtx {
 // Edges must be in sc->s_edge[0..S].  S is a multiple of 32.
 __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const RayCtx& R, int S,
                                                        const float2* __restrict__ table, const GridDev& G,
-                                                       const PropMlpSmem* W, const ModelDev& M, int lane) {
+                                                       const PropMlpSmem* W, const ModelDev& M, int lane,
+                                                       float* ds_out = nullptr) {
 #pragma unroll 1
   for (int i = lane; i < S; i += 32) {
     float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far);
@@ -144,6 +145,7 @@ __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const Ra
     float sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
                                sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
     sc->buf[i] = mul_rn(sub_rn(t1, t0), sigma);
+    if (ds_out) ds_out[i] = sc->buf[i];
   }
   __syncwarp();
   // exclusive prefix accumulated in float64 and rounded to float32 per prefix (ATen's CPU cumsum)

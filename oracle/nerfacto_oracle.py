@@ -226,10 +226,14 @@ def pdf_resample(w, s_edges, num_new: int, jitter: Optional[torch.Tensor], pad: 
 # --------------------------------------------------------------------------------------------
 def sample_levels(P, spec: EmitterModelSpec, o, d, near: float, far: float, aabb, *,
                   disable_inside_aabb=True, jitter: Optional[Sequence[torch.Tensor]] = None,
-                  anneal: float = 1.0, proposal_requires_grad: bool = False):
+                  anneal: float = 1.0, proposal_requires_grad: bool = False,
+                  edges_override: Optional[Sequence[Optional[torch.Tensor]]] = None):
     """nerfstudio/model_components/ray_samplers.py:584-626.  o, d (N,3) NeRF coords (detached by
     the caller for the backward variant, sdf_nerfacto.py:121-126).  Returns per-level spacing edges,
-    euclidean edges, weights and the searchsorted indices."""
+    euclidean edges, weights and the searchsorted indices.
+    edges_override (tests only): spacing edges [None, s_edges1, s_edges2] to use instead of this function's
+    own PDF-stage outputs, so that a checker can evaluate the field at bit-identical sample positions
+    (the path is ill-conditioned w.r.t. 1-ulp position changes, see DESIGN.md "Conditioning")."""
     N = o.shape[0]
     nears = torch.ones_like(o[..., 0:1]) * near
     fars = torch.ones_like(o[..., 0:1]) * far
@@ -246,6 +250,8 @@ def sample_levels(P, spec: EmitterModelSpec, o, d, near: float, far: float, aabb
             s_e, idx, cdf = pdf_resample(torch.pow(w, anneal), s_e, S, jit)
             out["inds"].append(idx)
             out["cdf"].append(cdf)
+            if edges_override is not None and edges_override[lvl] is not None:
+                s_e = edges_override[lvl].detach()
         t_e = s_to_euclid(s_e, s_near, s_far)                       # (N, S+1)
         out["s_edges"].append(s_e)
         out["t_edges"].append(t_e)
@@ -409,7 +415,8 @@ class OracleEmitter:
         return sample_levels(self.P, self.spec, o, d, self._near_plane(), self.spec.far_plane, self.aabb,
                              disable_inside_aabb=self.disable_inside_aabb,
                              jitter=jitter if self.training else None, anneal=self.anneal,
-                             proposal_requires_grad=proposal_requires_grad)
+                             proposal_requires_grad=proposal_requires_grad,
+                             edges_override=getattr(self, "edges_override", None))
 
     @torch.no_grad()
     def render(self, o3n, v3n, near=0.0, camera_idx=0, jitter=None, return_aux=False):

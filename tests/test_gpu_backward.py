@@ -1,0 +1,248 @@
+"""GPU parity: CUDA forward-mode (nemit_jvp) and reverse-mode (nemit_backward) through the C ABI vs the
+reference goldens (made by the reference's own torch classes) and the CPU oracle.
+Tolerance: 1e-3 max-norm relative per tensor (BASELINE.json north_star, fp32 mode)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import GOLDEN_CASES, golden_inputs, load_golden, make_rays, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def emitters(spec, params_factory):
+    from nerf_emitter_b200 import NerfEmitter
+    cache = {}
+
+    def get(seed, scale):
+        if (seed, scale) not in cache:
+            cache[(seed, scale)] = NerfEmitter(params_factory(seed, scale), spec, device=torch.device("cuda:0"))
+        return cache[(seed, scale)]
+    return get
+
+
+WELL_CONDITIONED = ["eval_default_init"]          # hash tables U(-1e-3,1e-3): strict gate on every ray
+STRESS = ["eval_stress", "train_stress"]          # tables x1e3: see _stability below
+
+
+def _oracle_for(G, spec, params_factory):
+    from oracle.nerfacto_oracle import OracleEmitter
+    O = OracleEmitter(params_factory(int(G["param_seed"]), float(G["table_scale"])), spec)
+    O.train(bool(G["training"]))
+    return O
+
+
+def _stability(O, I, prg=True):
+    """The stress init (tables U(-1,1) at resolutions up to 2047) makes the encoding move by ~2.6e-4 per
+    ulp of sample position, so first-layer ReLU signs of individual samples flip under 1-ulp input noise and
+    the REFERENCE's own per-ray derivatives jump by several percent on ~7 % of the rays (measured, DESIGN.md
+    "Conditioning").  This returns, from the oracle alone, which rays are stable under +-1 ulp of the
+    origins and how much the parameter gradients move.  End-to-end gates on the stress goldens therefore
+    ask for >= 85 % of the rays within 1e-3 (and none beyond 0.25) and bound parameter gradients by the
+    reference's own movement; the STRICT every-ray 1e-3 gate is test_derivatives_strict_given_same_samples."""
+    kw = dict(near=I["near"], camera_idx=I["camera_idx"], jitter=I["jitter"])
+    base = O.vjp(I["o"], I["v"], I["grad_out"], proposal_requires_grad=prg, **kw)
+    jb = O.jvp(I["o"], I["v"], I["do"], I["dv"], **kw)
+    stable = torch.ones(I["N"], dtype=torch.bool)
+    pmove = {k: 0.0 for k in base[2]}
+    for direction in (2.0, -2.0):
+        o2 = torch.nextafter(I["o"], torch.full_like(I["o"], direction))
+        alt = O.vjp(o2, I["v"], I["grad_out"], proposal_requires_grad=prg, **kw)
+        ja = O.jvp(o2, I["v"], I["do"], I["dv"], **kw)
+        for a, b in [(alt[0], base[0]), (alt[1], base[1])]:
+            stable &= (a - b).abs().max(0).values <= 2.5e-4 * b.abs().max()
+        stable &= (ja - jb).abs().max(1).values <= 2.5e-4 * jb.abs().max()
+        for k in pmove:
+            pmove[k] = max(pmove[k], rel_err(alt[2][k], base[2][k]))
+    return stable, pmove
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_jvp_matches_reference_golden(case, spec, params_factory, emitters):
+    G = load_golden(case)
+    I = golden_inputs(G)
+    E = emitters(int(G["param_seed"]), float(G["table_scale"]))
+    E.train(I["training"])
+    t = E.jvp(I["o"].cuda(), I["v"].cuda(), I["do"].cuda(), I["dv"].cuda(), near=I["near"],
+              camera_idx=I["camera_idx"], jitter=I["jitter"]).cpu()
+    ref = torch.from_numpy(G["jvp"])
+    if case in WELL_CONDITIONED:
+        assert rel_err(t, ref) < TOL, rel_err(t, ref)
+        return
+    stable, _ = _stability(_oracle_for(G, spec, params_factory), I)
+    per_ray = (t - ref).abs().max(1).values / ref.abs().max()
+    frac_ok = float((per_ray < TOL).float().mean())
+    print(case, "jvp: rays within 1e-3: %.1f%% (reference vs itself under +-1 ulp: %.1f%%), worst %.2e" % (
+        100 * frac_ok, 100 * float(stable.float().mean()), float(per_ray.max())))
+    assert frac_ok >= 0.85 and float(per_ray.max()) < 0.25
+
+
+def _check_param_grads(tag, grads, G, prefix, tol_of):
+    for name, g in grads.items():
+        g = g.cpu()
+        tol = tol_of(name)
+        if name.endswith("hash_table"):
+            flat = g.reshape(-1).double()
+            abssum = float(G[prefix + name + "::abssum"])
+            s = float(G[prefix + name + "::sum"])
+            if abssum == 0.0:
+                assert float(flat.abs().sum()) == 0.0, (tag, name)
+                continue
+            assert abs(float(flat.abs().sum()) - abssum) / abssum < tol, (tag, name, "abssum")
+            assert abs(float(flat.sum()) - s) / abssum < tol, (tag, name, "sum")
+            idx = torch.from_numpy(G[prefix + name + "::pick_idx"])
+            val = torch.from_numpy(G[prefix + name + "::pick_val"])
+            e = rel_err(flat[idx].float(), val)
+            assert e < tol, (tag, name, "picked rows", e, tol)
+        else:
+            ref = G[prefix + name]
+            e = rel_err(g, ref.reshape(g.shape))
+            assert e < tol, (tag, name, e, tol)
+
+
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+@pytest.mark.parametrize("prg", [True, False])
+def test_backward_matches_reference_golden(case, prg, spec, params_factory, emitters):
+    G = load_golden(case)
+    I = golden_inputs(G)
+    E = emitters(int(G["param_seed"]), float(G["table_scale"]))
+    E.train(I["training"])
+    E.bind_grads()
+    go, gv = E.backward(I["o"].cuda(), I["v"].cuda(), I["grad_out"].cuda(), near=I["near"],
+                        camera_idx=I["camera_idx"], jitter=I["jitter"], chunk_rays=I["N"],
+                        proposal_requires_grad=prg)
+    torch.cuda.synchronize()
+    pre = "vjp_prop%d::" % int(prg)
+    ro, rv = torch.from_numpy(G[pre + "grad_o"]), torch.from_numpy(G[pre + "grad_v"])
+    if case in WELL_CONDITIONED:
+        assert rel_err(go.cpu(), ro) < TOL and rel_err(gv.cpu(), rv) < TOL
+        _check_param_grads(case, E.grads, G, pre, lambda name: TOL)
+        return
+    stable, pmove = _stability(_oracle_for(G, spec, params_factory), I, prg)
+    per_ray = torch.maximum((go.cpu() - ro).abs().max(0).values / ro.abs().max(),
+                            (gv.cpu() - rv).abs().max(0).values / rv.abs().max())
+    frac_ok = float((per_ray < TOL).float().mean())
+    print(case, prg, "ray grads within 1e-3: %.1f%% of rays (reference vs itself under +-1 ulp: %.1f%%), worst %.2e" % (
+        100 * frac_ok, 100 * float(stable.float().mean()), float(per_ray.max())))
+    assert frac_ok >= 0.85 and float(per_ray.max()) < 0.25
+    # parameter gradients sum over all rays: gate at the reference's own movement under 1-ulp input noise
+    _check_param_grads(case, E.grads, G, pre, lambda name: max(TOL, 4.0 * pmove[name]))
+
+
+def _same_samples(O, E, o, v, **kw):
+    """Make the oracle evaluate at the GPU's own sample edges (bit-identical sample positions)."""
+    aux = E.sample_levels(o.cuda(), v.cuda(), **kw)
+    torch.cuda.synchronize()
+    O.edges_override = [None, aux["s_edges1"].cpu(), aux["s_edges2"].cpu()]
+
+
+@pytest.mark.parametrize("training", [False, True])
+def test_derivatives_strict_given_same_samples(training, spec, params_factory, emitters):
+    """Strict 1e-3 gate on EVERY ray and every parameter with the stress init: the oracle is evaluated at the
+    sample edges the CUDA path produced, which removes the 1-ulp position noise (and with it the ReLU-sign
+    lottery) from the comparison; everything downstream of the sampler is compared in full."""
+    from oracle.nerfacto_oracle import OracleEmitter
+    P = params_factory(0, 1e3)
+    O = OracleEmitter(P, spec)
+    E = emitters(0, 1e3)
+    O.train(training)
+    E.train(training)
+    N = 384
+    o, v, g = make_rays(N, seed=91)
+    jit = [torch.rand(N, 1, generator=g) for _ in range(3)] if training else None
+    do, dv = torch.randn(3, N, generator=g), torch.randn(3, N, generator=g)
+    gout = torch.randn(N, 3, generator=g)
+    kw = dict(near=0.02, camera_idx=1, jitter=jit)
+    _same_samples(O, E, o, v, **kw)
+    ref_t = O.jvp(o, v, do, dv, **kw)
+    t = E.jvp(o.cuda(), v.cuda(), do.cuda(), dv.cuda(), **kw).cpu()
+    assert rel_err(t, ref_t) < TOL, ("jvp", rel_err(t, ref_t))
+    ref_go, ref_gv, ref_grads, _ = O.vjp(o, v, gout, **kw)
+    E.bind_grads()
+    go, gv = E.backward(o.cuda(), v.cuda(), gout.cuda(), chunk_rays=N, **kw)
+    torch.cuda.synchronize()
+    assert rel_err(go.cpu(), ref_go) < TOL, ("grad_o", rel_err(go.cpu(), ref_go))
+    assert rel_err(gv.cpu(), ref_gv) < TOL, ("grad_v", rel_err(gv.cpu(), ref_gv))
+    for k, gr in E.grads.items():
+        e = rel_err(gr.cpu(), ref_grads[k])
+        print("%-60s %.3e" % (k, e))
+        assert e < TOL, (k, e)
+
+
+def test_backward_matches_oracle_chunked(spec, params_factory, emitters):
+    """512 rays in backward chunks of 200 (ragged last chunk): regulariser means are per chunk, parameter
+    gradients accumulate over chunks like .backward() does (mitsuba_sdf.py:1180-1190); loss_scale scales
+    parameter gradients only."""
+    from oracle.nerfacto_oracle import OracleEmitter
+    P = params_factory(0, 1e3)
+    O = OracleEmitter(P, spec)
+    E = emitters(0, 1e3)
+    O.train(True)
+    E.train(True)
+    N, C = 512, 200
+    o, v, g = make_rays(N, seed=77)
+    jit = [torch.rand(N, 1, generator=g) for _ in range(3)]
+    gout = torch.randn(N, 3, generator=g)
+    near = 0.05
+    ref_go, ref_gv = torch.zeros(3, N), torch.zeros(3, N)
+    ref_grads = None
+    aux = E.sample_levels(o.cuda(), v.cuda(), near=near, camera_idx=2, jitter=jit)
+    s1, s2 = aux["s_edges1"].cpu(), aux["s_edges2"].cpu()
+    for a in range(0, N, C):
+        b = min(a + C, N)
+        O.edges_override = [None, s1[a:b], s2[a:b]]
+        go, gv, grads, _ = O.vjp(o[:, a:b].contiguous(), v[:, a:b].contiguous(), gout[a:b], near=near, camera_idx=2,
+                                 jitter=[j[a:b] for j in jit])
+        ref_go[:, a:b], ref_gv[:, a:b] = go, gv
+        ref_grads = grads if ref_grads is None else {k: ref_grads[k] + grads[k] for k in grads}
+    E.bind_grads()
+    go, gv = E.backward(o.cuda(), v.cuda(), gout.cuda(), near=near, camera_idx=2, jitter=jit, chunk_rays=C,
+                        loss_scale=4.0)
+    torch.cuda.synchronize()
+    assert rel_err(go.cpu(), ref_go) < TOL and rel_err(gv.cpu(), ref_gv) < TOL
+    for k, gr in E.grads.items():
+        e = rel_err(gr.cpu() / 4.0, ref_grads[k])
+        print("%-60s %.3e" % (k, e))
+        assert e < TOL, (k, e)
+    # accumulation: a second call doubles the parameter gradients
+    snap = {k: t.clone() for k, t in E.grads.items()}
+    E.backward(o.cuda(), v.cuda(), gout.cuda(), near=near, camera_idx=2, jitter=jit, chunk_rays=C, loss_scale=4.0)
+    torch.cuda.synchronize()
+    for k in snap:
+        assert rel_err(E.grads[k].cpu(), 2 * snap[k].cpu()) < 1e-4, k
+
+
+def test_jvp_matches_oracle_per_ray_near(spec, params_factory, emitters):
+    from oracle.nerfacto_oracle import OracleEmitter
+    P = params_factory(0, 1e3)
+    O = OracleEmitter(P, spec)
+    E = emitters(0, 1e3)
+    O.train(False)
+    E.train(False)
+    N = 777
+    o, v, g = make_rays(N, seed=5)
+    do, dv = torch.randn(3, N, generator=g), torch.randn(3, N, generator=g)
+    near = torch.rand(N, generator=g) * 0.3
+    aux = E.sample_levels(o.cuda(), v.cuda(), near=near.cuda())
+    O.edges_override = [None, aux["s_edges1"].cpu(), aux["s_edges2"].cpu()]
+    ref = O.jvp(o, v, do, dv, near=near[:, None])
+    out = E.jvp(o.cuda(), v.cuda(), do.cuda(), dv.cuda(), near=near.cuda())
+    torch.cuda.synchronize()
+    assert rel_err(out.cpu(), ref) < TOL, rel_err(out.cpu(), ref)
+
+
+def test_backward_requires_bound_grads(spec, params_factory):
+    from nerf_emitter_b200 import NerfEmitter
+    import ctypes as C
+    from nerf_emitter_b200 import lib as L
+    E = NerfEmitter(params_factory(0, 1e3), spec, device=torch.device("cuda:0"))
+    o, v, _ = make_rays(4)
+    R = E._rays(o.cuda(), v.cuda(), 0.0, 0, None)
+    g = torch.zeros(4, 3, device="cuda")
+    go = torch.zeros(3, 4, device="cuda")
+    ws = E._workspace(4)
+    rc = E.lib.nemit_backward(E._h, C.byref(R), g.data_ptr(), 4, 1.0, 1, go.data_ptr(), go.data_ptr(), ws.data_ptr(),
+                              ws.numel(), None)
+    assert rc == -3 and b"not bound" in E.lib.nemit_last_error()
