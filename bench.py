@@ -26,6 +26,12 @@ import torch  # noqa: E402
 ALG_BYTES_SAMPLING = (256 * 5 + 96 * 5) * 8 * 8      # prop gathers per ray: 112 640 B
 ALG_BYTES_FIELD = 48 * 16 * 8 * 8                    # main-grid gathers per ray: 49 152 B
 RAY_IO_BYTES = 24 + 12
+# algorithmic table bytes per ray of each kernel
+ALG_BYTES = {"k_sample_levels": ALG_BYTES_SAMPLING, "k_field_forward": ALG_BYTES_FIELD,
+             "k_field_forward_tc": ALG_BYTES_FIELD, "k_field_forward<adjoint_seed>": ALG_BYTES_FIELD,
+             "k_field_backward": 3 * ALG_BYTES_FIELD,      # recompute gathers + d/dx gathers + float2 red.add
+             "k_prop_backward": 2 * ALG_BYTES_SAMPLING, "k_field_jvp": ALG_BYTES_FIELD,
+             "k_finalize_ray_grads": 24 + 24}
 
 
 def make_rays(n, seed, device):
@@ -218,8 +224,7 @@ def main():
             E.train(True)
             E.backward(o, v, gout, chunk_rays=16384)
             if world > 1:
-                for gname in E.grads:
-                    dist.all_reduce(E.grads[gname])
+                E.allreduce_grads()          # the one collective: flat parameter-gradient buffer over NVLink
         return rgb
 
     def barrier():
@@ -235,6 +240,8 @@ def main():
     if rank == 0:
         clocks.start()
     launches0 = E.launch_count()
+    E.profile(True)
+    E.profile_read(reset=True)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     barrier()
     ev[0].record()
@@ -244,6 +251,8 @@ def main():
     barrier()
     ms = ev[0].elapsed_time(ev[1])
     launches = E.launch_count() - launches0
+    prof = E.profile_read(reset=True)
+    E.profile(False)
     clk = clocks.stop() if rank == 0 else None
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
@@ -253,21 +262,43 @@ def main():
     value = n * world / (ms_per_step * 1e-3)
 
     # per-kernel timing for the roofline (forward kernels timed alone on this stream, same inputs)
-    roof = kernel_roofline(E, o, v, n)
+    roof = kernel_roofline(prof, n)
 
-    # e2e: pinned host rays in, host radiance out, through nemit_forward_host
+    # e2e: the same step through the public API with pinned HOST buffers, copies inside the timed region
     oh = o.cpu().pin_memory()
     vh = v.cpu().pin_memory()
     rh = torch.empty(n, 3).pin_memory()
-    E.train(False)
+    h2d, d2h = 24 * n, 12 * n
+    if args.mode == "fwd+bwd":
+        gh = gout.cpu().pin_memory()
+        goh, gvh = torch.empty(3, n).pin_memory(), torch.empty(3, n).pin_memory()
+        od, vd, gd = torch.empty_like(o), torch.empty_like(v), torch.empty_like(gout)
+        h2d, d2h = 36 * n, 36 * n
+
+    def e2e_step():
+        E.train(False)
+        if args.mode == "fwd":
+            E.render_host(oh, vh, rh)
+            return
+        od.copy_(oh, non_blocking=True)
+        vd.copy_(vh, non_blocking=True)
+        gd.copy_(gh, non_blocking=True)
+        rgb = E.render(od, vd)
+        E.train(True)
+        go, gv = E.backward(od, vd, gd, chunk_rays=16384)
+        if world > 1:
+            E.allreduce_grads()
+        rh.copy_(rgb, non_blocking=True)
+        goh.copy_(go, non_blocking=True)
+        gvh.copy_(gv, non_blocking=True)
     for _ in range(2):
-        E.render_host(oh, vh, rh)
+        e2e_step()
     barrier()
     ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     ev2[0].record()
     e2e_steps = max(3, args.steps // 2)
     for _ in range(e2e_steps):
-        E.render_host(oh, vh, rh)
+        e2e_step()
     ev2[1].record()
     barrier()
     t2 = torch.tensor([ev2[0].elapsed_time(ev2[1])], device=dev, dtype=torch.float64)
@@ -280,8 +311,8 @@ def main():
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
                 "clocks": clk, "gpu_launches": int(launches),
-                "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": 24 * n, "d2h_bytes_per_step": 12 * n,
-                        "note": "forward only through nemit_forward_host (pinned host rays in, host radiance out)"},
+                "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "note": "pinned host rays (+grad_out) in, host radiance (+ray grads) out, copies on the compute stream"},
                 "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
             rate, best = cpu_reference_rate(args.ref_rays, 3, args.mode)
@@ -301,33 +332,29 @@ def backward_available():
         return False
 
 
-def kernel_roofline(E, o, v, n):
-    """Times the two forward kernels separately (sample_levels alone; forward = both) with CUDA events."""
+def kernel_roofline(prof, n):
+    """Roofline of the dominant kernel from the library's own CUDA-event records of the timed region
+    (events recorded on the launching stream around every launch; nemit_profile_read)."""
     hbm, src = measured_peaks()
-    E.train(False)
-
-    def timed(fn, reps=5):
-        fn()
-        torch.cuda.synchronize()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(reps):
-            fn()
-        b.record()
-        torch.cuda.synchronize()
-        return a.elapsed_time(b) / reps
-    t_s = timed(lambda: E.sample_levels(o, v, edges_only=True))
-    t_f = timed(lambda: E.render(o, v))
-    t_field = max(t_f - t_s, 1e-6)
-    launches_per_call = max(1, (n + (1 << 18) - 1) >> 18)
-    dom, t_dom, alg = ("k_sample_levels", t_s, ALG_BYTES_SAMPLING) if t_s >= t_field else ("k_field_forward", t_field, ALG_BYTES_FIELD)
-    achieved = alg * n / (t_dom * 1e-3) / 1e9
+    chunk = 1 << 18
+    rays_per_launch = min(n, chunk)
+    kern = {k: {"ms_total": ms, "launches": c, "ms_per_launch": ms / c} for k, (ms, c) in prof.items()}
+    total = sum(v["ms_total"] for v in kern.values()) or 1.0
+    for v in kern.values():
+        v["share"] = v["ms_total"] / total
+    dom = max(kern, key=lambda k: kern[k]["ms_total"])
+    alg = ALG_BYTES[dom]
+    achieved = alg * rays_per_launch / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
     return {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "peak_source": src, "unit": "GB/s",
-            "frac": achieved / hbm, "traffic": None,
-            "algorithmic_bytes_per_ray": alg, "launches_per_step": launches_per_call,
-            "ms_k_sample_levels": t_s, "ms_k_field_forward": t_field,
-            "note": "achieved = algorithmic 8-byte-gather bytes of the dominant kernel / its CUDA-event time; "
-                    "tables (74 MiB) are L2-resident so DRAM traffic is far below this"}
+            "frac": achieved / hbm, "traffic": NCU_TRAFFIC.get(dom),
+            "algorithmic_bytes_per_ray": alg, "rays_per_launch": rays_per_launch, "kernels": kern,
+            "note": "achieved = algorithmic table bytes (8-byte gathers / float2 reductions) per launch / average "
+                    "CUDA-event launch duration in the timed region; tables (74 MiB) are L2-resident so DRAM "
+                    "traffic (ncu, per launch of 65536 rays, profiles/) is far below it"}
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/)
+NCU_TRAFFIC = {"k_sample_levels": 7.9e6, "k_field_forward": 63.9e6}
 
 
 if __name__ == "__main__":

@@ -187,6 +187,22 @@ int nemit_forward_host(NemitHandle* h, const NemitRays* rays_host, float* rgb_ho
 /* number of kernels the library has launched on this handle since creation (bench evidence) */
 int64_t nemit_launch_count(const NemitHandle* h);
 
+/* Optional per-kernel timing: CUDA events recorded around every kernel launch ON THE LAUNCHING STREAM
+ * (the reference's counterpart is the @profiler.time_function wall clock, NS/utils/profiler.py:68-131).
+ * nemit_profile_read synchronises the pending events and returns accumulated milliseconds and launch
+ * counts per kernel kind (arrays of NEMIT_PROFILE_KINDS). */
+#define NEMIT_K_SAMPLE 0      /* k_sample_levels */
+#define NEMIT_K_FIELD_FWD 1   /* k_field_forward (fp32) */
+#define NEMIT_K_FIELD_SEED 2  /* k_field_forward<adjoint seed> */
+#define NEMIT_K_FIELD_BWD 3   /* k_field_backward */
+#define NEMIT_K_PROP_BWD 4    /* k_prop_backward */
+#define NEMIT_K_FINALIZE 5    /* k_finalize_ray_grads */
+#define NEMIT_K_FIELD_JVP 6   /* k_field_jvp */
+#define NEMIT_K_FIELD_TC 7    /* k_field_forward_tc (tensor-core MLP) */
+#define NEMIT_PROFILE_KINDS 8
+int nemit_profile_enable(NemitHandle* h, int32_t on);
+int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int32_t reset);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,4 +13,7 @@ def __getattr__(name):
     if name == "VmfMixture":
         from .vmf import VmfMixture
         return VmfMixture
+    if name == "VmfGuiding":
+        from .vmf import VmfGuiding
+        return VmfGuiding
     raise AttributeError(name)

@@ -33,7 +33,58 @@ struct NemitHandle {
   bool params_bound, grads_bound;
   NemitParams P, G;
   int64_t launches;
+  // optional per-kernel timing (nemit_profile_*): CUDA events around every launch on the launching stream
+  bool profile;
+  int n_pending;
+  cudaEvent_t ev[2 * 512];
+  int ev_kind[512];
+  double kind_ms[NEMIT_PROFILE_KINDS];
+  int64_t kind_launches[NEMIT_PROFILE_KINDS];
 };
+
+// launch with launch counting and optional event bracketing
+template <class F>
+static cudaError_t timed_launch(NemitHandle* h, int kind, cudaStream_t st, F&& f) {
+  bool rec = h->profile && h->n_pending < 512;
+  int slot = h->n_pending;
+  if (rec) {
+    if (!h->ev[2 * slot]) { cudaEventCreate(&h->ev[2 * slot]); cudaEventCreate(&h->ev[2 * slot + 1]); }
+    cudaEventRecord(h->ev[2 * slot], st);
+  }
+  cudaError_t e = f();
+  if (rec) {
+    cudaEventRecord(h->ev[2 * slot + 1], st);
+    h->ev_kind[slot] = kind;
+    h->n_pending++;
+  }
+  h->launches++;
+  return e;
+}
+
+extern "C" int nemit_profile_enable(NemitHandle* h, int32_t on) {
+  if (!h) return NEMIT_E_INVALID;
+  h->profile = on != 0;
+  return NEMIT_OK;
+}
+extern "C" int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int32_t reset) {
+  if (!h) return NEMIT_E_INVALID;
+  cudaSetDevice(h->device);
+  for (int i = 0; i < h->n_pending; ++i) {
+    cudaEventSynchronize(h->ev[2 * i + 1]);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev[2 * i], h->ev[2 * i + 1]) == cudaSuccess) {
+      h->kind_ms[h->ev_kind[i]] += ms;
+      h->kind_launches[h->ev_kind[i]]++;
+    }
+  }
+  h->n_pending = 0;
+  for (int k = 0; k < NEMIT_PROFILE_KINDS; ++k) {
+    if (ms_per_kind) ms_per_kind[k] = h->kind_ms[k];
+    if (launches_per_kind) launches_per_kind[k] = h->kind_launches[k];
+    if (reset) { h->kind_ms[k] = 0.0; h->kind_launches[k] = 0; }
+  }
+  return NEMIT_OK;
+}
 
 static const int64_t kChunkRays = 1 << 18;
 
@@ -109,6 +160,7 @@ extern "C" int nemit_destroy(NemitHandle* h) {
   if (!h) return NEMIT_OK;
   cudaSetDevice(h->device);
   cudaFree(h->tables_dev);
+  for (int i = 0; i < 2 * 512; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   delete h;
   return NEMIT_OK;
 }
@@ -233,9 +285,8 @@ extern "C" int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const 
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     offset_levels(S, out, off);
-    cudaError_t e = launch_sample_levels(h->M, S, (cudaStream_t)stream);
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
-    h->launches++;
   }
   return NEMIT_OK;
 }
@@ -259,9 +310,8 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
     float* user_t = S.t_edges2;
     S.t_edges2 = t_edges;
-    cudaError_t e = launch_sample_levels(h->M, S, (cudaStream_t)stream);
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
-    h->launches++;
     if (user_t) {
       e = cudaMemcpyAsync(user_t, t_edges, sizeof(float) * n * (kS2 + 1), cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
       if (e != cudaSuccess) return cuda_fail(e, "copy t_edges2");
@@ -274,9 +324,8 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     F.rgb = rgb + off * 3;
     F.accumulation = accumulation ? accumulation + off : nullptr;
     F.weights2 = (levels && levels->weights2) ? levels->weights2 + off * kS2 : nullptr;
-    e = launch_field_forward(h->M, F, (cudaStream_t)stream);
+    e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
-    h->launches++;
   }
   return NEMIT_OK;
 }
@@ -347,9 +396,8 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
-    cudaError_t e = launch_sample_levels(h->M, S, st);
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
-    h->launches++;
     FieldArgs F;
     memset(&F, 0, sizeof(F));
     fill_ray_args(F, rays, off, n);
@@ -357,9 +405,8 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
     F.t_edges2 = S.t_edges2;
     F.d_o = d_o; F.d_v = d_v;
     F.d_rgb = d_rgb + off * 3;
-    e = launch_field_jvp(h->M, F, st);
+    e = timed_launch(h, NEMIT_K_FIELD_JVP, st, [&] { return launch_field_jvp(h->M, F, st); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_jvp");
-    h->launches++;
   }
   return NEMIT_OK;
 }
@@ -392,8 +439,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     fill_sample_args(h, S, rays, off, n);
     S.t_edges2 = t_edges;
     S.s_edges2 = s_edges;
-    if ((e = launch_sample_levels(h->M, S, st)) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
-    h->launches++;
+    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     // pass 1: forward of the 48-sample stage + composite adjoint
     FieldArgs F;
     memset(&F, 0, sizeof(F));
@@ -401,8 +447,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
     F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
-    if ((e = launch_field_adjoint_seed(h->M, F, st)) != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
-    h->launches++;
+    if ((e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(h->M, F, st); })) != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
     // pass 2: MLP / hash-grid backward
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
     FieldBwdArgs B;
@@ -414,8 +459,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     B.G.head_w0 = h->G.head_w0; B.G.head_b0 = h->G.head_b0; B.G.head_w1 = h->G.head_w1; B.G.head_b1 = h->G.head_b1;
     B.G.head_w2 = h->G.head_w2; B.G.head_b2 = h->G.head_b2; B.G.appearance = h->G.appearance;
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = loss_scale;
-    if ((e = launch_field_backward(h->M, B, st)) != cudaSuccess) return cuda_fail(e, "k_field_backward");
-    h->launches++;
+    if ((e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); })) != cudaSuccess) return cuda_fail(e, "k_field_backward");
     // pass 3: interlevel loss -> proposal networks (only when the sampler says they carry autograd)
     if (proposal_requires_grad && h->M.interlevel_mult != 0.f) {
       PropBwdArgs Q;
@@ -427,15 +471,13 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
         Q.g_w1[i] = h->G.prop_w1[i]; Q.g_b1[i] = h->G.prop_b1[i];
       }
       Q.weights2 = weights2; Q.s_edges2_in = s_edges; Q.reg_chunk = chunk_rays; Q.loss_scale = loss_scale;
-      if ((e = launch_prop_backward(h->M, Q, st)) != cudaSuccess) return cuda_fail(e, "k_prop_backward");
-      h->launches++;
+      if ((e = timed_launch(h, NEMIT_K_PROP_BWD, st, [&] { return launch_prop_backward(h->M, Q, st); })) != cudaSuccess) return cuda_fail(e, "k_prop_backward");
     }
     FinalizeArgs Z;
     memset(&Z, 0, sizeof(Z));
     fill_ray_args(Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = grad_o; Z.grad_v = grad_v;
-    if ((e = launch_finalize_ray_grads(h->M, Z, st)) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
-    h->launches++;
+    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(h->M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
   return NEMIT_OK;
 }

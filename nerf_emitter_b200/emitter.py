@@ -124,15 +124,35 @@ class NerfEmitter:
     def bind_grads(self, grads: Optional[Dict[str, torch.Tensor]] = None):
         """Bind gradient accumulators (``param.grad`` tensors). Created zero-filled if not given."""
         if grads is None:
-            grads = {k: torch.zeros_like(v) for k, v in self.params.items()}
+            # one flat fp32 buffer, every gradient tensor a view into it: the multi-GPU all-reduce is one call
+            sizes = [(k, v.numel()) for k, v in self.params.items()]
+            self.flat_grads = torch.zeros(sum((n + 63) // 64 * 64 for _, n in sizes), device=self.device)
+            grads, off = {}, 0
+            for k, n in sizes:
+                grads[k] = self.flat_grads[off:off + n].view_as(self.params[k])
+                off += (n + 63) // 64 * 64
+        else:
+            self.flat_grads = None
         self.grads = grads
         self._G = self._pack(self.grads)
         L.check(self.lib.nemit_bind_grads(self._h, C.byref(self._G)), "nemit_bind_grads")
         return grads
 
     def zero_grads(self):
+        if getattr(self, "flat_grads", None) is not None:
+            self.flat_grads.zero_()
+            return
         for g in self.grads.values():
             g.zero_()
+
+    def allreduce_grads(self, group=None, scale=None):
+        """The one collective of the path: sum parameter gradients over the ray-sharded ranks."""
+        from . import parallel
+        if getattr(self, "flat_grads", None) is not None:
+            parallel.allreduce_grads(self.flat_grads, group, scale)
+        else:
+            for g in self.grads.values():
+                parallel.allreduce_grads(g, group, scale)
 
     def train(self, mode: bool = True):
         self.training = bool(mode)
@@ -285,6 +305,17 @@ class NerfEmitter:
         out = torch.empty(n, g.num_levels * g.features_per_level, device=self.device, dtype=torch.float32)
         L.check(self.lib.nemit_hash_encode(self._h, which, _ptr(x), n, _ptr(out), self._stream()), "nemit_hash_encode")
         return out
+
+    def profile(self, on: bool = True):
+        """Per-kernel CUDA-event timing inside the library (on the launching stream)."""
+        L.check(self.lib.nemit_profile_enable(self._h, int(on)), "nemit_profile_enable")
+
+    def profile_read(self, reset: bool = True):
+        """{kernel: (total ms, launches)} accumulated since the last reset."""
+        ms = (C.c_double * len(L.PROFILE_KINDS))()
+        cnt = (C.c_int64 * len(L.PROFILE_KINDS))()
+        L.check(self.lib.nemit_profile_read(self._h, ms, cnt, int(reset)), "nemit_profile_read")
+        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(L.PROFILE_KINDS) if cnt[i]}
 
     def launch_count(self) -> int:
         return int(self.lib.nemit_launch_count(self._h))

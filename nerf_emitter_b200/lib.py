@@ -83,7 +83,12 @@ SYMBOLS = {
                                 C.c_void_p]),
     "nemit_forward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_launch_count": (C.c_int64, [_H]),
+    "nemit_profile_enable": (C.c_int, [_H, C.c_int32]),
+    "nemit_profile_read": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),
 }
+
+PROFILE_KINDS = ["k_sample_levels", "k_field_forward", "k_field_forward<adjoint_seed>", "k_field_backward",
+                 "k_prop_backward", "k_finalize_ray_grads", "k_field_jvp", "k_field_forward_tc"]
 
 _LIB = None
 

@@ -46,3 +46,52 @@ class VmfMixture:
         L.check(self.lib.nemit_vmf_pdf(C.byref(self._lobes), p.data_ptr(), d.data_ptr(), n, pdf.data_ptr(),
                                        self._stream()), "nemit_vmf_pdf")
         return pdf
+
+
+N_CLUSTER = 64     # NS/path_guiding/vmf_guiding.py:18
+
+
+class VmfGuiding:
+    """Host mirror of ``VonMisesFisherGuiding`` (NS/path_guiding/vmf_guiding.py:60-118) and of the ``PathGuiding``
+    hooks (NS/path_guiding/path_guiding.py:20-75) for the lobe tables this path consumes: holds the primal emitter's
+    mixture (and any adjoint emitters'), (de)serialises them under the reference's ``state_dict`` keys
+    ``vmf.{position,weight,std}`` / ``adjoint_emitter_i.*`` and exposes the no-op training hooks the op calls."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.mixtures = {}
+
+    def load_vmf_params(self, name: str, cluster):
+        """load_vmf_params (vmf_guiding.py:52-57): cluster = {position (K,3), weight (K), std (K)}."""
+        self.mixtures[name] = VmfMixture(torch.as_tensor(cluster["position"]).to(self.device).reshape(-1, 3),
+                                         torch.as_tensor(cluster["weight"]).to(self.device).reshape(-1),
+                                         torch.as_tensor(cluster["std"]).to(self.device).reshape(-1))
+        return self.mixtures[name]
+
+    @property
+    def primal(self) -> VmfMixture:
+        return self.mixtures["vmf"]
+
+    def state_dict(self, destination=None, prefix=""):
+        destination = {} if destination is None else destination
+        for name, m in self.mixtures.items():
+            destination[prefix + name + ".position"] = m.position.reshape(-1)      # dr.ravel order: xyzxyz...
+            destination[prefix + name + ".weight"] = m.weight
+            destination[prefix + name + ".std"] = m.std
+        return destination
+
+    def load_pipeline(self, loaded_state, step: int = 0):
+        names = sorted({k.rsplit(".", 1)[0] for k in loaded_state if k.endswith(".position")
+                        and (k.startswith("vmf") or k.startswith("adjoint_emitter_"))})
+        for name in names:
+            self.load_vmf_params(name, {key: loaded_state.pop(name + "." + key) for key in ("position", "weight", "std")})
+
+    # PathGuiding's hooks called from the op (nerf_emitter_op.py:57,88,117): no-ops for the vMF guiding
+    def train_primal(self, *a):
+        pass
+
+    def train_forward(self, *a):
+        pass
+
+    def train_backward(self, *a):
+        pass
