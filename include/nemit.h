@@ -127,6 +127,15 @@ int nemit_destroy(NemitHandle* h);
 int nemit_bind_params(NemitHandle* h, const NemitParams* p);
 int nemit_bind_grads(NemitHandle* h, const NemitParams* g);
 
+/* MLP arithmetic of the main field: NEMIT_PRECISION_FP32 = exact fp32 FMA path (parity mode, <=1e-3 vs the
+ * reference's fp32 torch path); NEMIT_PRECISION_FP16_TC = fp16 operands on the tcgen05 tensor cores with fp32
+ * accumulation - the reference's own mixed-precision mode (torch.autocast, NS/models/base_model.py:305;
+ * tiny-cuda-nn FullyFusedMLP is fp16, NS/field_components/mlp.py:117-144).  Hash tables, density / colour
+ * activations, weights and compositing are fp32 in both.  Default: FP32. */
+#define NEMIT_PRECISION_FP32 0
+#define NEMIT_PRECISION_FP16_TC 1
+int nemit_set_precision(NemitHandle* h, int32_t precision);
+
 /* bytes of scratch the calls below need for a batch of n rays (chunked internally) */
 size_t nemit_workspace_bytes(const NemitHandle* h, int64_t n);
 

@@ -33,6 +33,7 @@ struct NemitHandle {
   bool params_bound, grads_bound;
   NemitParams P, G;
   int64_t launches;
+  int precision;
   // optional per-kernel timing (nemit_profile_*): CUDA events around every launch on the launching stream
   bool profile;
   int n_pending;
@@ -187,6 +188,13 @@ extern "C" int nemit_bind_grads(NemitHandle* h, const NemitParams* g) {
   return NEMIT_OK;
 }
 extern "C" int64_t nemit_launch_count(const NemitHandle* h) { return h ? h->launches : 0; }
+extern "C" int nemit_set_precision(NemitHandle* h, int32_t precision) {
+  if (!h) return fail(NEMIT_E_INVALID, "nemit_set_precision: null handle%s");
+  if (precision != NEMIT_PRECISION_FP32 && precision != NEMIT_PRECISION_FP16_TC)
+    return fail(NEMIT_E_INVALID, "nemit_set_precision: unknown precision%s");
+  h->precision = precision;
+  return NEMIT_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // workspace
@@ -324,7 +332,10 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     F.rgb = rgb + off * 3;
     F.accumulation = accumulation ? accumulation + off : nullptr;
     F.weights2 = (levels && levels->weights2) ? levels->weights2 + off * kS2 : nullptr;
-    e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
+    if (h->precision == NEMIT_PRECISION_FP16_TC)
+      e = timed_launch(h, NEMIT_K_FIELD_TC, (cudaStream_t)stream, [&] { return launch_field_forward_tc(h->M, F, (cudaStream_t)stream); });
+    else
+      e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
   }
   return NEMIT_OK;

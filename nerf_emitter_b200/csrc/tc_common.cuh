@@ -1,0 +1,137 @@
+// tc_common.cuh - sm_100a tensor-core plumbing for the fused MLP kernels: tcgen05.mma (UMMA) issue, TMEM
+// allocation / loads, mbarrier waits and the shared-memory matrix descriptors, written as inline PTX.
+//
+// Operand layout used everywhere here: K-major, no swizzle ("interleave") canonical UMMA layout of fp16
+// elements.  A core matrix is 8 rows x 16 bytes (8 halves along K), stored as 8 consecutive 16-byte rows.
+// Element (row r, k) of an R x K operand lives at byte
+//      (k / 8) * LBO + (r / 8) * SBO + (r % 8) * 16 + (k % 8) * 2
+// with SBO = 128 (row groups contiguous) and LBO = R * 16 (one K-chunk of all rows after the other).
+// One tcgen05.mma of kind::f16 consumes K = 16, i.e. two K-chunks; k-step j starts at byte 2 * j * LBO.
+// The accumulator D (M = 128 rows, N fp32 columns) sits in TMEM: row m = lane m, column n = column n.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace nemit {
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- mbarrier ------------------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// bounded spin: a lost tensor-core completion traps (launch error) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t it = 0; it < (1u << 24); ++it)
+    if (mbar_try_wait(bar, parity)) return;
+  __trap();
+}
+
+// generic-proxy shared-memory writes -> visible to the async proxy (tcgen05.mma operand reads)
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// ---- TMEM ----------------------------------------------------------------------------------------
+// one full warp allocates NCOLS (power of two >= 32) columns; the base address lands in *slot (shared memory)
+template <int NCOLS>
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "n"(NCOLS)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+template <int NCOLS>
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(NCOLS) : "memory");
+}
+
+// 32 lanes x 32-bit, 16 consecutive columns: thread t of the warp gets lane (warp % 4) * 32 + t
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- descriptors ---------------------------------------------------------------------------------
+// shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor bit layout):
+// [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4, [46,48) version = 1, [61,64) layout type = 0
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// instruction descriptor, kind::f16, fp16 A/B (K-major), fp32 accumulate (cute::UMMA::InstrDescriptor):
+// [4,6) c_format = 1 (F32), [7,10) a_format = 0 (F16), [10,13) b_format = 0, bit 15/16 majors = 0 (K),
+// [17,23) N >> 3, [24,29) M >> 4
+__host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
+__device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on an mbarrier when all previously issued tcgen05.mma of this thread have completed
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+// One GEMM of the MLP chain: D[128 x N] = A[128 x K] * B[N x K]^T, fp16 operands in the layout above
+// (A: LBO = 128*16, B: LBO = N*16), issued by the calling thread; completion arrives on `bar`.
+template <int N, int K>
+__device__ __forceinline__ void issue_layer(uint32_t d_tmem, const void* a_smem, const void* b_smem, uint64_t* bar) {
+  constexpr uint32_t kALbo = 128 * 16, kBLbo = N * 16;
+  const uint32_t a0 = smem_u32(a_smem), b0 = smem_u32(b_smem);
+#pragma unroll
+  for (int j = 0; j < K / 16; ++j) {
+    mma_f16_ss(d_tmem, smem_desc(a0 + 2 * j * kALbo, kALbo, 128), smem_desc(b0 + 2 * j * kBLbo, kBLbo, 128),
+               idesc_f16(128, N), j > 0 ? 1u : 0u);
+  }
+  mma_commit(bar);
+}
+
+// byte offset of the 16-byte chunk (row r, K-chunk kc) of an operand with R rows
+template <int R>
+__device__ __forceinline__ uint32_t chunk_off(int r, int kc) { return (uint32_t)(kc * R * 16 + r * 16); }
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+}  // namespace tc
+}  // namespace nemit

@@ -154,6 +154,13 @@ class NerfEmitter:
             for g in self.grads.values():
                 parallel.allreduce_grads(g, group, scale)
 
+    def set_precision(self, precision: str = "fp32"):
+        """'fp32' = exact FMA path (parity mode); 'fp16' = fp16-operand tensor-core MLP (tcgen05, fp32 accumulate)."""
+        code = {"fp32": 0, "fp16": 1}[precision]
+        L.check(self.lib.nemit_set_precision(self._h, code), "nemit_set_precision")
+        self.precision = precision
+        return self
+
     def train(self, mode: bool = True):
         self.training = bool(mode)
         return self

@@ -67,6 +67,7 @@ SYMBOLS = {
     "nemit_destroy": (C.c_int, [_H]),
     "nemit_bind_params": (C.c_int, [_H, C.POINTER(NemitParams)]),
     "nemit_bind_grads": (C.c_int, [_H, C.POINTER(NemitParams)]),
+    "nemit_set_precision": (C.c_int, [_H, C.c_int32]),
     "nemit_workspace_bytes": (C.c_size_t, [_H, C.c_int64]),
     "nemit_forward": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.POINTER(NemitLevelsOut),
                                 C.c_void_p, C.c_size_t, C.c_void_p]),
