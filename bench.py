@@ -98,7 +98,7 @@ def measured_peaks():
     return 6650.0, "fallback"
 
 
-def cpu_reference_rate(n_rays, repeats, mode="fwd"):
+def cpu_reference_rate(n_rays, repeats, mode="fwd", proposal_grad=False):
     """The reference's torch-CPU algorithm (oracle port) on the host cores: rays/s on a bounded sample."""
     from nerf_emitter_b200 import EmitterModelSpec, make_params
     from oracle.nerfacto_oracle import OracleEmitter
@@ -114,7 +114,7 @@ def cpu_reference_rate(n_rays, repeats, mode="fwd"):
         O.render(o, v)
         if mode == "fwd+bwd":
             O.train(True)
-            O.vjp(o, v, g)
+            O.vjp(o, v, g, proposal_requires_grad=proposal_grad)
     one()
     best = 1e30
     for _ in range(repeats):
@@ -142,7 +142,7 @@ def run_reference_arm(args, rank, world):
         O.render(o, v)
         if args.mode == "fwd+bwd":
             O.train(True)
-            O.vjp(o, v, g)
+            O.vjp(o, v, g, proposal_requires_grad=args.proposal_grad)
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
@@ -167,7 +167,10 @@ METRIC = {"fwd": "NeRF-emitter rays/sec fwd (nerfacto 256/96/48 samples)",
 def workload_config(args, rays_per_gpu):
     return {"workload": "nerfacto emitter query, %d deterministic rays per GPU, 256/96/48 samples, random-init stress "
                         "weights (hash tables U(-1,1)), eval-mode forward%s" % (
-                            rays_per_gpu, " + training-mode backward (param + ray grads, interlevel+distortion)"
+                            rays_per_gpu, (" + training-mode backward (field-param + ray grads, distortion loss, t^2 "
+                                           "gradient scaling; proposal networks %s)" % (
+                                               "also get the interlevel-loss gradient" if args.proposal_grad else
+                                               "carry no autograd on this call, as in the reference's steady state"))
                             if args.mode == "fwd+bwd" else ""),
             "mode": args.mode, "rays_per_gpu": rays_per_gpu, "mlp_precision": args.precision,
             "l2_policy": "inputs+tables (%.0f MiB/step touched) exceed L2; no explicit flush" % (
@@ -184,7 +187,11 @@ def main():
     ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU per step")
     ap.add_argument("--ref-rays", type=int, default=4096, help="rays per step of the CPU reference arm")
     ap.add_argument("--mode", default=None, choices=["fwd", "fwd+bwd"])
-    ap.add_argument("--precision", default="fp32")
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"],
+                    help="MLP arithmetic of the main field: fp16 tensor-core (BASELINE configs[1]) or exact fp32")
+    ap.add_argument("--proposal-grad", action="store_true",
+                    help="also back-propagate the interlevel loss into the proposal networks (the reference's sampler "
+                         "only lets them carry autograd on its first call after an update step, SURVEY 8a quirk 13)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -210,6 +217,7 @@ def main():
     spec = EmitterModelSpec()
     P = make_params(spec, seed=0, table_scale=1e3)
     E = NerfEmitter(P, spec, device=dev)
+    E.set_precision(args.precision)
     n = args.rays
     o, v = make_rays(n, 1 + rank, dev)
     gout = torch.randn(n, 3, device=dev)
@@ -222,7 +230,7 @@ def main():
         rgb = E.render(o, v)
         if args.mode == "fwd+bwd":
             E.train(True)
-            E.backward(o, v, gout, chunk_rays=16384)
+            E.backward(o, v, gout, chunk_rays=16384, proposal_requires_grad=args.proposal_grad)
             if world > 1:
                 E.allreduce_grads()          # the one collective: flat parameter-gradient buffer over NVLink
         return rgb
@@ -285,7 +293,7 @@ def main():
         gd.copy_(gh, non_blocking=True)
         rgb = E.render(od, vd)
         E.train(True)
-        go, gv = E.backward(od, vd, gd, chunk_rays=16384)
+        go, gv = E.backward(od, vd, gd, chunk_rays=16384, proposal_requires_grad=args.proposal_grad)
         if world > 1:
             E.allreduce_grads()
         rh.copy_(rgb, non_blocking=True)
@@ -309,13 +317,14 @@ def main():
     if rank == 0:
         line = {"metric": METRIC[args.mode], "value": value, "unit": "rays/s", "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, n),
+                "vs_baseline": None, "dtype": "f16" if args.precision == "fp16" else "f32", "data": "synthetic",
+                "config": workload_config(args, n),
                 "clocks": clk, "gpu_launches": int(launches),
                 "e2e": {"value": e2e_val, "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "note": "pinned host rays (+grad_out) in, host radiance (+ray grads) out, copies on the compute stream"},
                 "roofline": roof}
         if world == 1 and not args.no_cpu_baseline:
-            rate, best = cpu_reference_rate(args.ref_rays, 3, args.mode)
+            rate, best = cpu_reference_rate(args.ref_rays, 3, args.mode, args.proposal_grad)
             line["cpu_baseline"] = {"value": rate, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
                                     "sample": "%d rays of the same workload, best of 3 (%.2f s each), oracle/nerfacto_oracle.py "
                                               "torch CPU fp32" % (args.ref_rays, best)}

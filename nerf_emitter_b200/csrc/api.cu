@@ -458,7 +458,11 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
     F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
-    if ((e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(h->M, F, st); })) != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
+    if (h->precision == NEMIT_PRECISION_FP16_TC)
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
+    else
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(h->M, F, st); });
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
     // pass 2: MLP / hash-grid backward
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
     FieldBwdArgs B;

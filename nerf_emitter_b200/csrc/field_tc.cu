@@ -34,6 +34,7 @@ struct TcSmem {
   float ray_o[kRaysPerGroup * 3];
   float ray_d[kRaysPerGroup * 3];
   float app_tmp[kApp];
+  float s_edge[kRaysPerGroup * (kS2 + 1)];   // adjoint-seed mode only
   alignas(8) uint64_t mbar;
   uint32_t tmem_slot;
 };
@@ -87,6 +88,8 @@ __device__ __forceinline__ void run_layer(TcSmem* sm, const uint8_t* b, uint32_t
   tc::tc_fence_after();
 }
 
+// MODE 0: forward.  MODE 1: first pass of the backward (same forward, then the per-ray composite adjoint).
+template <int MODE>
 __global__ void __launch_bounds__(128)
 k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -146,6 +149,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
     for (int i = tid; i < kRaysPerGroup * (kS2 + 1); i += 128) {
       int rr = i / (kS2 + 1);
       sm->t_edge[i] = rr < rays_here ? A.t_edges2[r0 * (kS2 + 1) + i] : 0.f;
+      if (MODE == 1) sm->s_edge[i] = rr < rays_here ? A.s_edges2[r0 * (kS2 + 1) + i] : 0.f;
     }
     __syncthreads();
 
@@ -229,6 +233,11 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 
     // composite: warp w handles rays w and w+4; lane handles samples lane and lane+32 (fp32, as field.cu)
     for (int rr = wid; rr < rays_here; rr += 4) {
+      if (MODE == 1) {
+        composite_adjoint_ray(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)], &sm->sigma[rr * kS2],
+                              &sm->rgb[rr * kS2 * 3], r0 + rr, lane);
+        continue;
+      }
       float ds[2], w[2];
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
@@ -271,19 +280,26 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   if (wid == 0) tc::tmem_dealloc<64>(tmem);
 }
 
-cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+template <int MODE>
+static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static bool attr_set = false;
   size_t smem = sizeof(TcSmem) + 128;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   int64_t ctas = groups < 148 * 4 ? groups : 148 * 4;     // persistent: 4 CTAs per SM share the tensor core
-  k_field_forward_tc<<<(unsigned)ctas, 128, smem, stream>>>(M, A);
+  k_field_forward_tc<MODE><<<(unsigned)ctas, 128, smem, stream>>>(M, A);
   return cudaGetLastError();
+}
+cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+  return launch_tc_mode<0>(M, A, stream);
+}
+cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
+  return launch_tc_mode<1>(M, A, stream);
 }
 
 }  // namespace nemit

@@ -105,6 +105,7 @@ struct FinalizeArgs : RayArgs {
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
+cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_adjoint_seed(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_jvp(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_backward(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
