@@ -30,6 +30,7 @@ RAY_IO_BYTES = 24 + 12
 ALG_BYTES = {"k_sample_levels": ALG_BYTES_SAMPLING, "k_field_forward": ALG_BYTES_FIELD,
              "k_field_forward_tc": ALG_BYTES_FIELD, "k_field_forward<adjoint_seed>": ALG_BYTES_FIELD,
              "k_field_backward": 3 * ALG_BYTES_FIELD,      # recompute gathers + d/dx gathers + float2 red.add
+             "k_field_backward_tc": 2 * ALG_BYTES_FIELD,   # recompute gathers (Jacobian kept on chip) + float2 red.add
              "k_prop_backward": 2 * ALG_BYTES_SAMPLING, "k_field_jvp": ALG_BYTES_FIELD,
              "k_finalize_ray_grads": 24 + 24}
 

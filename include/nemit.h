@@ -208,7 +208,8 @@ int64_t nemit_launch_count(const NemitHandle* h);
 #define NEMIT_K_FINALIZE 5    /* k_finalize_ray_grads */
 #define NEMIT_K_FIELD_JVP 6   /* k_field_jvp */
 #define NEMIT_K_FIELD_TC 7    /* k_field_forward_tc (tensor-core MLP) */
-#define NEMIT_PROFILE_KINDS 8
+#define NEMIT_K_FIELD_BWD_TC 8 /* k_field_backward_tc (tensor-core dgrad / wgrad) */
+#define NEMIT_PROFILE_KINDS 9
 int nemit_profile_enable(NemitHandle* h, int32_t on);
 int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int32_t reset);
 

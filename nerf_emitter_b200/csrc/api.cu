@@ -203,7 +203,7 @@ static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
   size_t t_edges2, s_edges2, host_stage, bwd, total;
-  size_t g_sigma, g_rgbs, weights2, ray_grad;   // inside the backward block
+  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax;   // inside the backward block
 };
 static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   size_t off = base;
@@ -215,6 +215,8 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   off += align_up(sizeof(float) * (size_t)c * kS2);
   if (L) L->ray_grad = off;
   off += align_up(sizeof(float) * (size_t)c * 6);
+  if (L) L->g_absmax = off;
+  off += align_up(sizeof(float));
   return off - base;
 }
 static WsLayout ws_layout(int64_t n) {
@@ -458,6 +460,11 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
     F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
+    float* g_absmax = reinterpret_cast<float*>(ws + L.g_absmax);
+    if (h->precision == NEMIT_PRECISION_FP16_TC) {
+      if ((e = cudaMemsetAsync(g_absmax, 0, sizeof(float), st)) != cudaSuccess) return cuda_fail(e, "memset g_absmax");
+      F.g_absmax = g_absmax;
+    }
     if (h->precision == NEMIT_PRECISION_FP16_TC)
       e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
     else
@@ -474,7 +481,13 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     B.G.head_w0 = h->G.head_w0; B.G.head_b0 = h->G.head_b0; B.G.head_w1 = h->G.head_w1; B.G.head_b1 = h->G.head_b1;
     B.G.head_w2 = h->G.head_w2; B.G.head_b2 = h->G.head_b2; B.G.appearance = h->G.appearance;
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = loss_scale;
-    if ((e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); })) != cudaSuccess) return cuda_fail(e, "k_field_backward");
+    if (h->precision == NEMIT_PRECISION_FP16_TC) {
+      B.g_absmax = g_absmax;
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(h->M, B, st); });
+    } else {
+      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); });
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_backward");
     // pass 3: interlevel loss -> proposal networks (only when the sampler says they carry autograd)
     if (proposal_requires_grad && h->M.interlevel_mult != 0.f) {
       PropBwdArgs Q;

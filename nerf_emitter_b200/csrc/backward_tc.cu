@@ -1,0 +1,522 @@
+// backward_tc.cu - k_field_backward_tc: reverse mode of the main field (48 final samples per ray) with every
+// dense contraction on the 5th-generation tensor cores (tcgen05.mma, fp16 operands, fp32 accumulation in TMEM).
+//
+// One CTA = 256 threads = two independent halves of 128 threads; a half owns one 128-sample tile at a time
+// (thread t = sample row t) and the two halves share the staged weights, so that one half's gather / scatter
+// phase (LSU bound) overlaps the other half's MMA / epilogue phases.  Per tile:
+//   gather   : 16-level hash encoding of the row (fp16 A operand E) + its Jacobian d enc / d p (fp16, 96 values)
+//   forward  : E W_b0^T -> H1 -> [raw | geo] ; [SH16 | geo15 | 1] W_h0^T -> H2 -> H3 -> rgb pre-activation
+//              (the activations stay in shared memory; ReLU masks stay in registers)
+//   backward : for every layer, in ONE commit group,
+//                 dgrad  G_in [128 x K]  = G_out [128 x N] W        (A = G_out K-major, B = the FORWARD weight
+//                                                                    buffer read MN-major: no transposed copy)
+//                 wgrad  dW  [N x K]    += G_out^T X                (A = G_out buffer read MN-major, M = 64,
+//                                                                    B = activation buffer read MN-major, K = 128
+//                                                                    samples; accumulator lives in TMEM for the
+//                                                                    whole kernel)
+//                 bias   db  [N]        += G_out^T 1                (B = a constant ones operand; the head input
+//                                                                    carries a ones column instead)
+//   scatter  : d enc (TMEM) -> float2 red.add on the gradient table, d enc . Jacobian -> d/d(position) -> per-ray sums
+// Gradient operands are fp16 as in the reference's autocast path (torch.cuda.amp, NS/pipelines/mitsuba_sdf.py:
+// 1177,1193): the seed pass records max |seed| of the launch, the seeds are multiplied by the power of two that
+// brings that maximum to 16, and every result is divided by it again (exact), so the fp16 range is used without
+// an externally tuned loss scale.
+//
+// Reference: SdfNerfactoModel.get_backward_outputs (NS/models/sdf_nerfacto.py:115-168),
+// MitsubaSdfPipeline.backward_for_camera_ray_bundle (NS/pipelines/mitsuba_sdf.py:1144-1219),
+// NerfactoField.get_density / get_outputs (NS/fields/nerfacto_field.py:228-334), _TruncExp.backward
+// (NS/field_components/activations.py:44-48).
+#include "kernels.h"
+#include "field_common.cuh"
+#include "tc_common.cuh"
+
+namespace nemit {
+namespace {
+
+// TMEM columns of one half (256 per half, 512 per CTA = the whole SM)
+constexpr uint32_t kColD0 = 0;      // 128 x 64 work accumulator (forward layers and dgrads)
+constexpr uint32_t kColH1 = 64;     // d head_w1   [n][k]   64 x 64   (M = 64: row r in lane (r/16)*32 + r%16)
+constexpr uint32_t kColH0 = 128;    // d head_w0   [n][k]   64 x 32   (column 31 = d head_b0_eff)
+constexpr uint32_t kColB0 = 160;    // d base_w0   [n][k]   64 x 32
+constexpr uint32_t kColB1T = 192;   // d base_w1^T [k][n]   64 x 16
+constexpr uint32_t kColH2T = 208;   // d head_w2^T [k][n]   64 x 8
+constexpr uint32_t kColBH1 = 216;   // d head_b1   [n][*]   64 x 8 (8 identical columns)
+constexpr uint32_t kColBB0 = 224;   // d base_b0   [n][*]   64 x 8
+constexpr uint32_t kHalfCols = 256;
+
+struct BwdTcCommon {
+  alignas(128) uint8_t b1[64 * 32 * 2];   // base layer 0   (64 x 32)   forward K-major layout, rows = outputs
+  alignas(128) uint8_t b2[16 * 64 * 2];   // base layer 1   (16 x 64)
+  alignas(128) uint8_t b3[64 * 32 * 2];   // head layer 0   (64 x [SH16 | geo15 | 0])
+  alignas(128) uint8_t b4[64 * 64 * 2];   // head layer 1   (64 x 64)
+  alignas(128) uint8_t b5[16 * 64 * 2];   // head layer 2   (3 rows used of 16)
+  alignas(128) uint8_t ones[8 * 128 * 2]; // MN-major 8 x 128 operand of fp16 ones
+  float bias_b0[64], bias_b1[16], bias_h0[64], bias_h1[64], bias_h2[4];
+  float app[kApp];
+  uint32_t tmem_slot;
+};
+struct BwdTcHalf {
+  alignas(128) uint8_t e[128 * 32 * 2];   // hash encoding
+  alignas(128) uint8_t h1[128 * 64 * 2];  // base hidden         -> its gradient
+  alignas(128) uint8_t in[128 * 32 * 2];  // [SH16 | geo15 | 1]
+  alignas(128) uint8_t h2[128 * 64 * 2];  // head hidden 1       -> its gradient
+  alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
+  alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
+  alignas(16) uint8_t jac[12 * 128 * 16]; // d enc / d offset: chunk c of row t at (c * 128 + t) * 16
+  float db_h2[4], db_b1[16];              // bias gradients that are reduced with shuffles (true scale)
+  float dvec[64];
+  alignas(8) uint64_t mbar;
+};
+struct BwdTcSmem {
+  BwdTcCommon c;
+  BwdTcHalf h[2];
+};
+
+__device__ __forceinline__ void half_sync(int half) {
+  asm volatile("bar.sync %0, 128;" ::"r"(half + 1) : "memory");
+}
+
+// make the half's operand writes visible to the tensor core, let its thread 0 issue one commit group, wait for it
+template <class F>
+__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue) {
+  tc::fence_proxy_async();
+  tc::tc_fence_before();
+  half_sync(half);
+  if (t == 0) {
+    tc::tc_fence_after();
+    issue();
+    tc::mma_commit(&H->mbar);
+  }
+  tc::mbar_wait(&H->mbar, phase);
+  phase ^= 1u;
+  tc::tc_fence_after();
+}
+
+// forward hidden layer: accumulator row + bias, ReLU -> fp16 row (8 K-chunks); returns the ReLU mask
+__device__ __forceinline__ uint64_t epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
+  float v[4][16];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
+  tc::tmem_ld_wait();
+  uint64_t mask = 0;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = hh * 8 + q * 2;
+        const float x0 = v[c][j] + bias[c * 16 + j], x1 = v[c][j + 1] + bias[c * 16 + j + 1];
+        if (x0 > 0.f) mask |= 1ull << (c * 16 + j);
+        if (x1 > 0.f) mask |= 1ull << (c * 16 + j + 1);
+        w[q] = tc::pack_h2(fmaxf(x0, 0.f), fmaxf(x1, 0.f));
+      }
+      *reinterpret_cast<uint4*>(a + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  return mask;
+}
+
+// backward hidden layer: accumulator row x ReLU mask -> fp16 gradient row written over the activation row
+__device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint64_t mask, uint8_t* g, int row) {
+  float v[4][16];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
+  tc::tmem_ld_wait();
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = hh * 8 + q * 2;
+        const float x0 = ((mask >> (c * 16 + j)) & 1ull) ? v[c][j] : 0.f;
+        const float x1 = ((mask >> (c * 16 + j + 1)) & 1ull) ? v[c][j + 1] : 0.f;
+        w[q] = tc::pack_h2_sat(x0, x1);
+      }
+      *reinterpret_cast<uint4*>(g + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(256, 1)
+k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldBwdArgs A) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  BwdTcSmem* sm = reinterpret_cast<BwdTcSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  const int tid = threadIdx.x, half = tid >> 7, t = tid & 127, lane = tid & 31, wq = (tid >> 5) & 3;
+  BwdTcCommon* C = &sm->c;
+  BwdTcHalf* H = &sm->h[half];
+
+  // ---- one-time setup ------------------------------------------------------------------------------
+  tc::stage_weight<64, 32>(C->b1, A.P.base_w0, 64, 32, 32, tid, 256);
+  tc::stage_weight<16, 64>(C->b2, A.P.base_w1, 16, 64, 64, tid, 256);
+  tc::stage_weight<64, 32>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, 256);
+  tc::stage_weight<64, 64>(C->b4, A.P.head_w1, 64, 64, 64, tid, 256);
+  tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, 256);
+  for (int i = tid; i < 8 * 128; i += 256) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
+  for (int i = tid; i < 64; i += 256) { C->bias_b0[i] = A.P.base_b0[i]; C->bias_h1[i] = A.P.head_b1[i]; }
+  for (int i = tid; i < 16; i += 256) C->bias_b1[i] = A.P.base_b1[i];
+  for (int i = tid; i < 4; i += 256) C->bias_h2[i] = i < 3 ? A.P.head_b2[i] : 0.f;
+  for (int i = tid; i < kApp; i += 256) {
+    float e;
+    if (A.training) {
+      e = A.P.appearance[(int64_t)A.camera_idx * kApp + i];
+    } else {
+      float s = 0.f;
+      for (int r = 0; r < M.num_images; ++r) s += A.P.appearance[(int64_t)r * kApp + i];
+      e = s / (float)M.num_images;
+    }
+    C->app[i] = e;
+  }
+  if (t < 4) H->db_h2[t] = 0.f;
+  if (t < 16) H->db_b1[t] = 0.f;
+  if (t == 0) {
+    tc::mbar_init(&H->mbar, 1);
+    tc::fence_mbar_init();
+  }
+  if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
+  __syncthreads();
+  for (int n = tid; n < 64; n += 256) {
+    float b = A.P.head_b0[n];
+    for (int k = 0; k < kApp; ++k) b = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], C->app[k], b);
+    C->bias_h0[n] = b;
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tm = C->tmem_slot + (uint32_t)half * kHalfCols;   // this half's columns, lane 0
+  const uint32_t taddr = tm + ((uint32_t)(wq * 32) << 16);         // this warp's 32 TMEM lanes
+  uint32_t phase = 0;
+
+  // gradient operand scale: power of two that maps the launch's largest seed to 16
+  float S = 1.f, invS = 1.f;
+  {
+    const float gmax = A.g_absmax ? *A.g_absmax : 0.f;
+    if (gmax > 0.f && gmax < 3.0e38f) {
+      int e;
+      frexpf(gmax, &e);                       // gmax = m * 2^e, m in [0.5, 1)
+      e = 4 - e;
+      e = e < -60 ? -60 : (e > 60 ? 60 : e);
+      S = ldexpf(1.f, e);
+      invS = ldexpf(1.f, -e);
+    }
+  }
+  const tc::Operand op_ones{tc::smem_u32(C->ones), 128u, 2048u, 256u};
+
+  const int64_t n_samples = A.n * kS2;
+  const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
+  bool first = true;
+  for (int64_t tile = (int64_t)blockIdx.x * 2 + half; tile < n_tiles; tile += (int64_t)gridDim.x * 2) {
+    const int64_t s = tile * kTileM + t;
+    const bool valid = s < n_samples;
+    const int64_t rr = valid ? s / kS2 : 0;
+    const int si = valid ? (int)(s % kS2) : 0;
+    float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, t0 = 0.f, t1 = 0.f;
+    float seed_rgb[3] = {0.f, 0.f, 0.f}, seed_sigma = 0.f;
+    if (valid) {
+      load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, M.scene_scale, o, d);
+      t0 = A.t_edges2[rr * (kS2 + 1) + si];
+      t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
+      seed_rgb[0] = A.g_rgbs[s * 3 + 0]; seed_rgb[1] = A.g_rgbs[s * 3 + 1]; seed_rgb[2] = A.g_rgbs[s * 3 + 2];
+      seed_sigma = A.g_sigma[s];
+    }
+    const float tsum = add_rn(t0, t1);
+    float x[3], p[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) x[k] = sample_pos(o[k], d[k], tsum);
+    const bool sel = contract_normalise(x, M, p);
+
+    // ---- gather: encoding row and its Jacobian -------------------------------------------------------
+#pragma unroll 1
+    for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
+      LevelCell cell[4];
+      float2 v[4][8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        level_cell(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[j][c] = ldg_f2(A.P.main_table, cell[j].idx[c]);
+      }
+      uint32_t we[4], wj[12];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 r = blend_cell(v[j], cell[j]);
+        we[j] = tc::pack_h2(r.x, r.y);
+        float2 dx, dy, dz;
+        blend_cell_grad(v[j], cell[j], dx, dy, dz);
+        wj[3 * j + 0] = tc::pack_h2_sat(dx.x, dx.y);
+        wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
+        wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
+      }
+      *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, l0 >> 2)) = make_uint4(we[0], we[1], we[2], we[3]);
+      uint4* jp = reinterpret_cast<uint4*>(H->jac) + (l0 >> 2) * 3 * 128 + t;
+      jp[0] = make_uint4(wj[0], wj[1], wj[2], wj[3]);
+      jp[128] = make_uint4(wj[4], wj[5], wj[6], wj[7]);
+      jp[256] = make_uint4(wj[8], wj[9], wj[10], wj[11]);
+    }
+
+    // ---- forward recompute ---------------------------------------------------------------------------
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->e, 128), tc::op_kmajor(C->b1, 64), tc::idesc_f16(128, 64), 2, false);
+    });
+    const uint64_t mask1 = epi_fwd_hidden(taddr + kColD0, C->bias_b0, H->h1, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_kmajor(C->b2, 16), tc::idesc_f16(128, 16), 4, false);
+    });
+    float raw;
+    {
+      float v[16];
+      tc::tmem_ld16(taddr + kColD0, v);
+      tc::tmem_ld_wait();
+      raw = v[0] + C->bias_b1[0];
+      float c[16];
+      sh16((d[0] + 1.f) * 0.5f, (d[1] + 1.f) * 0.5f, (d[2] + 1.f) * 0.5f, c);
+      uint32_t w[4];
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
+        *reinterpret_cast<uint4*>(H->in + tc::chunk_off<128>(t, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      float gfe[16];
+#pragma unroll
+      for (int k = 0; k < 15; ++k) gfe[k] = v[k + 1] + C->bias_b1[k + 1];
+      gfe[15] = 1.f;                                   // ones column: its wgrad column is d head_b0_eff
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
+        *reinterpret_cast<uint4*>(H->in + tc::chunk_off<128>(t, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->in, 128), tc::op_kmajor(C->b3, 64), tc::idesc_f16(128, 64), 2, false);
+    });
+    const uint64_t mask2 = epi_fwd_hidden(taddr + kColD0, C->bias_h0, H->h2, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_kmajor(C->b4, 64), tc::idesc_f16(128, 64), 4, false);
+    });
+    const uint64_t mask3 = epi_fwd_hidden(taddr + kColD0, C->bias_h1, H->h3, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_kmajor(C->b5, 16), tc::idesc_f16(128, 8), 4, false);
+    });
+    {
+      float v[8];
+      tc::tmem_ld8(taddr + kColD0, v);
+      tc::tmem_ld_wait();
+      float gout[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        // SafeExp backward: exp(clamp(x, max=88)) -> gradient exp(x) below the clamp, 0 above
+        const float a = v[j] + C->bias_h2[j] + M.rgb_bias;
+        gout[j] = (a < 88.f) ? seed_rgb[j] * expf(a) : 0.f;
+        const float sum = warp_sum(gout[j]);
+        if (lane == 0) atomicAdd(&H->db_h2[j], sum);
+      }
+      *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 0)) =
+          make_uint4(tc::pack_h2_sat(gout[0] * S, gout[1] * S), tc::pack_h2_sat(gout[2] * S, 0.f), 0u, 0u);
+      *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 1)) = make_uint4(0u, 0u, 0u, 0u);
+    }
+
+    // ---- head MLP backward ---------------------------------------------------------------------------
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+    });
+    epi_bwd_hidden(taddr + kColD0, mask3, H->h3, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
+    });
+    epi_bwd_hidden(taddr + kColD0, mask2, H->h2, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
+    });
+    {
+      float v[16];
+      tc::tmem_ld16(taddr + kColD0, v);
+      tc::tmem_ld_wait();
+      // trunc_exp backward: exp(clamp(raw, -15, 15)); the selector multiplies the density
+      float g16[16];
+      g16[0] = (valid && sel) ? seed_sigma * expf(fminf(fmaxf(raw, -15.f), 15.f)) * S : 0.f;
+#pragma unroll
+      for (int k = 0; k < 15; ++k) g16[k + 1] = v[k];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const float sum = warp_sum(g16[k]);
+        if (lane == 0) atomicAdd(&H->db_b1[k], sum * invS);
+      }
+      uint32_t w[4];
+#pragma unroll
+      for (int hh = 0; hh < 2; ++hh) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2_sat(g16[hh * 8 + q * 2], g16[hh * 8 + q * 2 + 1]);
+        *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+
+    // ---- base MLP backward ---------------------------------------------------------------------------
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+    });
+    epi_bwd_hidden(taddr + kColD0, mask1, H->h1, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
+    });
+
+    // ---- hash grid backward: table scatter-add and d/d(position) ----------------------------------------
+    {
+      float gp[3] = {0.f, 0.f, 0.f};
+      const float gscale = invS * A.loss_scale;
+#pragma unroll 1
+      for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
+        float g[8];
+        tc::tmem_ld8(taddr + kColD0 + 2 * l0, g);
+        tc::tmem_ld_wait();
+        const uint4* jp = reinterpret_cast<const uint4*>(H->jac) + (l0 >> 2) * 3 * 128 + t;
+        const uint4 j0 = jp[0], j1 = jp[128], j2 = jp[256];
+        const uint32_t wj[12] = {j0.x, j0.y, j0.z, j0.w, j1.x, j1.y, j1.z, j1.w, j2.x, j2.y, j2.z, j2.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float gx = g[2 * j], gy = g[2 * j + 1];
+          if (!valid || (gx == 0.f && gy == 0.f)) continue;
+          LevelCell cell;
+          const float sc = M.main_grid.scal[l0 + j];
+          level_cell(p, sc, M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell);
+          float cw[8];
+          corner_weights(cell, cw);
+          const float gxs = gx * gscale, gys = gy * gscale;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+          if (sel) {
+            const float2 dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
+            const float2 dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
+            const float2 dz = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 2]));
+            const float scs = sc * invS;
+            gp[0] = fmaf(scs, gx * dx.x + gy * dx.y, gp[0]);
+            gp[1] = fmaf(scs, gx * dy.x + gy * dy.y, gp[1]);
+            gp[2] = fmaf(scs, gx * dz.x + gy * dz.y, gp[2]);
+          }
+        }
+      }
+      if (valid && sel) {
+        float gx[3];
+        contract_vjp(x, sel, gp, gx);
+        const float tmid = tsum * 0.5f;
+        float* rg = A.ray_grad + rr * 6;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          atomicAdd(rg + k, gx[k]);
+          atomicAdd(rg + 3 + k, gx[k] * tmid);
+        }
+      }
+    }
+    first = false;
+  }
+
+  // ---- flush this half's weight-gradient accumulators (torch layouts, loss scale applied) ---------------
+  if (!first) {
+    tc::tc_fence_before();
+    half_sync(half);
+    tc::tc_fence_after();
+    const bool has = lane < 16;             // M = 64 accumulators: row r lives in lane (r / 16) * 32 + r % 16
+    const int r = wq * 16 + (lane & 15);
+    const float fs = A.loss_scale * invS;
+    float v[16];
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      tc::tmem_ld16(taddr + kColH1 + c * 16, v);
+      tc::tmem_ld_wait();
+      if (has)
+        for (int i = 0; i < 16; ++i) atomicAdd(A.G.head_w1 + r * kHidden + c * 16 + i, fs * v[i]);
+    }
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      tc::tmem_ld16(taddr + kColH0 + c * 16, v);
+      tc::tmem_ld_wait();
+      if (has) {
+        for (int i = 0; i < 16; ++i) {
+          const int k = c * 16 + i;
+          if (k < kHeadK) {
+            atomicAdd(A.G.head_w0 + r * kHeadIn + k, fs * v[i]);
+          } else {
+            // ones column = d head_b0_eff; the appearance columns are rank-1 with it (same 32-vector every sample)
+            const float db = fs * v[i];
+            H->dvec[r] = db;
+            atomicAdd(A.G.head_b0 + r, db);
+            for (int j = 0; j < kApp; ++j) atomicAdd(A.G.head_w0 + r * kHeadIn + kHeadK + j, db * C->app[j]);
+          }
+        }
+      }
+    }
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      tc::tmem_ld16(taddr + kColB0 + c * 16, v);
+      tc::tmem_ld_wait();
+      if (has)
+        for (int i = 0; i < 16; ++i) atomicAdd(A.G.base_w0 + r * kMainEnc + c * 16 + i, fs * v[i]);
+    }
+    tc::tmem_ld16(taddr + kColB1T, v);
+    tc::tmem_ld_wait();
+    if (has)
+      for (int n = 0; n < 16; ++n) atomicAdd(A.G.base_w1 + n * kHidden + r, fs * v[n]);
+    {
+      float u[8];
+      tc::tmem_ld8(taddr + kColH2T, u);
+      tc::tmem_ld_wait();
+      if (has)
+        for (int n = 0; n < 3; ++n) atomicAdd(A.G.head_w2 + n * kHidden + r, fs * u[n]);
+      tc::tmem_ld8(taddr + kColBH1, u);
+      tc::tmem_ld_wait();
+      if (has) atomicAdd(A.G.head_b1 + r, fs * u[0]);
+      tc::tmem_ld8(taddr + kColBB0, u);
+      tc::tmem_ld_wait();
+      if (has) atomicAdd(A.G.base_b0 + r, fs * u[0]);
+    }
+    half_sync(half);
+    if (t < 3) atomicAdd(A.G.head_b2 + t, A.loss_scale * H->db_h2[t]);
+    if (t < 16) atomicAdd(A.G.base_b1 + t, A.loss_scale * H->db_b1[t]);
+    // appearance embedding (NS/fields/nerfacto_field.py:272-285): the camera's row in training mode, the mean of
+    // all rows in eval mode
+    if (t < kApp) {
+      float g = 0.f;
+      for (int n = 0; n < kHidden; ++n) g = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + t], H->dvec[n], g);
+      if (A.training) {
+        atomicAdd(A.G.appearance + (int64_t)A.camera_idx * kApp + t, g);
+      } else {
+        for (int q = 0; q < M.num_images; ++q) atomicAdd(A.G.appearance + (int64_t)q * kApp + t, g / (float)M.num_images);
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (tid < 32) tc::tmem_dealloc<512>(C->tmem_slot);
+}
+
+cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
+  if (A.n <= 0) return cudaSuccess;
+  static bool attr_set = false;
+  const size_t smem = sizeof(BwdTcSmem) + 128;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(k_field_backward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  const int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
+  const int64_t pairs = (tiles + 1) / 2;
+  const int64_t ctas = pairs < 148 ? pairs : 148;      // persistent: one CTA (two halves, all of TMEM) per SM
+  k_field_backward_tc<<<(unsigned)ctas, 256, smem, stream>>>(M, A);
+  return cudaGetLastError();
+}
+
+}  // namespace nemit

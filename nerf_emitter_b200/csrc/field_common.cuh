@@ -161,18 +161,22 @@ __device__ __forceinline__ void load_field_weights(FieldWeightsSmem* S, const Fi
 // t_edge / s_edge: the ray's 49 euclidean / spacing edges; sigma (48) and rgb (48x3) in shared memory
 // (sigma is overwritten with the weights).  Writes dL/dsigma, dL/drgb_sample (t^2 scaling applied)
 // and the final weights of global ray r (chunk-local index).
-__device__ __forceinline__ void composite_adjoint_ray(const ModelDev& M, const FieldArgs& A, const float* t_edge,
-                                                      const float* s_edge, float* sigma, const float* rgb,
-                                                      int64_t r, int lane) {
+// Returns this lane's max |d/d(pre-activation)| over its samples: |dL/drgb| * rgb (SafeExp) and
+// |dL/dsigma| * exp(clamp(raw, -15, 15)) (trunc_exp) - the tensor-core backward scales its fp16 operands by it.
+__device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const FieldArgs& A, const float* t_edge,
+                                                       const float* s_edge, float* sigma, const float* rgb,
+                                                       int64_t r, int lane) {
   const bool eval = !A.training;
-  float ds[2], w[2], T[2], e[2], delta[2], scale[2];
+  float ds[2], w[2], T[2], e[2], delta[2], scale[2], sg[2];
+  float seed_max = 0.f;
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
     int si = k * 32 + lane;
-    ds[k] = 0.f; delta[k] = 0.f; scale[k] = 0.f;
+    ds[k] = 0.f; delta[k] = 0.f; scale[k] = 0.f; sg[k] = 0.f;
     if (si < kS2) {
       float t0 = t_edge[si], t1 = t_edge[si + 1];
       delta[k] = sub_rn(t1, t0);
+      sg[k] = sigma[si];
       ds[k] = mul_rn(delta[k], sigma[si]);
       float tm = (t0 + t1) * 0.5f;
       scale[k] = fminf(fmaxf(tm * tm, 0.f), 1.f);
@@ -254,13 +258,20 @@ __device__ __forceinline__ void composite_adjoint_ray(const ModelDev& M, const F
     int si = k * 32 + lane;
     if (si < kS2) {
       float gds = gw[k] * T[k] * e[k] - suffix[k];
-      A.g_sigma[r * kS2 + si] = gds * delta[k] * scale[k];
+      const float gsig = gds * delta[k] * scale[k];
+      A.g_sigma[r * kS2 + si] = gsig;
+      seed_max = fmaxf(seed_max, fabsf(gsig) * fminf(fmaxf(sg[k], 3.0590232e-7f), 3269017.4f));
       float wl = w[k] + (si == kS2 - 1 ? bg : 0.f);
 #pragma unroll
-      for (int ch = 0; ch < 3; ++ch) A.g_rgbs[(r * kS2 + si) * 3 + ch] = gb[ch] * wl * fin[k][ch] * scale[k];
+      for (int ch = 0; ch < 3; ++ch) {
+        const float gc = gb[ch] * wl * fin[k][ch] * scale[k];
+        A.g_rgbs[(r * kS2 + si) * 3 + ch] = gc;
+        seed_max = fmaxf(seed_max, fabsf(gc * rgb[si * 3 + ch]));
+      }
     }
   }
   __syncwarp();
+  return seed_max;
 }
 
 // Tangent GEMM: Yd[n][m] = (MASK ? Yp[n][m] > 0 : 1) * sum_k Wt[k][n] * Xd[k][m]  (no bias; ReLU mask from

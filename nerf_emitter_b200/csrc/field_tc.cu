@@ -37,19 +37,10 @@ struct TcSmem {
   float s_edge[kRaysPerGroup * (kS2 + 1)];   // adjoint-seed mode only
   alignas(8) uint64_t mbar;
   uint32_t tmem_slot;
+  int seed_max_bits;                         // adjoint-seed mode: max seed magnitude of this CTA (float bits)
 };
 
-// W (rows x cols_src, torch (out,in) layout, fp32) -> fp16 UMMA K-major B operand with R rows and K columns;
-// entries outside [rows, cols_used) are zero.
-template <int R, int K>
-__device__ __forceinline__ void stage_weight(uint8_t* dst, const float* __restrict__ W, int rows, int cols_src,
-                                             int cols_used, int tid, int nthreads) {
-  for (int i = tid; i < R * K; i += nthreads) {
-    int n = i / K, k = i % K;
-    float v = (n < rows && k < cols_used) ? W[n * cols_src + k] : 0.f;
-    *reinterpret_cast<__half*>(dst + tc::chunk_off<R>(n, k >> 3) + (k & 7) * 2) = __float2half_rn(v);
-  }
-}
+using tc::stage_weight;
 
 // accumulator row (64 columns) -> +bias, ReLU -> fp16 row of the next A operand (8 K-chunks)
 __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
@@ -119,7 +110,9 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   if (tid == 0) {
     tc::mbar_init(&sm->mbar, 1);
     tc::fence_mbar_init();
+    sm->seed_max_bits = 0;
   }
+  float seed_max = 0.f;
   if (wid == 0) tc::tmem_alloc<64>(&sm->tmem_slot);
   __syncthreads();
   for (int n = tid; n < 64; n += 128) {
@@ -234,8 +227,8 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
     // composite: warp w handles rays w and w+4; lane handles samples lane and lane+32 (fp32, as field.cu)
     for (int rr = wid; rr < rays_here; rr += 4) {
       if (MODE == 1) {
-        composite_adjoint_ray(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)], &sm->sigma[rr * kS2],
-                              &sm->rgb[rr * kS2 * 3], r0 + rr, lane);
+        seed_max = fmaxf(seed_max, composite_adjoint_ray(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)],
+                                                         &sm->sigma[rr * kS2], &sm->rgb[rr * kS2 * 3], r0 + rr, lane));
         continue;
       }
       float ds[2], w[2];
@@ -275,8 +268,14 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       }
     }
   }
+  if (MODE == 1 && A.g_absmax) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) seed_max = fmaxf(seed_max, __shfl_xor_sync(0xffffffffu, seed_max, o));
+    if (lane == 0) atomicMax(&sm->seed_max_bits, __float_as_int(seed_max));   // non-negative floats order as ints
+  }
   tc::tc_fence_before();
   __syncthreads();
+  if (MODE == 1 && A.g_absmax && tid == 0) atomicMax(reinterpret_cast<int*>(A.g_absmax), sm->seed_max_bits);
   if (wid == 0) tc::tmem_dealloc<64>(tmem);
 }
 

@@ -64,6 +64,7 @@ struct FieldArgs : RayArgs {
   float* g_sigma;          // (n, 48)  dL/dsigma (post-selector density), gradient scaling applied
   float* g_rgbs;           // (n, 48, 3) dL/drgb_sample, gradient scaling applied
   int64_t reg_chunk;       // rays per backward chunk over which the regulariser means are taken
+  float* g_absmax;         // or null: max |d/d(pre-activation) seed| of the launch (atomicMax on the float bits)
 };
 
 // gradient accumulators in the torch parameter layouts (atomically accumulated)
@@ -85,6 +86,7 @@ struct FieldBwdArgs : RayArgs {
   const float* g_rgbs;     // (n, 48, 3)
   float* ray_grad;         // (n, 6) zero-initialised accumulators: d/d(o_nerf), d/d(d_nerf)
   float loss_scale;        // applied to parameter gradients only
+  const float* g_absmax;   // tensor-core path: written by the seed pass (fp16 gradient operand scale)
 };
 
 struct PropBwdArgs : SampleArgs {
@@ -109,6 +111,7 @@ cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, 
 cudaError_t launch_field_adjoint_seed(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_jvp(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_backward(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
+cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
 cudaError_t launch_prop_backward(const ModelDev& M, const PropBwdArgs& A, cudaStream_t stream);
 cudaError_t launch_finalize_ray_grads(const ModelDev& M, const FinalizeArgs& A, cudaStream_t stream);
 cudaError_t launch_hash_encode(const GridDev& G, const float2* table, const float* x, int64_t n, float* out,

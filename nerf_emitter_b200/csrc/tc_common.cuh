@@ -73,6 +73,16 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+// same shape, 8 consecutive columns
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ---------------------------------------------------------------------------------
@@ -91,6 +101,12 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
 // [17,23) N >> 3, [24,29) M >> 4
 __host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// general form: operand majors selectable (1 = MN-major: the operand's M/N index is the contiguous one)
+__host__ __device__ constexpr uint32_t idesc_f16_mj(int M, int N, int a_mn, int b_mn) {
+  return (1u << 4) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
 }
 
 // D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread
@@ -124,6 +140,28 @@ __device__ __forceinline__ void issue_layer(uint32_t d_tmem, const void* a_smem,
   mma_commit(bar);
 }
 
+// A view of one fp16 buffer in the layout above as an MMA operand.  The SAME buffer of R rows x C columns,
+// element (r, c) at (c / 8) * R * 16 + (r / 8) * 128 + (r % 8) * 16 + (c % 8) * 2, can be read
+//   * K-major  (rows = the operand's M/N index, columns = K):  LBO = R * 16, SBO = 128, 16 columns per k-step
+//   * MN-major (columns = the operand's M/N index, rows = K):  LBO = 128 (next 8 rows), SBO = R * 16 (next 8
+//     columns), 16 rows per k-step (verified on B200 with tools/umma_probe.cu)
+struct Operand {
+  uint32_t addr, lbo, sbo, step;
+};
+__device__ __forceinline__ Operand op_kmajor(const void* buf, int rows) {
+  return Operand{smem_u32(buf), (uint32_t)rows * 16u, 128u, 2u * (uint32_t)rows * 16u};
+}
+__device__ __forceinline__ Operand op_mnmajor(const void* buf, int rows, int first_col = 0) {
+  return Operand{smem_u32(buf) + (uint32_t)(first_col >> 3) * (uint32_t)rows * 16u, 128u, (uint32_t)rows * 16u, 256u};
+}
+// D (+)= A * B^T over `ksteps` k-steps of 16; the first k-step overwrites D unless `accumulate`
+__device__ __forceinline__ void mma_chain(uint32_t d_tmem, const Operand& a, const Operand& b, uint32_t idesc, int ksteps,
+                                          bool accumulate) {
+  for (int j = 0; j < ksteps; ++j)
+    mma_f16_ss(d_tmem, smem_desc(a.addr + j * a.step, a.lbo, a.sbo), smem_desc(b.addr + j * b.step, b.lbo, b.sbo), idesc,
+               (accumulate || j > 0) ? 1u : 0u);
+}
+
 // byte offset of the 16-byte chunk (row r, K-chunk kc) of an operand with R rows
 template <int R>
 __device__ __forceinline__ uint32_t chunk_off(int r, int kc) { return (uint32_t)(kc * R * 16 + r * 16); }
@@ -131,6 +169,22 @@ __device__ __forceinline__ uint32_t chunk_off(int r, int kc) { return (uint32_t)
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
+}
+// saturating variant for gradient operands: +-inf would poison a whole accumulator column
+__device__ __forceinline__ uint32_t pack_h2_sat(float a, float b) {
+  return pack_h2(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
+}
+
+// W (rows x cols_src, torch (out,in) layout, fp32) -> fp16 K-major operand buffer with R rows and K columns;
+// entries outside [rows, cols_used) are zero.
+template <int R, int K>
+__device__ __forceinline__ void stage_weight(uint8_t* dst, const float* __restrict__ W, int rows, int cols_src,
+                                             int cols_used, int tid, int nthreads) {
+  for (int i = tid; i < R * K; i += nthreads) {
+    int n = i / K, k = i % K;
+    float v = (n < rows && k < cols_used) ? W[n * cols_src + k] : 0.f;
+    *reinterpret_cast<__half*>(dst + chunk_off<R>(n, k >> 3) + (k & 7) * 2) = __float2half_rn(v);
+  }
 }
 
 }  // namespace tc

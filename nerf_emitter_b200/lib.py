@@ -89,7 +89,7 @@ SYMBOLS = {
 }
 
 PROFILE_KINDS = ["k_sample_levels", "k_field_forward", "k_field_forward<adjoint_seed>", "k_field_backward",
-                 "k_prop_backward", "k_finalize_ray_grads", "k_field_jvp", "k_field_forward_tc"]
+                 "k_prop_backward", "k_finalize_ray_grads", "k_field_jvp", "k_field_forward_tc", "k_field_backward_tc"]
 
 _LIB = None
 

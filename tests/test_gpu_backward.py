@@ -248,30 +248,78 @@ def test_backward_requires_bound_grads(spec, params_factory):
     assert rc == -3 and b"not bound" in E.lib.nemit_last_error()
 
 
-def test_fp16_mode_backward_seed_pass(spec, params_factory, emitters):
-    """In fp16 mode the first backward pass (forward recompute + composite adjoint) runs on the tensor cores; the
-    MLP / hash backward is shared with the fp32 mode.  Gate: ray gradients within 2e-2 of the fp32 mode's on >= 90 % of
-    rays (a 1e-4 change of the recomputed activations moves ReLU masks of single samples) and
-    parameter gradients within 2e-2."""
-    E = emitters(0, 1e3)
-    E.train(True)
-    N = 1024
-    o, v, g = make_rays(N, seed=3)
+def _fp16_vs_fp32_backward(E, N, seed=3, prg=False):
+    o, v, g = make_rays(N, seed=seed)
     jit = [torch.rand(N, 1, generator=g) for _ in range(3)]
     gout = torch.randn(N, 3, generator=g)
     res = {}
     for prec in ("fp32", "fp16"):
         E.set_precision(prec)
         E.bind_grads()
-        go, gv = E.backward(o.cuda(), v.cuda(), gout.cuda(), jitter=jit, chunk_rays=N)
+        go, gv = E.backward(o.cuda(), v.cuda(), gout.cuda(), jitter=jit, chunk_rays=N, proposal_requires_grad=prg)
         torch.cuda.synchronize()
         res[prec] = (go.cpu(), gv.cpu(), {k: t.cpu().clone() for k, t in E.grads.items()})
     E.set_precision("fp32")
-    a, b = res["fp32"], res["fp16"]
+    return res["fp32"], res["fp16"]
+
+
+@pytest.mark.parametrize("scale,N", [(1e3, 1024), (1.0, 1001)])
+def test_fp16_mode_backward_tensor_core(scale, N, spec, params_factory, emitters):
+    """fp16 mode: forward recompute, composite adjoint (k_field_forward_tc<1>) and the whole MLP backward - dgrad, wgrad
+    and bias gradients (k_field_backward_tc) - run on the tensor cores with fp16 operands / fp32 accumulation, as the
+    reference's autocast path does.  Gates against the fp32 mode: ray gradients within 2e-2 on >= 90 % of rays (a 1e-4
+    change of the recomputed activations moves ReLU masks of single samples), MLP parameter
+    gradients within 2e-2 max-norm, the hash-table gradient (16.8 M entries, single-sample entries feel mask flips)
+    cosine >= 0.9995 and max-norm within 0.1, identical sparsity pattern.  N = 1001 leaves a ragged last tile."""
+    E = emitters(0, scale)
+    E.train(True)
+    a, b = _fp16_vs_fp32_backward(E, N)
     per_ray = torch.maximum((a[0] - b[0]).abs().max(0).values / a[0].abs().max(),
                             (a[1] - b[1]).abs().max(0).values / a[1].abs().max())
     print("fp16 vs fp32 backward: rays within 2e-2: %.1f%%" % (100 * float((per_ray < 2e-2).float().mean())))
     assert float((per_ray < 2e-2).float().mean()) >= 0.90
     for k in a[2]:
+        if "proposal" in k:
+            continue
         e = rel_err(b[2][k], a[2][k])
-        assert e < 2e-2, (k, e)
+        if k.endswith("hash_table"):
+            x, y = a[2][k].double().flatten(), b[2][k].double().flatten()
+            cos = float((x * y).sum() / (x.norm() * y.norm()))
+            assert cos >= 0.9995 and e < 0.1, (k, cos, e)
+            assert int((x != 0).sum()) == int((y != 0).sum())
+        else:
+            assert e < 2e-2, (k, e)
+
+
+def test_fp16_mode_backward_tiny_batch_strict(spec, params_factory, emitters):
+    """Two rays = one 96-sample tile (the second half of the CTA gets no tile): no mask flip happens to matter here and
+    every gradient agrees with the fp32 mode within 2e-3."""
+    E = emitters(0, 1.0)
+    E.train(True)
+    a, b = _fp16_vs_fp32_backward(E, 2)
+    assert rel_err(b[0], a[0]) < 2e-3 and rel_err(b[1], a[1]) < 2e-3
+    for k in a[2]:
+        if "proposal" not in k:
+            assert rel_err(b[2][k], a[2][k]) < 2e-3, k
+
+
+def test_fp16_mode_backward_scale_invariance(spec, params_factory, emitters):
+    """The fp16 gradient operands are scaled by a power of two derived from the launch's largest seed, so multiplying
+    grad_out by 2^-20 (far below the fp16 range if unscaled) must give exactly 2^-20 times the same gradients."""
+    E = emitters(0, 1e3)
+    E.train(True)
+    E.set_precision("fp16")
+    N = 512
+    o, v, g = make_rays(N, seed=7)
+    gout = torch.randn(N, 3, generator=g)
+    out = []
+    for mul in (1.0, 2.0 ** -20):
+        E.bind_grads()
+        go, gv = E.backward(o.cuda(), v.cuda(), (gout * mul).cuda(), chunk_rays=N, proposal_requires_grad=False)
+        torch.cuda.synchronize()
+        out.append((go.cpu() / mul, gv.cpu() / mul, {k: t.cpu().clone() / mul for k, t in E.grads.items()}))
+    E.set_precision("fp32")
+    # the distortion regulariser does not scale with grad_out, so compare with a tolerance that admits its share
+    assert rel_err(out[1][0], out[0][0]) < 2e-2 and rel_err(out[1][1], out[0][1]) < 2e-2
+    k = "field.mlp_head.layers.2.weight"
+    assert rel_err(out[1][2][k], out[0][2][k]) < 2e-2
