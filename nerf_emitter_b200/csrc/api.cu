@@ -88,6 +88,7 @@ extern "C" int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* 
 }
 
 static const int64_t kChunkRays = 1 << 18;
+static const int64_t kBwdChunkRays = 1 << 16;   // reverse mode keeps 256 B / sample of encoding tiles in the workspace
 
 extern "C" const char* nemit_last_error(void) { return g_err.c_str(); }
 extern "C" int nemit_version(void) { return 100; }
@@ -203,7 +204,7 @@ static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
   size_t t_edges2, s_edges2, host_stage, bwd, total;
-  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax;   // inside the backward block
+  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles;   // inside the backward block
 };
 static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   size_t off = base;
@@ -217,6 +218,13 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   off += align_up(sizeof(float) * (size_t)c * 6);
   if (L) L->g_absmax = off;
   off += align_up(sizeof(float));
+  // tensor-core backward: encoding rows (64 B / sample) and Jacobians (192 B / sample) of the backward sub-chunk
+  const size_t bc = (size_t)(c < kBwdChunkRays ? c : kBwdChunkRays);
+  const size_t tiles = (bc * kS2 + 127) / 128 + 3;
+  if (L) L->enc_tiles = off;
+  off += align_up(tiles * 8192);
+  if (L) L->jac_tiles = off;
+  off += align_up(tiles * 24576);
   return off - base;
 }
 static WsLayout ws_layout(int64_t n) {
@@ -440,8 +448,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
   char* ws = static_cast<char*>(workspace);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
-  for (int64_t off = 0; off < rays->n; off += kChunkRays) {
-    int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
+  for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
+    int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
     float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
     float* s_edges = reinterpret_cast<float*>(ws + L.s_edges2);
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
@@ -464,6 +472,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     if (h->precision == NEMIT_PRECISION_FP16_TC) {
       if ((e = cudaMemsetAsync(g_absmax, 0, sizeof(float), st)) != cudaSuccess) return cuda_fail(e, "memset g_absmax");
       F.g_absmax = g_absmax;
+      F.enc_tiles = reinterpret_cast<uint8_t*>(ws + L.enc_tiles);
+      F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
     }
     if (h->precision == NEMIT_PRECISION_FP16_TC)
       e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
@@ -483,6 +493,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = loss_scale;
     if (h->precision == NEMIT_PRECISION_FP16_TC) {
       B.g_absmax = g_absmax;
+      B.enc_tiles = reinterpret_cast<const uint8_t*>(ws + L.enc_tiles);
+      B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
       e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(h->M, B, st); });
     } else {
       e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); });

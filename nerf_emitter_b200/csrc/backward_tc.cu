@@ -4,7 +4,9 @@
 // One CTA = 256 threads = two independent halves of 128 threads; a half owns one 128-sample tile at a time
 // (thread t = sample row t) and the two halves share the staged weights, so that one half's gather / scatter
 // phase (LSU bound) overlaps the other half's MMA / epilogue phases.  Per tile:
-//   gather   : 16-level hash encoding of the row (fp16 A operand E) + its Jacobian d enc / d p (fp16, 96 values)
+//   load     : the row's 16-level hash encoding (fp16 A operand E), written by the seed pass k_field_forward_tc<1>
+//              together with its Jacobian d enc / d offset (fp16, 96 values): the backward never gathers from the
+//              parameter table, so its L2 working set is the gradient table alone
 //   forward  : E W_b0^T -> H1 -> [raw | geo] ; [SH16 | geo15 | 1] W_h0^T -> H2 -> H3 -> rgb pre-activation
 //              (the activations stay in shared memory; ReLU masks stay in registers)
 //   backward : for every layer, in ONE commit group,
@@ -16,7 +18,8 @@
 //                                                                    whole kernel)
 //                 bias   db  [N]        += G_out^T 1                (B = a constant ones operand; the head input
 //                                                                    carries a ones column instead)
-//   scatter  : d enc (TMEM) -> float2 red.add on the gradient table, d enc . Jacobian -> d/d(position) -> per-ray sums
+//   scatter  : d enc (TMEM) -> red.add on the gradient table (x-neighbour corners that share an aligned 16-byte pair
+//              go out as one red.v4.f32), d enc . Jacobian -> d/d(position) -> per-ray sums
 // Gradient operands are fp16 as in the reference's autocast path (torch.cuda.amp, NS/pipelines/mitsuba_sdf.py:
 // 1177,1193): the seed pass records max |seed| of the launch, the seeds are multiplied by the power of two that
 // brings that maximum to 16, and every result is divided by it again (exact), so the fp16 range is used without
@@ -62,7 +65,6 @@ struct BwdTcHalf {
   alignas(128) uint8_t h2[128 * 64 * 2];  // head hidden 1       -> its gradient
   alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
   alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
-  alignas(16) uint8_t jac[12 * 128 * 16]; // d enc / d offset: chunk c of row t at (c * 128 + t) * 16
   float db_h2[4], db_b1[16];              // bias gradients that are reduced with shuffles (true scale)
   float dvec[64];
   alignas(8) uint64_t mbar;
@@ -230,33 +232,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     for (int k = 0; k < 3; ++k) x[k] = sample_pos(o[k], d[k], tsum);
     const bool sel = contract_normalise(x, M, p);
 
-    // ---- gather: encoding row and its Jacobian -------------------------------------------------------
-#pragma unroll 1
-    for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
-      LevelCell cell[4];
-      float2 v[4][8];
+    // ---- this tile's encoding rows (the first tile of the half; later tiles were prefetched during the scatter) ----
+    if (first) {
+      const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + tile * 8192) + t;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        level_cell(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) v[j][c] = ldg_f2(A.P.main_table, cell[j].idx[c]);
-      }
-      uint32_t we[4], wj[12];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 r = blend_cell(v[j], cell[j]);
-        we[j] = tc::pack_h2(r.x, r.y);
-        float2 dx, dy, dz;
-        blend_cell_grad(v[j], cell[j], dx, dy, dz);
-        wj[3 * j + 0] = tc::pack_h2_sat(dx.x, dx.y);
-        wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
-        wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
-      }
-      *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, l0 >> 2)) = make_uint4(we[0], we[1], we[2], we[3]);
-      uint4* jp = reinterpret_cast<uint4*>(H->jac) + (l0 >> 2) * 3 * 128 + t;
-      jp[0] = make_uint4(wj[0], wj[1], wj[2], wj[3]);
-      jp[128] = make_uint4(wj[4], wj[5], wj[6], wj[7]);
-      jp[256] = make_uint4(wj[8], wj[9], wj[10], wj[11]);
+      for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = __ldcs(ep + c * 128);
     }
 
     // ---- forward recompute ---------------------------------------------------------------------------
@@ -376,16 +356,29 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
     // ---- hash grid backward: table scatter-add and d/d(position) ----------------------------------------
     {
+      // next tile's encoding rows: E is dead after the last commit group; the loads fly during the scatter
+      const int64_t next_tile = tile + (int64_t)gridDim.x * 2;
+      uint4 en[4];
+      if (next_tile < n_tiles) {
+        const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + next_tile * 8192) + t;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) en[c] = __ldcs(ep + c * 128);
+      }
       float gp[3] = {0.f, 0.f, 0.f};
       const float gscale = invS * A.loss_scale;
+      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * 24576) + t;
+      uint4 jn[3] = {__ldcs(jp), __ldcs(jp + 128), __ldcs(jp + 256)};
 #pragma unroll 1
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
         float g[8];
         tc::tmem_ld8(taddr + kColD0 + 2 * l0, g);
         tc::tmem_ld_wait();
-        const uint4* jp = reinterpret_cast<const uint4*>(H->jac) + (l0 >> 2) * 3 * 128 + t;
-        const uint4 j0 = jp[0], j1 = jp[128], j2 = jp[256];
-        const uint32_t wj[12] = {j0.x, j0.y, j0.z, j0.w, j1.x, j1.y, j1.z, j1.w, j2.x, j2.y, j2.z, j2.w};
+        const uint32_t wj[12] = {jn[0].x, jn[0].y, jn[0].z, jn[0].w, jn[1].x, jn[1].y, jn[1].z, jn[1].w,
+                                 jn[2].x, jn[2].y, jn[2].z, jn[2].w};
+        if (l0 + 4 < kMainLevels) {
+          const uint4* jq = jp + ((l0 >> 2) + 1) * 3 * 128;
+          jn[0] = __ldcs(jq); jn[1] = __ldcs(jq + 128); jn[2] = __ldcs(jq + 256);
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float gx = g[2 * j], gy = g[2 * j + 1];
@@ -396,8 +389,22 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           float cw[8];
           corner_weights(cell, cw);
           const float gxs = gx * gscale, gys = gy * gscale;
+          // corners (2q, 2q+1) differ in x only (ceil, floor).  For an even floor coordinate the two hashed indices
+          // differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
+          const float xs = mul_rn(p[0], sc);
+          const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
+          if (pair) {
 #pragma unroll
-          for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+            for (int q = 0; q < 4; ++q) {
+              const uint32_t ia = cell.idx[2 * q], ib = cell.idx[2 * q + 1];
+              const float wa = (ia & 1u) ? cw[2 * q + 1] : cw[2 * q], wb = (ia & 1u) ? cw[2 * q] : cw[2 * q + 1];
+              atomicAdd(reinterpret_cast<float4*>(A.G.main_table + (ia < ib ? ia : ib)),
+                        make_float4(wa * gxs, wa * gys, wb * gxs, wb * gys));
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+          }
           if (sel) {
             const float2 dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
             const float2 dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
@@ -419,6 +426,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           atomicAdd(rg + k, gx[k]);
           atomicAdd(rg + 3 + k, gx[k] * tmid);
         }
+      }
+      if (next_tile < n_tiles) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = en[c];
       }
     }
     first = false;

@@ -173,6 +173,24 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
           w[j] = tc::pack_h2(r.x, r.y);
         }
         *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, l0 >> 2)) = make_uint4(w[0], w[1], w[2], w[3]);
+        if (MODE == 1 && A.enc_tiles) {
+          // keep the row and its Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles)
+          const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
+          reinterpret_cast<uint4*>(A.enc_tiles + tile_id * 8192)[(l0 >> 2) * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
+          uint32_t wj[12];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float2 dx, dy, dz;
+            blend_cell_grad(v[j], cell[j], dx, dy, dz);
+            wj[3 * j + 0] = tc::pack_h2_sat(dx.x, dx.y);
+            wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
+            wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
+          }
+          uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * 24576) + (l0 >> 2) * 3 * 128 + tid;
+          jp[0] = make_uint4(wj[0], wj[1], wj[2], wj[3]);
+          jp[128] = make_uint4(wj[4], wj[5], wj[6], wj[7]);
+          jp[256] = make_uint4(wj[8], wj[9], wj[10], wj[11]);
+        }
       }
       // ---- base MLP ------------------------------------------------------------------------------------
       run_layer<64, 32>(sm, sm->b1, tmem, phase, tid);

@@ -65,6 +65,13 @@ struct FieldArgs : RayArgs {
   float* g_rgbs;           // (n, 48, 3) dL/drgb_sample, gradient scaling applied
   int64_t reg_chunk;       // rays per backward chunk over which the regulariser means are taken
   float* g_absmax;         // or null: max |d/d(pre-activation) seed| of the launch (atomicMax on the float bits)
+  // tensor-core seed pass only: the encoding rows and their Jacobians, kept for k_field_backward_tc so that the
+  // backward never touches the parameter table (its L2 working set is the gradient table alone).
+  // Tile = 128 consecutive samples of the chunk; 16-byte chunk c of row r of tile i lives at
+  //   enc_tiles + i * 8192  + (c * 128 + r) * 16   (c < 4 : fp16 encoding, 8 values per chunk, = the UMMA A operand)
+  //   jac_tiles + i * 24576 + (c * 128 + r) * 16   (c < 12: fp16 d enc / d offset, per level dx.xy dy.xy dz.xy)
+  uint8_t* enc_tiles;
+  uint8_t* jac_tiles;
 };
 
 // gradient accumulators in the torch parameter layouts (atomically accumulated)
@@ -87,6 +94,8 @@ struct FieldBwdArgs : RayArgs {
   float* ray_grad;         // (n, 6) zero-initialised accumulators: d/d(o_nerf), d/d(d_nerf)
   float loss_scale;        // applied to parameter gradients only
   const float* g_absmax;   // tensor-core path: written by the seed pass (fp16 gradient operand scale)
+  const uint8_t* enc_tiles;  // tensor-core path: see FieldArgs
+  const uint8_t* jac_tiles;
 };
 
 struct PropBwdArgs : SampleArgs {
