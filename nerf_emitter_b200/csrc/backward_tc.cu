@@ -45,6 +45,8 @@ constexpr uint32_t kColB1T = 192;   // d base_w1^T [k][n]   64 x 16
 constexpr uint32_t kColH2T = 208;   // d head_w2^T [k][n]   64 x 8
 constexpr uint32_t kColBH1 = 216;   // d head_b1   [n][*]   64 x 8 (8 identical columns)
 constexpr uint32_t kColBB0 = 224;   // d base_b0   [n][*]   64 x 8
+constexpr uint32_t kColBB1 = 232;   // d base_b1   [*][n]   64 x 16 (64 identical rows: A = ones)
+constexpr uint32_t kColBH2 = 248;   // d head_b2   [*][n]   64 x 8
 constexpr uint32_t kHalfCols = 256;
 
 struct BwdTcCommon {
@@ -57,6 +59,7 @@ struct BwdTcCommon {
   float bias_b0[64], bias_b1[16], bias_h0[64], bias_h1[64], bias_h2[4];
   float app[kApp];
   uint32_t tmem_slot;
+  volatile int stagger;                   // set by half 0 when it first reaches its scatter phase
 };
 struct BwdTcHalf {
   alignas(128) uint8_t e[128 * 32 * 2];   // hash encoding
@@ -65,7 +68,6 @@ struct BwdTcHalf {
   alignas(128) uint8_t h2[128 * 64 * 2];  // head hidden 1       -> its gradient
   alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
   alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
-  float db_h2[4], db_b1[16];              // bias gradients that are reduced with shuffles (true scale)
   float dvec[64];
   alignas(8) uint64_t mbar;
 };
@@ -174,12 +176,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     }
     C->app[i] = e;
   }
-  if (t < 4) H->db_h2[t] = 0.f;
-  if (t < 16) H->db_b1[t] = 0.f;
   if (t == 0) {
     tc::mbar_init(&H->mbar, 1);
     tc::fence_mbar_init();
   }
+  if (tid == 0) C->stagger = 0;
   if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
   __syncthreads();
   for (int n = tid; n < 64; n += 256) {
@@ -208,6 +209,8 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     }
   }
   const tc::Operand op_ones{tc::smem_u32(C->ones), 128u, 2048u, 256u};
+  // the same ones as an A operand with M = 64: every 8-row group re-reads the one group that exists (SBO = 0)
+  const tc::Operand op_ones_a{tc::smem_u32(C->ones), 128u, 0u, 256u};
 
   const int64_t n_samples = A.n * kS2;
   const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
@@ -237,6 +240,14 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + tile * 8192) + t;
 #pragma unroll
       for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = __ldcs(ep + c * 128);
+      // The two halves share the SM's LSU, and the scatter phase is bound by its reduction issue rate (1.5 cycles
+      // per lane, tools/red_bench.cu) while the MLP chain is latency bound: started together they would stay in
+      // phase and scatter at the same time.  Half 1 therefore starts when half 0 first reaches its scatter.
+      if (half == 1) {
+        if (t == 0)
+          for (uint32_t it = 0; it < (1u << 20) && C->stagger == 0; ++it) __nanosleep(200);
+        half_sync(half);
+      }
     }
 
     // ---- forward recompute ---------------------------------------------------------------------------
@@ -294,8 +305,6 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
         // SafeExp backward: exp(clamp(x, max=88)) -> gradient exp(x) below the clamp, 0 above
         const float a = v[j] + C->bias_h2[j] + M.rgb_bias;
         gout[j] = (a < 88.f) ? seed_rgb[j] * expf(a) : 0.f;
-        const float sum = warp_sum(gout[j]);
-        if (lane == 0) atomicAdd(&H->db_h2[j], sum);
       }
       *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 0)) =
           make_uint4(tc::pack_h2_sat(gout[0] * S, gout[1] * S), tc::pack_h2_sat(gout[2] * S, 0.f), 0u, 0u);
@@ -305,6 +314,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     // ---- head MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden(taddr + kColD0, mask3, H->h3, t);
@@ -328,11 +338,6 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       g16[0] = (valid && sel) ? seed_sigma * expf(fminf(fmaxf(raw, -15.f), 15.f)) * S : 0.f;
 #pragma unroll
       for (int k = 0; k < 15; ++k) g16[k + 1] = v[k];
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const float sum = warp_sum(g16[k]);
-        if (lane == 0) atomicAdd(&H->db_b1[k], sum * invS);
-      }
       uint32_t w[4];
 #pragma unroll
       for (int hh = 0; hh < 2; ++hh) {
@@ -345,9 +350,23 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     // ---- base MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden(taddr + kColD0, mask1, H->h1, t);
+    // next tile's encoding rows and this tile's Jacobian: the loads fly under the last commit group
+    const int64_t next_tile = tile + (int64_t)gridDim.x * 2;
+    uint4 en[4], jn[12];
+    {
+      if (next_tile < n_tiles) {
+        const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + next_tile * 8192) + t;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) en[c] = __ldcs(ep + c * 128);
+      }
+      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * 24576) + t;
+#pragma unroll
+      for (int c = 0; c < 12; ++c) jn[c] = __ldcs(jp + c * 128);
+    }
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
@@ -355,30 +374,22 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     });
 
     // ---- hash grid backward: table scatter-add and d/d(position) ----------------------------------------
+    if (first && half == 0 && t == 0) C->stagger = 1;
     {
-      // next tile's encoding rows: E is dead after the last commit group; the loads fly during the scatter
-      const int64_t next_tile = tile + (int64_t)gridDim.x * 2;
-      uint4 en[4];
+      // E is dead after the last commit group
       if (next_tile < n_tiles) {
-        const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + next_tile * 8192) + t;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) en[c] = __ldcs(ep + c * 128);
+        for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = en[c];
       }
       float gp[3] = {0.f, 0.f, 0.f};
       const float gscale = invS * A.loss_scale;
-      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * 24576) + t;
-      uint4 jn[3] = {__ldcs(jp), __ldcs(jp + 128), __ldcs(jp + 256)};
-#pragma unroll 1
+#pragma unroll
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
         float g[8];
         tc::tmem_ld8(taddr + kColD0 + 2 * l0, g);
         tc::tmem_ld_wait();
-        const uint32_t wj[12] = {jn[0].x, jn[0].y, jn[0].z, jn[0].w, jn[1].x, jn[1].y, jn[1].z, jn[1].w,
-                                 jn[2].x, jn[2].y, jn[2].z, jn[2].w};
-        if (l0 + 4 < kMainLevels) {
-          const uint4* jq = jp + ((l0 >> 2) + 1) * 3 * 128;
-          jn[0] = __ldcs(jq); jn[1] = __ldcs(jq + 128); jn[2] = __ldcs(jq + 256);
-        }
+        const uint4 ja = jn[(l0 >> 2) * 3], jb = jn[(l0 >> 2) * 3 + 1], jc = jn[(l0 >> 2) * 3 + 2];
+        const uint32_t wj[12] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w, jc.x, jc.y, jc.z, jc.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float gx = g[2 * j], gy = g[2 * j + 1];
@@ -426,10 +437,6 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           atomicAdd(rg + k, gx[k]);
           atomicAdd(rg + 3 + k, gx[k] * tmid);
         }
-      }
-      if (next_tile < n_tiles) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = en[c];
       }
     }
     first = false;
@@ -494,9 +501,18 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::tmem_ld_wait();
       if (has) atomicAdd(A.G.base_b0 + r, fs * u[0]);
     }
+    tc::tmem_ld16(taddr + kColBB1, v);
+    tc::tmem_ld_wait();
+    if (t == 0)
+      for (int n = 0; n < 16; ++n) atomicAdd(A.G.base_b1 + n, fs * v[n]);
+    {
+      float u[8];
+      tc::tmem_ld8(taddr + kColBH2, u);
+      tc::tmem_ld_wait();
+      if (t == 0)
+        for (int n = 0; n < 3; ++n) atomicAdd(A.G.head_b2 + n, fs * u[n]);
+    }
     half_sync(half);
-    if (t < 3) atomicAdd(A.G.head_b2 + t, A.loss_scale * H->db_h2[t]);
-    if (t < 16) atomicAdd(A.G.base_b1 + t, A.loss_scale * H->db_b1[t]);
     // appearance embedding (NS/fields/nerfacto_field.py:272-285): the camera's row in training mode, the mean of
     // all rows in eval mode
     if (t < kApp) {

@@ -206,5 +206,28 @@ int main(int argc, char** argv) {
     }
     printf("[3] column sums via ones operand (N = 8): max abs err %.3e\n", err);
   }
+  // ---------------- (5) column sums with ones as the A operand (M = 64, SBO = 0): D[i][n] = sum_m G[m][n]
+  if (test == 5) {
+    const int NN = 16;
+    std::vector<float> G(128 * NN);
+    std::vector<uint8_t> a(128 * 8 * 2), b(128 * NN * 2);
+    for (int m = 0; m < 128; ++m) for (int n = 0; n < NN; ++n) {
+      uint16_t u = f2h(frand()); G[m * NN + n] = h2f(u);
+      *reinterpret_cast<uint16_t*>(&b[off_rk(128, m, n)]) = u;
+    }
+    for (int i = 0; i < 128 * 8; ++i) *reinterpret_cast<uint16_t*>(&a[i * 2]) = f2h(1.f);
+    ProbeArgs P{};
+    P.a_lbo = 128; P.a_sbo = 0; P.a_step = 2 * 128;
+    P.b_lbo = 128; P.b_sbo = 128 * 16; P.b_step = 2 * 128;
+    P.idesc = idesc(64, NN, 0, 0, 1, 1);
+    P.ksteps = 8; P.ncols = 16;
+    auto out = run(a, b, P);
+    double err = 0;
+    for (int i = 0; i < 64; ++i) for (int n = 0; n < NN; ++n) {
+      double r = 0; for (int m = 0; m < 128; ++m) r += G[m * NN + n];
+      err = fmax(err, fabs(r - out[((i / 16) * 32 + i % 16) * 16 + n]));
+    }
+    printf("[5] column sums with ones as A (M = 64, SBO = 0, N = 16): max abs err %.3e\n", err);
+  }
   return 0;
 }
