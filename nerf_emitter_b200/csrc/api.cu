@@ -204,7 +204,7 @@ static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
   size_t t_edges2, s_edges2, host_stage, bwd, total;
-  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles;   // inside the backward block
+  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles, act_tiles, seeds4;   // inside the backward block
 };
 static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   size_t off = base;
@@ -218,13 +218,18 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   off += align_up(sizeof(float) * (size_t)c * 6);
   if (L) L->g_absmax = off;
   off += align_up(sizeof(float));
-  // tensor-core backward: encoding rows (64 B / sample) and Jacobians (192 B / sample) of the backward sub-chunk
+  // tensor-core backward: per sample of the backward sub-chunk the encoding row (64 B), its Jacobian (192 B), the
+  // activations H1 / IN / H2 / H3 (448 B) and the pre-activation seeds (16 B), kept by the seed pass
   const size_t bc = (size_t)(c < kBwdChunkRays ? c : kBwdChunkRays);
   const size_t tiles = (bc * kS2 + 127) / 128 + 3;
   if (L) L->enc_tiles = off;
   off += align_up(tiles * 8192);
   if (L) L->jac_tiles = off;
   off += align_up(tiles * 24576);
+  if (L) L->act_tiles = off;
+  off += align_up(tiles * 57344);
+  if (L) L->seeds4 = off;
+  off += align_up(tiles * 128 * 16);
   return off - base;
 }
 static WsLayout ws_layout(int64_t n) {
@@ -474,6 +479,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
       F.g_absmax = g_absmax;
       F.enc_tiles = reinterpret_cast<uint8_t*>(ws + L.enc_tiles);
       F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
+      F.act_tiles = reinterpret_cast<uint8_t*>(ws + L.act_tiles);
+      F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
     }
     if (h->precision == NEMIT_PRECISION_FP16_TC)
       e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
@@ -495,6 +502,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
       B.g_absmax = g_absmax;
       B.enc_tiles = reinterpret_cast<const uint8_t*>(ws + L.enc_tiles);
       B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
+      B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
+      B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
       e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(h->M, B, st); });
     } else {
       e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); });

@@ -1,14 +1,17 @@
 // backward_tc.cu - k_field_backward_tc: reverse mode of the main field (48 final samples per ray) with every
 // dense contraction on the 5th-generation tensor cores (tcgen05.mma, fp16 operands, fp32 accumulation in TMEM).
 //
-// One CTA = 256 threads = two independent halves of 128 threads; a half owns one 128-sample tile at a time
-// (thread t = sample row t) and the two halves share the staged weights, so that one half's gather / scatter
-// phase (LSU bound) overlaps the other half's MMA / epilogue phases.  Per tile:
-//   load     : the row's 16-level hash encoding (fp16 A operand E), written by the seed pass k_field_forward_tc<1>
-//              together with its Jacobian d enc / d offset (fp16, 96 values): the backward never gathers from the
-//              parameter table, so its L2 working set is the gradient table alone
-//   forward  : E W_b0^T -> H1 -> [raw | geo] ; [SH16 | geo15 | 1] W_h0^T -> H2 -> H3 -> rgb pre-activation
-//              (the activations stay in shared memory; ReLU masks stay in registers)
+// The seed pass (k_field_forward_tc<1>, field_tc.cu) has already run the forward of the chunk on the tensor cores and
+// kept, per 128-sample tile and in the UMMA operand layout: the hash encoding E, its Jacobian d enc / d offset, the
+// post-ReLU activations H1, IN = [SH16 | geo15 | 1], H2, H3, and per sample the seed d loss / d pre-activation
+// (rgb xyz with the SafeExp derivative, density w with the trunc_exp derivative and the selector).  So this kernel
+// neither gathers from the parameter table (its L2 working set is the gradient table alone) nor recomputes anything.
+//
+// One CTA = 256 threads = two independent halves of 128 threads; a half owns one tile at a time (thread t = sample
+// row t).  Per tile:
+//   load     : E, H1, IN, H2, H3 arrive by five 1-D bulk copies (cp.async.bulk -> mbarrier complete_tx) straight into
+//              the operand buffers; the copies of the NEXT tile are issued as soon as a buffer's last reader (an MMA
+//              commit group) has completed, so they fly under the remaining layers and the scatter
 //   backward : for every layer, in ONE commit group,
 //                 dgrad  G_in [128 x K]  = G_out [128 x N] W        (A = G_out K-major, B = the FORWARD weight
 //                                                                    buffer read MN-major: no transposed copy)
@@ -16,10 +19,13 @@
 //                                                                    B = activation buffer read MN-major, K = 128
 //                                                                    samples; accumulator lives in TMEM for the
 //                                                                    whole kernel)
-//                 bias   db  [N]        += G_out^T 1                (B = a constant ones operand; the head input
+//                 bias   db  [N]        += G_out^T 1                (a constant ones operand; the head input
 //                                                                    carries a ones column instead)
+//              the epilogue masks the accumulator row with (activation > 0) and writes the fp16 gradient row over
+//              the activation row
 //   scatter  : d enc (TMEM) -> red.add on the gradient table (x-neighbour corners that share an aligned 16-byte pair
-//              go out as one red.v4.f32), d enc . Jacobian -> d/d(position) -> per-ray sums
+//              go out as one red.v4.f32), d enc . Jacobian -> d/d(position) -> per-ray sums.  This phase is bound by
+//              the SM's reduction issue rate (1.5 cycles per lane, tools/red_bench.cu).
 // Gradient operands are fp16 as in the reference's autocast path (torch.cuda.amp, NS/pipelines/mitsuba_sdf.py:
 // 1177,1193): the seed pass records max |seed| of the launch, the seeds are multiplied by the power of two that
 // brings that maximum to 16, and every result is divided by it again (exact), so the fp16 range is used without
@@ -56,10 +62,8 @@ struct BwdTcCommon {
   alignas(128) uint8_t b4[64 * 64 * 2];   // head layer 1   (64 x 64)
   alignas(128) uint8_t b5[16 * 64 * 2];   // head layer 2   (3 rows used of 16)
   alignas(128) uint8_t ones[8 * 128 * 2]; // MN-major 8 x 128 operand of fp16 ones
-  float bias_b0[64], bias_b1[16], bias_h0[64], bias_h1[64], bias_h2[4];
   float app[kApp];
   uint32_t tmem_slot;
-  volatile int stagger;                   // set by half 0 when it first reaches its scatter phase
 };
 struct BwdTcHalf {
   alignas(128) uint8_t e[128 * 32 * 2];   // hash encoding
@@ -69,12 +73,14 @@ struct BwdTcHalf {
   alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
   alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
   float dvec[64];
-  alignas(8) uint64_t mbar;
+  alignas(8) uint64_t mbar;               // MMA commit groups
+  alignas(8) uint64_t ld_bar;             // bulk copies of one tile (65536 bytes per phase)
 };
 struct BwdTcSmem {
   BwdTcCommon c;
   BwdTcHalf h[2];
 };
+constexpr uint32_t kTileLoadBytes = 8192 + 57344;
 
 __device__ __forceinline__ void half_sync(int half) {
   asm volatile("bar.sync %0, 128;" ::"r"(half + 1) : "memory");
@@ -96,34 +102,8 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
   tc::tc_fence_after();
 }
 
-// forward hidden layer: accumulator row + bias, ReLU -> fp16 row (8 K-chunks); returns the ReLU mask
-__device__ __forceinline__ uint64_t epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
-  float v[4][16];
-#pragma unroll
-  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
-  tc::tmem_ld_wait();
-  uint64_t mask = 0;
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
-#pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      uint32_t w[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int j = hh * 8 + q * 2;
-        const float x0 = v[c][j] + bias[c * 16 + j], x1 = v[c][j + 1] + bias[c * 16 + j + 1];
-        if (x0 > 0.f) mask |= 1ull << (c * 16 + j);
-        if (x1 > 0.f) mask |= 1ull << (c * 16 + j + 1);
-        w[q] = tc::pack_h2(fmaxf(x0, 0.f), fmaxf(x1, 0.f));
-      }
-      *reinterpret_cast<uint4*>(a + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-    }
-  }
-  return mask;
-}
-
-// backward hidden layer: accumulator row x ReLU mask -> fp16 gradient row written over the activation row
-__device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint64_t mask, uint8_t* g, int row) {
+// hidden layer: accumulator row x (activation row > 0) -> fp16 gradient row written over the activation row
+__device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int row) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
@@ -132,15 +112,19 @@ __device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint64_t mask, ui
   for (int c = 0; c < 4; ++c) {
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
+      uint4* pr = reinterpret_cast<uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh));
+      const uint4 act = *pr;
+      const uint32_t aw[4] = {act.x, act.y, act.z, act.w};
       uint32_t w[4];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int j = hh * 8 + q * 2;
-        const float x0 = ((mask >> (c * 16 + j)) & 1ull) ? v[c][j] : 0.f;
-        const float x1 = ((mask >> (c * 16 + j + 1)) & 1ull) ? v[c][j + 1] : 0.f;
+        // post-ReLU fp16 activations are >= 0: a non-zero half pattern (sign bit aside) means the unit was active
+        const float x0 = (aw[q] & 0x00007fffu) ? v[c][j] : 0.f;
+        const float x1 = (aw[q] & 0x7fff0000u) ? v[c][j + 1] : 0.f;
         w[q] = tc::pack_h2_sat(x0, x1);
       }
-      *reinterpret_cast<uint4*>(g + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      *pr = make_uint4(w[0], w[1], w[2], w[3]);
     }
   }
 }
@@ -162,9 +146,6 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   tc::stage_weight<64, 64>(C->b4, A.P.head_w1, 64, 64, 64, tid, 256);
   tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, 256);
   for (int i = tid; i < 8 * 128; i += 256) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
-  for (int i = tid; i < 64; i += 256) { C->bias_b0[i] = A.P.base_b0[i]; C->bias_h1[i] = A.P.head_b1[i]; }
-  for (int i = tid; i < 16; i += 256) C->bias_b1[i] = A.P.base_b1[i];
-  for (int i = tid; i < 4; i += 256) C->bias_h2[i] = i < 3 ? A.P.head_b2[i] : 0.f;
   for (int i = tid; i < kApp; i += 256) {
     float e;
     if (A.training) {
@@ -178,16 +159,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   }
   if (t == 0) {
     tc::mbar_init(&H->mbar, 1);
+    tc::mbar_init(&H->ld_bar, 1);
     tc::fence_mbar_init();
   }
-  if (tid == 0) C->stagger = 0;
   if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
-  __syncthreads();
-  for (int n = tid; n < 64; n += 256) {
-    float b = A.P.head_b0[n];
-    for (int k = 0; k < kApp; ++k) b = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], C->app[k], b);
-    C->bias_h0[n] = b;
-  }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -214,20 +189,36 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
   const int64_t n_samples = A.n * kS2;
   const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
+  const int64_t tile_stride = (int64_t)gridDim.x * 2;
   bool first = true;
-  for (int64_t tile = (int64_t)blockIdx.x * 2 + half; tile < n_tiles; tile += (int64_t)gridDim.x * 2) {
+  uint32_t ld_phase = 0;
+  // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
+  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar); };
+  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * 57344, 16384, &H->ld_bar); };
+  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * 57344 + 16384, 8192, &H->ld_bar); };
+  auto load_h2 = [&](int64_t tl) { tc::bulk_g2s(H->h2, A.act_tiles + tl * 57344 + 24576, 16384, &H->ld_bar); };
+  auto load_h3 = [&](int64_t tl) { tc::bulk_g2s(H->h3, A.act_tiles + tl * 57344 + 40960, 16384, &H->ld_bar); };
+  {
+    const int64_t tile0 = (int64_t)blockIdx.x * 2 + half;
+    if (t == 0 && tile0 < n_tiles) {
+      tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
+      load_h3(tile0); load_h2(tile0); load_in(tile0); load_h1(tile0); load_e(tile0);
+    }
+  }
+  for (int64_t tile = (int64_t)blockIdx.x * 2 + half; tile < n_tiles; tile += tile_stride) {
+    const int64_t next_tile = tile + tile_stride;
+    const bool has_next = next_tile < n_tiles;
     const int64_t s = tile * kTileM + t;
     const bool valid = s < n_samples;
     const int64_t rr = valid ? s / kS2 : 0;
     const int si = valid ? (int)(s % kS2) : 0;
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, t0 = 0.f, t1 = 0.f;
-    float seed_rgb[3] = {0.f, 0.f, 0.f}, seed_sigma = 0.f;
+    float4 seed = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
       load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, M.scene_scale, o, d);
       t0 = A.t_edges2[rr * (kS2 + 1) + si];
       t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
-      seed_rgb[0] = A.g_rgbs[s * 3 + 0]; seed_rgb[1] = A.g_rgbs[s * 3 + 1]; seed_rgb[2] = A.g_rgbs[s * 3 + 2];
-      seed_sigma = A.g_sigma[s];
+      seed = __ldcs(A.seeds4 + s);
     }
     const float tsum = add_rn(t0, t1);
     float x[3], p[3];
@@ -235,81 +226,13 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     for (int k = 0; k < 3; ++k) x[k] = sample_pos(o[k], d[k], tsum);
     const bool sel = contract_normalise(x, M, p);
 
-    // ---- this tile's encoding rows (the first tile of the half; later tiles were prefetched during the scatter) ----
-    if (first) {
-      const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + tile * 8192) + t;
-#pragma unroll
-      for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = __ldcs(ep + c * 128);
-      // The two halves share the SM's LSU, and the scatter phase is bound by its reduction issue rate (1.5 cycles
-      // per lane, tools/red_bench.cu) while the MLP chain is latency bound: started together they would stay in
-      // phase and scatter at the same time.  Half 1 therefore starts when half 0 first reaches its scatter.
-      if (half == 1) {
-        if (t == 0)
-          for (uint32_t it = 0; it < (1u << 20) && C->stagger == 0; ++it) __nanosleep(200);
-        half_sync(half);
-      }
-    }
-
-    // ---- forward recompute ---------------------------------------------------------------------------
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->e, 128), tc::op_kmajor(C->b1, 64), tc::idesc_f16(128, 64), 2, false);
-    });
-    const uint64_t mask1 = epi_fwd_hidden(taddr + kColD0, C->bias_b0, H->h1, t);
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_kmajor(C->b2, 16), tc::idesc_f16(128, 16), 4, false);
-    });
-    float raw;
-    {
-      float v[16];
-      tc::tmem_ld16(taddr + kColD0, v);
-      tc::tmem_ld_wait();
-      raw = v[0] + C->bias_b1[0];
-      float c[16];
-      sh16((d[0] + 1.f) * 0.5f, (d[1] + 1.f) * 0.5f, (d[2] + 1.f) * 0.5f, c);
-      uint32_t w[4];
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
-        *reinterpret_cast<uint4*>(H->in + tc::chunk_off<128>(t, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-      }
-      float gfe[16];
-#pragma unroll
-      for (int k = 0; k < 15; ++k) gfe[k] = v[k + 1] + C->bias_b1[k + 1];
-      gfe[15] = 1.f;                                   // ones column: its wgrad column is d head_b0_eff
-#pragma unroll
-      for (int hh = 0; hh < 2; ++hh) {
-#pragma unroll
-        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
-        *reinterpret_cast<uint4*>(H->in + tc::chunk_off<128>(t, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-      }
-    }
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->in, 128), tc::op_kmajor(C->b3, 64), tc::idesc_f16(128, 64), 2, false);
-    });
-    const uint64_t mask2 = epi_fwd_hidden(taddr + kColD0, C->bias_h0, H->h2, t);
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_kmajor(C->b4, 64), tc::idesc_f16(128, 64), 4, false);
-    });
-    const uint64_t mask3 = epi_fwd_hidden(taddr + kColD0, C->bias_h1, H->h3, t);
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_kmajor(C->b5, 16), tc::idesc_f16(128, 8), 4, false);
-    });
-    {
-      float v[8];
-      tc::tmem_ld8(taddr + kColD0, v);
-      tc::tmem_ld_wait();
-      float gout[3];
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        // SafeExp backward: exp(clamp(x, max=88)) -> gradient exp(x) below the clamp, 0 above
-        const float a = v[j] + C->bias_h2[j] + M.rgb_bias;
-        gout[j] = (a < 88.f) ? seed_rgb[j] * expf(a) : 0.f;
-      }
-      *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 0)) =
-          make_uint4(tc::pack_h2_sat(gout[0] * S, gout[1] * S), tc::pack_h2_sat(gout[2] * S, 0.f), 0u, 0u);
-      *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 1)) = make_uint4(0u, 0u, 0u, 0u);
-    }
+    // d loss / d (rgb pre-activation): 3 of 16 columns
+    *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 0)) =
+        make_uint4(tc::pack_h2_sat(seed.x * S, seed.y * S), tc::pack_h2_sat(seed.z * S, 0.f), 0u, 0u);
+    *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 1)) = make_uint4(0u, 0u, 0u, 0u);
+    // this tile's operand buffers have landed
+    tc::mbar_wait(&H->ld_bar, ld_phase);
+    ld_phase ^= 1u;
 
     // ---- head MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
@@ -317,25 +240,29 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
-    epi_bwd_hidden(taddr + kColD0, mask3, H->h3, t);
+    epi_bwd_hidden(taddr + kColD0, H->h3, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
     });
-    epi_bwd_hidden(taddr + kColD0, mask2, H->h2, t);
+    if (t == 0 && has_next) {       // H3 / G3 has no reader left: the next tile's copies start here
+      tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
+      load_h3(next_tile);
+    }
+    epi_bwd_hidden(taddr + kColD0, H->h2, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
     });
+    if (t == 0 && has_next) { load_h2(next_tile); load_in(next_tile); }
     {
       float v[16];
       tc::tmem_ld16(taddr + kColD0, v);
       tc::tmem_ld_wait();
-      // trunc_exp backward: exp(clamp(raw, -15, 15)); the selector multiplies the density
       float g16[16];
-      g16[0] = (valid && sel) ? seed_sigma * expf(fminf(fmaxf(raw, -15.f), 15.f)) * S : 0.f;
+      g16[0] = seed.w * S;
 #pragma unroll
       for (int k = 0; k < 15; ++k) g16[k + 1] = v[k];
       uint32_t w[4];
@@ -353,16 +280,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
-    epi_bwd_hidden(taddr + kColD0, mask1, H->h1, t);
-    // next tile's encoding rows and this tile's Jacobian: the loads fly under the last commit group
-    const int64_t next_tile = tile + (int64_t)gridDim.x * 2;
-    uint4 en[4], jn[12];
+    epi_bwd_hidden(taddr + kColD0, H->h1, t);
+    // this tile's Jacobian rows: the loads fly under the last commit group
+    uint4 jn[12];
     {
-      if (next_tile < n_tiles) {
-        const uint4* ep = reinterpret_cast<const uint4*>(A.enc_tiles + next_tile * 8192) + t;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) en[c] = __ldcs(ep + c * 128);
-      }
       const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * 24576) + t;
 #pragma unroll
       for (int c = 0; c < 12; ++c) jn[c] = __ldcs(jp + c * 128);
@@ -372,15 +293,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
     });
+    if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 
     // ---- hash grid backward: table scatter-add and d/d(position) ----------------------------------------
-    if (first && half == 0 && t == 0) C->stagger = 1;
     {
-      // E is dead after the last commit group
-      if (next_tile < n_tiles) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(H->e + tc::chunk_off<128>(t, c)) = en[c];
-      }
       float gp[3] = {0.f, 0.f, 0.f};
       const float gscale = invS * A.loss_scale;
 #pragma unroll

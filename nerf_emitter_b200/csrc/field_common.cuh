@@ -259,15 +259,22 @@ __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const 
     if (si < kS2) {
       float gds = gw[k] * T[k] * e[k] - suffix[k];
       const float gsig = gds * delta[k] * scale[k];
-      A.g_sigma[r * kS2 + si] = gsig;
-      seed_max = fmaxf(seed_max, fabsf(gsig) * fminf(fmaxf(sg[k], 3.0590232e-7f), 3269017.4f));
+      // trunc_exp backward exp(clamp(raw, -15, 15)) = clamp(sigma, e^-15, e^15); sigma == 0 <=> selector off
+      const float dpre_sigma = sg[k] > 0.f ? gsig * fminf(fmaxf(sg[k], 3.0590232e-7f), 3269017.4f) : 0.f;
+      seed_max = fmaxf(seed_max, fabsf(dpre_sigma));
       float wl = w[k] + (si == kS2 - 1 ? bg : 0.f);
+      float dpre[3];
 #pragma unroll
       for (int ch = 0; ch < 3; ++ch) {
         const float gc = gb[ch] * wl * fin[k][ch] * scale[k];
-        A.g_rgbs[(r * kS2 + si) * 3 + ch] = gc;
-        seed_max = fmaxf(seed_max, fabsf(gc * rgb[si * 3 + ch]));
+        if (!A.seeds4) A.g_rgbs[(r * kS2 + si) * 3 + ch] = gc;
+        // SafeExp backward: exp(x) below the clamp at 88, 0 above (rgb = exp(min(x, 88)))
+        const float c_raw = rgb[si * 3 + ch];
+        dpre[ch] = c_raw < 1.6516e38f ? gc * c_raw : 0.f;
+        seed_max = fmaxf(seed_max, fabsf(dpre[ch]));
       }
+      if (A.seeds4) A.seeds4[r * kS2 + si] = make_float4(dpre[0], dpre[1], dpre[2], dpre_sigma);
+      else A.g_sigma[r * kS2 + si] = gsig;
     }
   }
   __syncwarp();

@@ -43,7 +43,8 @@ struct TcSmem {
 using tc::stage_weight;
 
 // accumulator row (64 columns) -> +bias, ReLU -> fp16 row of the next A operand (8 K-chunks)
-__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
+__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row,
+                                                uint4* keep = nullptr) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
@@ -60,6 +61,7 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
         w[q] = tc::pack_h2(x0, x1);
       }
       *reinterpret_cast<uint4*>(a + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      if (keep) keep[(c * 2 + hh) * 128 + row] = make_uint4(w[0], w[1], w[2], w[3]);   // same layout, for the backward
     }
   }
 }
@@ -192,9 +194,12 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
           jp[256] = make_uint4(wj[8], wj[9], wj[10], wj[11]);
         }
       }
+      // adjoint-seed mode keeps the activations (fp16 operand rows) for k_field_backward_tc
+      uint8_t* act = nullptr;
+      if (MODE == 1 && A.act_tiles) act = A.act_tiles + (g * (kGroupSamples / kTileM) + tile) * 57344;
       // ---- base MLP ------------------------------------------------------------------------------------
       run_layer<64, 32>(sm, sm->b1, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_b0, sm->a, tid);
+      epilogue_hidden(taddr, sm->bias_b0, sm->a, tid, act ? reinterpret_cast<uint4*>(act) : nullptr);
       run_layer<16, 64>(sm, sm->b2, tmem, phase, tid);
       {
         float v[16];
@@ -211,23 +216,25 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+          if (act) reinterpret_cast<uint4*>(act + 16384)[hh * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
         }
         float gfe[16];
 #pragma unroll
         for (int k = 0; k < 15; ++k) gfe[k] = v[k + 1] + sm->bias_b1[k + 1];
-        gfe[15] = 0.f;
+        gfe[15] = MODE == 1 ? 1.f : 0.f;   // pad column (zero weights); the backward's wgrad reads it as a ones column
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+          if (act) reinterpret_cast<uint4*>(act + 16384)[(2 + hh) * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
         }
       }
       // ---- head MLP ------------------------------------------------------------------------------------
       run_layer<64, 32>(sm, sm->b3, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_h0, sm->a, tid);
+      epilogue_hidden(taddr, sm->bias_h0, sm->a, tid, act ? reinterpret_cast<uint4*>(act + 24576) : nullptr);
       run_layer<64, 64>(sm, sm->b4, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_h1, sm->a, tid);
+      epilogue_hidden(taddr, sm->bias_h1, sm->a, tid, act ? reinterpret_cast<uint4*>(act + 40960) : nullptr);
       run_layer<16, 64>(sm, sm->b5, tmem, phase, tid);
       {
         float v[16];

@@ -70,8 +70,14 @@ struct FieldArgs : RayArgs {
   // Tile = 128 consecutive samples of the chunk; 16-byte chunk c of row r of tile i lives at
   //   enc_tiles + i * 8192  + (c * 128 + r) * 16   (c < 4 : fp16 encoding, 8 values per chunk, = the UMMA A operand)
   //   jac_tiles + i * 24576 + (c * 128 + r) * 16   (c < 12: fp16 d enc / d offset, per level dx.xy dy.xy dz.xy)
+  //   act_tiles + i * 57344 + {0: H1 (8 chunks), 16384: IN = [SH16 | geo15 | 1] (4), 24576: H2 (8), 40960: H3 (8)}
+  //             + (c * 128 + r) * 16                          fp16 post-ReLU activations = UMMA operands as well
   uint8_t* enc_tiles;
   uint8_t* jac_tiles;
+  uint8_t* act_tiles;
+  // d loss / d (rgb pre-activation xyz, density pre-activation w) per sample, i.e. the seeds with the SafeExp /
+  // trunc_exp derivatives and the selector already applied (written instead of g_sigma / g_rgbs when set)
+  float4* seeds4;
 };
 
 // gradient accumulators in the torch parameter layouts (atomically accumulated)
@@ -96,6 +102,8 @@ struct FieldBwdArgs : RayArgs {
   const float* g_absmax;   // tensor-core path: written by the seed pass (fp16 gradient operand scale)
   const uint8_t* enc_tiles;  // tensor-core path: see FieldArgs
   const uint8_t* jac_tiles;
+  const uint8_t* act_tiles;
+  const float4* seeds4;
 };
 
 struct PropBwdArgs : SampleArgs {
