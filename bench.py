@@ -27,12 +27,16 @@ ALG_BYTES_SAMPLING = (256 * 5 + 96 * 5) * 8 * 8      # prop gathers per ray (SUR
 ALG_BYTES_FIELD = 48 * 16 * 8 * 8                    # main-grid gathers per ray: 49 152 B
 RAY_IO_BYTES = 24 + 12
 # algorithmic table bytes per ray of each kernel
+SEED_KEEP_BYTES = 48 * (64 + 192 + 448 + 16)        # per ray: encoding, Jacobian, activations, seeds kept for the backward
 ALG_BYTES = {"k_sample_levels": ALG_BYTES_SAMPLING, "k_field_forward": ALG_BYTES_FIELD,
-             "k_field_forward_tc": ALG_BYTES_FIELD, "k_field_forward<adjoint_seed>": ALG_BYTES_FIELD,
+             "k_field_forward_tc": ALG_BYTES_FIELD,
+             "k_field_forward<adjoint_seed>": ALG_BYTES_FIELD + SEED_KEEP_BYTES,   # fp16 mode; fp32 mode keeps 16 B/sample
              "k_field_backward": 3 * ALG_BYTES_FIELD,      # recompute gathers + d/dx gathers + float2 red.add
-             "k_field_backward_tc": 2 * ALG_BYTES_FIELD,   # recompute gathers (Jacobian kept on chip) + float2 red.add
+             "k_field_backward_tc": ALG_BYTES_FIELD + SEED_KEEP_BYTES,   # float2 red.add + streamed tiles, no gathers
              "k_prop_backward": 2 * ALG_BYTES_SAMPLING, "k_field_jvp": ALG_BYTES_FIELD,
              "k_finalize_ray_grads": 24 + 24}
+# launches of a kernel per step over the same n rays (the sampler runs in the forward and in the backward)
+PASSES = {"k_sample_levels": 2}
 
 
 def make_rays(n, seed, device):
@@ -271,7 +275,7 @@ def main():
     value = n * world / (ms_per_step * 1e-3)
 
     # per-kernel timing for the roofline (forward kernels timed alone on this stream, same inputs)
-    roof = kernel_roofline(prof, n)
+    roof = kernel_roofline(prof, n, args.steps)
 
     # e2e: the same step through the public API with pinned HOST buffers, copies inside the timed region
     oh = o.cpu().pin_memory()
@@ -342,29 +346,32 @@ def backward_available():
         return False
 
 
-def kernel_roofline(prof, n):
+def kernel_roofline(prof, n, steps):
     """Roofline of the dominant kernel from the library's own CUDA-event records of the timed region
     (events recorded on the launching stream around every launch; nemit_profile_read)."""
     hbm, src = measured_peaks()
-    chunk = 1 << 18
-    rays_per_launch = min(n, chunk)
     kern = {k: {"ms_total": ms, "launches": c, "ms_per_launch": ms / c} for k, (ms, c) in prof.items()}
     total = sum(v["ms_total"] for v in kern.values()) or 1.0
-    for v in kern.values():
+    for k, v in kern.items():
         v["share"] = v["ms_total"] / total
+        # rays one launch processed, and the kernel's own algorithmic GB/s
+        v["rays_per_launch"] = n * steps * PASSES.get(k, 1) / v["launches"]
+        v["achieved_gbs"] = ALG_BYTES[k] * v["rays_per_launch"] / (v["ms_per_launch"] * 1e-3) / 1e9
     dom = max(kern, key=lambda k: kern[k]["ms_total"])
     alg = ALG_BYTES[dom]
-    achieved = alg * rays_per_launch / (kern[dom]["ms_per_launch"] * 1e-3) / 1e9
+    achieved = kern[dom]["achieved_gbs"]
     return {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm, "peak_source": src, "unit": "GB/s",
             "frac": achieved / hbm, "traffic": NCU_TRAFFIC.get(dom),
-            "algorithmic_bytes_per_ray": alg, "rays_per_launch": rays_per_launch, "kernels": kern,
-            "note": "achieved = algorithmic table bytes (8-byte gathers / float2 reductions) per launch / average "
-                    "CUDA-event launch duration in the timed region; tables (74 MiB) are L2-resident so DRAM "
-                    "traffic (ncu, per launch of 65536 rays, profiles/) is far below it"}
+            "algorithmic_bytes_per_ray": alg, "rays_per_launch": kern[dom]["rays_per_launch"], "kernels": kern,
+            "note": "achieved = algorithmic bytes (8-byte table gathers / float2 reductions / streamed tiles) per launch / "
+                    "average CUDA-event launch duration in the timed region; the tables (74 MiB) are L2-resident, so the "
+                    "DRAM traffic of the gather kernels (ncu, per launch of 65536 rays, profiles/) is far below it; the "
+                    "k_field_backward_tc scatter is bound by the SM reduction issue rate (188 G red lane-ops/s measured, "
+                    "profiles/r1_red_bench.txt), not by bytes"}
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures (profiles/)
-NCU_TRAFFIC = {"k_sample_levels": 7.9e6, "k_field_forward": 63.9e6}
+NCU_TRAFFIC = {"k_sample_levels": 7.9e6, "k_field_forward": 63.9e6, "k_field_forward_tc": 64.0e6}
 
 
 if __name__ == "__main__":
