@@ -193,11 +193,12 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   bool first = true;
   uint32_t ld_phase = 0;
   // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
-  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar); };
-  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * 57344, 16384, &H->ld_bar); };
-  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * 57344 + 16384, 8192, &H->ld_bar); };
-  auto load_h2 = [&](int64_t tl) { tc::bulk_g2s(H->h2, A.act_tiles + tl * 57344 + 24576, 16384, &H->ld_bar); };
-  auto load_h3 = [&](int64_t tl) { tc::bulk_g2s(H->h3, A.act_tiles + tl * 57344 + 40960, 16384, &H->ld_bar); };
+  const uint64_t pol = tc::l2_evict_first_policy();
+  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar, pol); };
+  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * 57344, 16384, &H->ld_bar, pol); };
+  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * 57344 + 16384, 8192, &H->ld_bar, pol); };
+  auto load_h2 = [&](int64_t tl) { tc::bulk_g2s(H->h2, A.act_tiles + tl * 57344 + 24576, 16384, &H->ld_bar, pol); };
+  auto load_h3 = [&](int64_t tl) { tc::bulk_g2s(H->h3, A.act_tiles + tl * 57344 + 40960, 16384, &H->ld_bar, pol); };
   {
     const int64_t tile0 = (int64_t)blockIdx.x * 2 + half;
     if (t == 0 && tile0 < n_tiles) {

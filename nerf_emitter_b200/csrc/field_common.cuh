@@ -273,7 +273,7 @@ __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const 
         dpre[ch] = c_raw < 1.6516e38f ? gc * c_raw : 0.f;
         seed_max = fmaxf(seed_max, fabsf(dpre[ch]));
       }
-      if (A.seeds4) A.seeds4[r * kS2 + si] = make_float4(dpre[0], dpre[1], dpre[2], dpre_sigma);
+      if (A.seeds4) __stcs(A.seeds4 + r * kS2 + si, make_float4(dpre[0], dpre[1], dpre[2], dpre_sigma));
       else A.g_sigma[r * kS2 + si] = gsig;
     }
   }

@@ -61,7 +61,7 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
         w[q] = tc::pack_h2(x0, x1);
       }
       *reinterpret_cast<uint4*>(a + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-      if (keep) keep[(c * 2 + hh) * 128 + row] = make_uint4(w[0], w[1], w[2], w[3]);   // same layout, for the backward
+      if (keep) __stcs(keep + (c * 2 + hh) * 128 + row, make_uint4(w[0], w[1], w[2], w[3]));   // same layout, for the backward
     }
   }
 }
@@ -178,7 +178,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         if (MODE == 1 && A.enc_tiles) {
           // keep the row and its Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles)
           const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
-          reinterpret_cast<uint4*>(A.enc_tiles + tile_id * 8192)[(l0 >> 2) * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
+          __stcs(reinterpret_cast<uint4*>(A.enc_tiles + tile_id * 8192) + (l0 >> 2) * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
           uint32_t wj[12];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -189,9 +189,9 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
             wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
           }
           uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * 24576) + (l0 >> 2) * 3 * 128 + tid;
-          jp[0] = make_uint4(wj[0], wj[1], wj[2], wj[3]);
-          jp[128] = make_uint4(wj[4], wj[5], wj[6], wj[7]);
-          jp[256] = make_uint4(wj[8], wj[9], wj[10], wj[11]);
+          __stcs(jp, make_uint4(wj[0], wj[1], wj[2], wj[3]));
+          __stcs(jp + 128, make_uint4(wj[4], wj[5], wj[6], wj[7]));
+          __stcs(jp + 256, make_uint4(wj[8], wj[9], wj[10], wj[11]));
         }
       }
       // adjoint-seed mode keeps the activations (fp16 operand rows) for k_field_backward_tc
@@ -216,7 +216,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-          if (act) reinterpret_cast<uint4*>(act + 16384)[hh * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
+          if (act) __stcs(reinterpret_cast<uint4*>(act + 16384) + hh * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
         }
         float gfe[16];
 #pragma unroll
@@ -227,7 +227,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-          if (act) reinterpret_cast<uint4*>(act + 16384)[(2 + hh) * 128 + tid] = make_uint4(w[0], w[1], w[2], w[3]);
+          if (act) __stcs(reinterpret_cast<uint4*>(act + 16384) + (2 + hh) * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
         }
       }
       // ---- head MLP ------------------------------------------------------------------------------------
