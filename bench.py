@@ -178,6 +178,7 @@ def workload_config(args, rays_per_gpu):
                                                "carry no autograd on this call, as in the reference's steady state"))
                             if args.mode == "fwd+bwd" else ""),
             "mode": args.mode, "rays_per_gpu": rays_per_gpu, "mlp_precision": args.precision,
+            "sampler": getattr(args, "sampler", None) or ("fast" if args.precision == "fp16" else "exact"),
             "l2_policy": "inputs+tables (%.0f MiB/step touched) exceed L2; no explicit flush" % (
                 (rays_per_gpu * (36 + 49 * 4 * 2) + 74 * 2 ** 20) / 2 ** 20),
             "parallelism": "ray-sharded x%d, weights replicated" % args.gpus}
@@ -194,6 +195,9 @@ def main():
     ap.add_argument("--mode", default=None, choices=["fwd", "fwd+bwd"])
     ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"],
                     help="MLP arithmetic of the main field: fp16 tensor-core (BASELINE configs[1]) or exact fp32")
+    ap.add_argument("--sampler", default=None, choices=["exact", "fast"],
+                    help="proposal sampler arithmetic: exact = the reference's fp32 CPU arithmetic (bit-equal indices), "
+                         "fast = packed-half proposal networks (autocast behaviour); default: fast with --precision fp16")
     ap.add_argument("--proposal-grad", action="store_true",
                     help="also back-propagate the interlevel loss into the proposal networks (the reference's sampler "
                          "only lets them carry autograd on its first call after an update step, SURVEY 8a quirk 13)")
@@ -223,6 +227,9 @@ def main():
     P = make_params(spec, seed=0, table_scale=1e3)
     E = NerfEmitter(P, spec, device=dev)
     E.set_precision(args.precision)
+    if args.sampler is None:
+        args.sampler = "fast" if args.precision == "fp16" else "exact"
+    E.set_sampler(args.sampler)
     n = args.rays
     o, v = make_rays(n, 1 + rank, dev)
     gout = torch.randn(n, 3, device=dev)

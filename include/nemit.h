@@ -136,6 +136,16 @@ int nemit_bind_grads(NemitHandle* h, const NemitParams* g);
 #define NEMIT_PRECISION_FP16_TC 1
 int nemit_set_precision(NemitHandle* h, int32_t precision);
 
+/* Arithmetic of the proposal-network sampler (ProposalNetworkSampler, NS/model_components/ray_samplers.py:584-626):
+ * NEMIT_SAMPLER_EXACT (default) reproduces the reference's fp32 CPU arithmetic operation by operation, so that the
+ * searchsorted indices are bit-equal (parity mode); NEMIT_SAMPLER_FAST evaluates the two proposal density fields
+ * (hash blend + 10->16->1 MLP) in packed half precision, which is what the reference does under torch.autocast /
+ * tiny-cuda-nn - sample positions then agree to ~1e-3 of a bin, not bit for bit.  The PDF resampling itself
+ * (cumsum / searchsorted) is the same code in both modes. */
+#define NEMIT_SAMPLER_EXACT 0
+#define NEMIT_SAMPLER_FAST 1
+int nemit_set_sampler(NemitHandle* h, int32_t sampler);
+
 /* bytes of scratch the calls below need for a batch of n rays (chunked internally) */
 size_t nemit_workspace_bytes(const NemitHandle* h, int64_t n);
 

@@ -34,6 +34,7 @@ struct NemitHandle {
   NemitParams P, G;
   int64_t launches;
   int precision;
+  int sampler;
   // optional per-kernel timing (nemit_profile_*): CUDA events around every launch on the launching stream
   bool profile;
   int n_pending;
@@ -189,6 +190,13 @@ extern "C" int nemit_bind_grads(NemitHandle* h, const NemitParams* g) {
   return NEMIT_OK;
 }
 extern "C" int64_t nemit_launch_count(const NemitHandle* h) { return h ? h->launches : 0; }
+extern "C" int nemit_set_sampler(NemitHandle* h, int32_t sampler) {
+  if (!h) return fail(NEMIT_E_INVALID, "nemit_set_sampler: null handle%s");
+  if (sampler != NEMIT_SAMPLER_EXACT && sampler != NEMIT_SAMPLER_FAST)
+    return fail(NEMIT_E_INVALID, "nemit_set_sampler: unknown sampler%s");
+  h->sampler = sampler;
+  return NEMIT_OK;
+}
 extern "C" int nemit_set_precision(NemitHandle* h, int32_t precision) {
   if (!h) return fail(NEMIT_E_INVALID, "nemit_set_precision: null handle%s");
   if (precision != NEMIT_PRECISION_FP32 && precision != NEMIT_PRECISION_FP16_TC)
@@ -308,7 +316,7 @@ extern "C" int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const 
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     offset_levels(S, out, off);
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream); });
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
   }
   return NEMIT_OK;
@@ -333,7 +341,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
     float* user_t = S.t_edges2;
     S.t_edges2 = t_edges;
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream); });
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     if (user_t) {
       e = cudaMemcpyAsync(user_t, t_edges, sizeof(float) * n * (kS2 + 1), cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
@@ -422,7 +430,7 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st); });
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st, h->sampler == NEMIT_SAMPLER_FAST); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     FieldArgs F;
     memset(&F, 0, sizeof(F));
@@ -465,7 +473,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     fill_sample_args(h, S, rays, off, n);
     S.t_edges2 = t_edges;
     S.s_edges2 = s_edges;
-    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st, h->sampler == NEMIT_SAMPLER_FAST); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     // pass 1: forward of the 48-sample stage + composite adjoint
     FieldArgs F;
     memset(&F, 0, sizeof(F));

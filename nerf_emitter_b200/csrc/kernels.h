@@ -121,7 +121,7 @@ struct FinalizeArgs : RayArgs {
   float* grad_v;
 };
 
-cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream);
+cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast = false);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);

@@ -7,18 +7,25 @@ namespace nemit {
 
 constexpr int kWarpsPerCta = 8;
 
+template <class MLP>
 struct SampleSmem {
-  PropMlpSmem mlp[2];
+  MLP mlp[2];
   WarpScratch warp[kWarpsPerCta];
 };
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+// MLP = PropMlpSmem: exact fp32 sampler (parity mode); PropMlpFastSmem: packed-half proposal networks (sampling.cuh)
+template <class MLP>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
 k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ SampleArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  SampleSmem* sm = reinterpret_cast<SampleSmem*>(smem_raw);
+  SampleSmem<MLP>* sm = reinterpret_cast<SampleSmem<MLP>*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  for (int i = 0; i < 2; ++i)
-    load_prop_mlp(&sm->mlp[i], A.prop_w0[i], A.prop_b0[i], A.prop_w1[i], A.prop_b1[i], tid, blockDim.x);
+  for (int i = 0; i < 2; ++i) {
+    if constexpr (cuda::std::is_same<MLP, PropMlpSmem>::value)
+      load_prop_mlp(&sm->mlp[i], A.prop_w0[i], A.prop_b0[i], A.prop_w1[i], A.prop_b1[i], tid, blockDim.x);
+    else
+      load_prop_mlp_fast(&sm->mlp[i], A.prop_w0[i], A.prop_b0[i], A.prop_w1[i], A.prop_b1[i], tid, blockDim.x);
+  }
   __syncthreads();
   WarpScratch* sc = &sm->warp[wid];
 
@@ -64,20 +71,24 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
   }
 }
 
-cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream) {
+template <class MLP>
+static cudaError_t launch_sample_levels_t(const ModelDev& M, const SampleArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static bool attr_set = false;
-  size_t smem = sizeof(SampleSmem);
+  size_t smem = sizeof(SampleSmem<MLP>);
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(k_sample_levels, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_sample_levels<MLP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
   int64_t ctas = (A.n + kWarpsPerCta - 1) / kWarpsPerCta;
   const int64_t max_ctas = 148 * 8 * 16;
   if (ctas > max_ctas) ctas = max_ctas;
-  k_sample_levels<<<(unsigned)ctas, kWarpsPerCta * 32, smem, stream>>>(M, A);
+  k_sample_levels<MLP><<<(unsigned)ctas, kWarpsPerCta * 32, smem, stream>>>(M, A);
   return cudaGetLastError();
+}
+cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast) {
+  return fast ? launch_sample_levels_t<PropMlpFastSmem>(M, A, stream) : launch_sample_levels_t<PropMlpSmem>(M, A, stream);
 }
 
 }  // namespace nemit

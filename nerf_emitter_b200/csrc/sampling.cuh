@@ -13,6 +13,8 @@
 // HashMLPDensityField.get_density (NS/fields/density_fields.py:95-122) and RaySamples.get_weights
 // (NS/cameras/rays.py:128-150).
 #pragma once
+#include <cuda_fp16.h>
+#include <cuda/std/type_traits>
 #include "common.cuh"
 
 namespace nemit {
@@ -83,6 +85,122 @@ static __device__ __noinline__ float prop_density(float x0, float x1, float x2, 
   return expf(prop_mlp_raw(enc, W));
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Fast proposal density (NEMIT_SAMPLER_FAST, the fp16 mode's sampler): same algorithm, packed-half arithmetic.
+// The two features of a table entry travel as one half2 through the trilinear blend (7 fused lerps instead of
+// 2 x 7 x (2 mul + add)), the 10 -> 16 -> 1 MLP runs on half2 pairs of hidden units (80 HFMA2 instead of 176 FFMA),
+// the contraction uses reciprocal approximations.  This is what the reference does under torch.autocast / tcnn
+// (fp16 proposal networks); sample indices are then no longer bit-equal to the fp32 CPU path, which is why the
+// exact sampler stays the default and the parity mode.
+// ---------------------------------------------------------------------------------------------------------
+struct PropMlpFastSmem {
+  __half2 w0[kPropEnc][8];   // [k][jp] = (W0[2jp][k], W0[2jp+1][k])
+  __half2 b0[8];
+  __half2 w1[8];
+  float b1;
+  float pad[3];
+};
+
+__device__ __forceinline__ void load_prop_mlp_fast(PropMlpFastSmem* dst, const float* __restrict__ w0,
+                                                   const float* __restrict__ b0, const float* __restrict__ w1,
+                                                   const float* __restrict__ b1, int tid, int nthreads) {
+  for (int i = tid; i < kPropEnc * 8; i += nthreads) {
+    int k = i / 8, jp = i % 8;
+    dst->w0[k][jp] = __floats2half2_rn(w0[(2 * jp) * kPropEnc + k], w0[(2 * jp + 1) * kPropEnc + k]);
+  }
+  for (int jp = tid; jp < 8; jp += nthreads) {
+    dst->b0[jp] = __floats2half2_rn(b0[2 * jp], b0[2 * jp + 1]);
+    dst->w1[jp] = __floats2half2_rn(w1[2 * jp], w1[2 * jp + 1]);
+  }
+  if (tid == 0) dst->b1 = b1[0];
+}
+
+// hash coordinates and fractions as level_cell, without the second rounding of ceil (x1 = x0 + (frac > 0))
+__device__ __forceinline__ __half2 lerp_h2(__half2 a_hi, __half2 b_lo, __half2 f) {
+  return __hfma2(f, __hsub2(a_hi, b_lo), b_lo);
+}
+__device__ __forceinline__ __half2 blend_cell_h2(const float2 v[8], const LevelCell& c) {
+  __half2 h[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) h[k] = __float22half2_rn(v[k]);
+  const __half2 fx = __float2half2_rn(c.fx), fy = __float2half2_rn(c.fy), fz = __float2half2_rn(c.fz);
+  const __half2 a = lerp_h2(h[0], h[1], fx), b = lerp_h2(h[2], h[3], fx);
+  const __half2 cc = lerp_h2(h[4], h[5], fx), d = lerp_h2(h[6], h[7], fx);
+  return lerp_h2(lerp_h2(a, b, fy), lerp_h2(cc, d, fy), fz);
+}
+
+__device__ __forceinline__ bool contract_normalise_fast(const float x[3], const ModelDev& M, float p[3]) {
+  const float mag = fmaxf(fabsf(x[0]), fmaxf(fabsf(x[1]), fabsf(x[2])));
+  float f = 1.f;
+  if (mag >= 1.f) {
+    const float inv = __frcp_rn(mag);
+    f = (2.f - inv) * inv;
+  }
+  bool sel = true;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    p[k] = fmaf(x[k], 0.25f * f, 0.5f);
+    sel = sel && (p[k] > 0.f) && (p[k] < 1.f);
+  }
+  if (M.disable_inside_aabb) {
+    bool inside = true;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) inside = inside && (x[k] > M.aabb_min[k]) && (x[k] < M.aabb_max[k]);
+    sel = sel && !inside;
+  }
+  return sel;
+}
+
+static __device__ __noinline__ float prop_density_fast(float x0, float x1, float x2, const float2* __restrict__ table,
+                                                       const GridDev& G, const PropMlpFastSmem* W, const ModelDev& M) {
+  float x[3] = {x0, x1, x2}, p[3];
+  if (!contract_normalise_fast(x, M, p)) return 0.f;
+  LevelCell cell[kPropLevels];
+  float2 v[kPropLevels][8];
+#pragma unroll
+  for (int l = 0; l < kPropLevels; ++l) {
+    level_cell(p, G.scal[l], G.table_mask, (uint32_t)l * G.table_size, cell[l]);
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v[l][c] = ldg_f2(table, cell[l].idx[c]);
+  }
+  __half2 acc[8];
+  {
+    const uint4* b0 = reinterpret_cast<const uint4*>(W->b0);
+    const uint4 t0 = b0[0], t1 = b0[1];
+    const uint32_t u[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+#pragma unroll
+    for (int jp = 0; jp < 8; ++jp) acc[jp] = *reinterpret_cast<const __half2*>(&u[jp]);
+  }
+#pragma unroll
+  for (int l = 0; l < kPropLevels; ++l) {
+    const __half2 e = blend_cell_h2(v[l], cell[l]);
+    const __half2 e0 = __low2half2(e), e1 = __high2half2(e);
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      const uint4* wr = reinterpret_cast<const uint4*>(W->w0[2 * l + f]);
+      const uint4 t0 = wr[0], t1 = wr[1];
+      const uint32_t u[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+      const __half2 ev = f == 0 ? e0 : e1;
+#pragma unroll
+      for (int jp = 0; jp < 8; ++jp) acc[jp] = __hfma2(*reinterpret_cast<const __half2*>(&u[jp]), ev, acc[jp]);
+    }
+  }
+  const uint4* w1p = reinterpret_cast<const uint4*>(W->w1);
+  const uint4 t0 = w1p[0], t1 = w1p[1];
+  const uint32_t u[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+  const __half2 zero = __float2half2_rn(0.f);
+  // the hidden -> 1 reduction in fp32: 16 terms of either sign
+  float raw = W->b1;
+#pragma unroll
+  for (int jp = 0; jp < 8; ++jp) {
+    const float2 h = __half22float2(__hmax2(acc[jp], zero));
+    const float2 w = __half22float2(*reinterpret_cast<const __half2*>(&u[jp]));
+    raw = fmaf(h.x, w.x, raw);
+    raw = fmaf(h.y, w.y, raw);
+  }
+  return __expf(raw);
+}
+
 // per-warp scratch of the proposal loop
 struct WarpScratch {
   float s_edge[kS0 + 4];   // spacing edges of the current level (S+1 used)
@@ -133,17 +251,24 @@ struct RayCtx {
 
 // One proposal level: density at the S bin midpoints -> weights (in sc->buf[0..S)).
 // Edges must be in sc->s_edge[0..S].  S is a multiple of 32.
+template <class MLP = PropMlpSmem>
 __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const RayCtx& R, int S,
                                                        const float2* __restrict__ table, const GridDev& G,
-                                                       const PropMlpSmem* W, const ModelDev& M, int lane,
+                                                       const MLP* W, const ModelDev& M, int lane,
                                                        float* ds_out = nullptr) {
+  constexpr bool kFast = !cuda::std::is_same<MLP, PropMlpSmem>::value;
 #pragma unroll 1
   for (int i = lane; i < S; i += 32) {
     float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far);
     float t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
     float tsum = add_rn(t0, t1);
-    float sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
-                               sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
+    float sigma;
+    if constexpr (kFast)
+      sigma = prop_density_fast(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
+                                sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
+    else
+      sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
+                           sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
     sc->buf[i] = mul_rn(sub_rn(t1, t0), sigma);
     if (ds_out) ds_out[i] = sc->buf[i];
   }

@@ -161,6 +161,14 @@ class NerfEmitter:
         self.precision = precision
         return self
 
+    def set_sampler(self, sampler: str = "exact"):
+        """'exact' = the reference's fp32 CPU arithmetic (bit-equal searchsorted indices, default); 'fast' = proposal
+        density fields in packed half precision (the reference's autocast / tcnn behaviour)."""
+        code = {"exact": 0, "fast": 1}[sampler]
+        L.check(self.lib.nemit_set_sampler(self._h, code), "nemit_set_sampler")
+        self.sampler = sampler
+        return self
+
     def train(self, mode: bool = True):
         self.training = bool(mode)
         return self

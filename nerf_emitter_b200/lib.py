@@ -84,6 +84,7 @@ SYMBOLS = {
                                 C.c_void_p]),
     "nemit_forward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_launch_count": (C.c_int64, [_H]),
+    "nemit_set_sampler": (C.c_int, [_H, C.c_int32]),
     "nemit_profile_enable": (C.c_int, [_H, C.c_int32]),
     "nemit_profile_read": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),
 }

@@ -177,3 +177,37 @@ def test_fp16_tensor_core_mode_psnr(spec, params_factory, emitters):
         psnr = 10 * math.log10(peak * peak / max(float(((out - ref) ** 2).mean()), 1e-30))
         print("table_scale %g: fp16-TC PSNR vs oracle %.1f dB, rel err %.2e" % (scale, psnr, rel_err(out, ref)))
         assert psnr >= 70.0 and rel_err(out, ref) < TOL
+
+
+def test_fast_sampler_mode(spec, params_factory, emitters):
+    """NEMIT_SAMPLER_FAST (proposal density fields in packed half precision, the reference's autocast / tcnn behaviour)
+    with the fp16 tensor-core field: stated bound PSNR >= 45 dB against the fp32 CPU oracle (peak = max radiance).  The
+    final sample edges stay ordered and stay close to the exact sampler's: median |dt| / bin width below 2e-2."""
+    import math
+    from oracle.nerfacto_oracle import OracleEmitter
+    for scale in (1e3, 1.0):
+        P = params_factory(0, scale)
+        O = OracleEmitter(P, spec)
+        E = emitters(0, scale)
+        O.train(False)
+        E.train(False)
+        o, v, _ = make_rays(2048, seed=12)
+        ref = O.render(o, v)
+        exact = E.sample_levels(o.cuda(), v.cuda(), edges_only=True)["t_edges2"].cpu()
+        E.set_precision("fp16")
+        E.set_sampler("fast")
+        try:
+            out = E.render(o.cuda(), v.cuda()).cpu()
+            fast = E.sample_levels(o.cuda(), v.cuda(), edges_only=True)["t_edges2"].cpu()
+        finally:
+            E.set_precision("fp32")
+            E.set_sampler("exact")
+        peak = float(ref.max())
+        psnr = 10 * math.log10(peak * peak / max(float(((out - ref) ** 2).mean()), 1e-30))
+        width = (exact[:, 1:] - exact[:, :-1]).clamp_min(1e-12)
+        shift = ((fast - exact).abs()[:, :-1] / width)
+        print("table_scale %g: fast sampler + fp16-TC PSNR vs oracle %.1f dB, rel err %.2e, median edge shift %.2e bins" % (
+            scale, psnr, rel_err(out, ref), float(shift.median())))
+        assert torch.isfinite(fast).all() and bool((fast[:, 1:] >= fast[:, :-1]).all())
+        assert psnr >= 45.0
+        assert float(shift.median()) < 2e-2
