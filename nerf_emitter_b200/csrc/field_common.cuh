@@ -163,6 +163,10 @@ __device__ __forceinline__ void load_field_weights(FieldWeightsSmem* S, const Fi
 // and the final weights of global ray r (chunk-local index).
 // Returns this lane's max |d/d(pre-activation)| over its samples: |dL/drgb| * rgb (SafeExp) and
 // |dL/dsigma| * exp(clamp(raw, -15, 15)) (trunc_exp) - the tensor-core backward scales its fp16 operands by it.
+// SCAN_DIST: the pairwise distortion term sum_j w_j |u_i - u_j| over the sorted midpoints u through two prefix sums,
+// u_i (2 A_i - A) + B - 2 B_i with A_i = sum_{j<i} w_j, B_i = sum_{j<i} w_j u_j (48 terms instead of 48^2; used by
+// the tensor-core seed pass; the fp32 kernels keep the reference's O(n^2) summation order).
+template <bool SCAN_DIST = false>
 __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const FieldArgs& A, const float* t_edge,
                                                        const float* s_edge, float* sigma, const float* rgb,
                                                        int64_t r, int lane) {
@@ -230,6 +234,23 @@ __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const 
   const float cnt = (float)min(chunk, A.n_total - c0);
   const float dm = M.distortion_mult / cnt;
   float gw[2], gww[2];
+  float pa[2] = {0.f, 0.f}, pb[2] = {0.f, 0.f}, at = 0.f, bt = 0.f;
+  if (SCAN_DIST) {
+    float um[2], wv[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      int si = k * 32 + lane;
+      um[k] = si < kS2 ? (s_edge[si] + s_edge[si + 1]) * 0.5f : 0.f;
+      wv[k] = si < kS2 ? w[k] : 0.f;
+    }
+    const float ia0 = warp_incl_scan_f(wv[0], lane), ib0 = warp_incl_scan_f(wv[0] * um[0], lane);
+    const float ta0 = __shfl_sync(0xffffffffu, ia0, 31), tb0 = __shfl_sync(0xffffffffu, ib0, 31);
+    const float ia1 = warp_incl_scan_f(wv[1], lane) + ta0, ib1 = warp_incl_scan_f(wv[1] * um[1], lane) + tb0;
+    at = __shfl_sync(0xffffffffu, ia1, 31);
+    bt = __shfl_sync(0xffffffffu, ib1, 31);
+    pa[0] = ia0 - wv[0]; pb[0] = ib0 - wv[0] * um[0];
+    pa[1] = ia1 - wv[1]; pb[1] = ib1 - wv[1] * um[1];
+  }
 #pragma unroll
   for (int k = 0; k < 2; ++k) {
     int si = k * 32 + lane;
@@ -237,10 +258,14 @@ __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const 
     if (si < kS2) {
       float ui = (s_edge[si] + s_edge[si + 1]) * 0.5f;
       float inter = 0.f;
+      if (SCAN_DIST) {
+        inter = fmaf(ui, 2.f * pa[k] - at, bt - 2.f * pb[k]);
+      } else {
 #pragma unroll 4
-      for (int j = 0; j < kS2; ++j) {
-        float uj = (s_edge[j] + s_edge[j + 1]) * 0.5f;
-        inter = fmaf(sigma[j], fabsf(ui - uj), inter);
+        for (int j = 0; j < kS2; ++j) {
+          float uj = (s_edge[j] + s_edge[j + 1]) * 0.5f;
+          inter = fmaf(sigma[j], fabsf(ui - uj), inter);
+        }
       }
       float dist = 2.f * inter + 2.f * w[k] * (s_edge[si + 1] - s_edge[si]) * (1.f / 3.f);
       gw[k] = gb[0] * (c[k][0] - last[0]) + gb[1] * (c[k][1] - last[1]) + gb[2] * (c[k][2] - last[2]) + dm * dist;

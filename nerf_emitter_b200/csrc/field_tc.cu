@@ -252,7 +252,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
     // composite: warp w handles rays w and w+4; lane handles samples lane and lane+32 (fp32, as field.cu)
     for (int rr = wid; rr < rays_here; rr += 4) {
       if (MODE == 1) {
-        seed_max = fmaxf(seed_max, composite_adjoint_ray(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)],
+        seed_max = fmaxf(seed_max, composite_adjoint_ray<true>(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)],
                                                          &sm->sigma[rr * kS2], &sm->rgb[rr * kS2 * 3], r0 + rr, lane));
         continue;
       }

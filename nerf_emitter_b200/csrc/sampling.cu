@@ -15,7 +15,7 @@ struct SampleSmem {
 
 // MLP = PropMlpSmem: exact fp32 sampler (parity mode); PropMlpFastSmem: packed-half proposal networks (sampling.cuh)
 template <class MLP>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 4)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 3)   // 80 registers: measured best for both variants (4 -> spills, 2 -> too few warps)
 k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ SampleArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SampleSmem<MLP>* sm = reinterpret_cast<SampleSmem<MLP>*>(smem_raw);
