@@ -282,7 +282,7 @@ def main():
     value = n * world / (ms_per_step * 1e-3)
 
     # per-kernel timing for the roofline (forward kernels timed alone on this stream, same inputs)
-    roof = kernel_roofline(prof, n, args.steps)
+    roof = kernel_roofline(prof, n, args.steps, args.mode)
 
     # e2e: the same step through the public API with pinned HOST buffers, copies inside the timed region
     oh = o.cpu().pin_memory()
@@ -353,7 +353,7 @@ def backward_available():
         return False
 
 
-def kernel_roofline(prof, n, steps):
+def kernel_roofline(prof, n, steps, mode="fwd+bwd"):
     """Roofline of the dominant kernel from the library's own CUDA-event records of the timed region
     (events recorded on the launching stream around every launch; nemit_profile_read)."""
     hbm, src = measured_peaks()
@@ -362,7 +362,7 @@ def kernel_roofline(prof, n, steps):
     for k, v in kern.items():
         v["share"] = v["ms_total"] / total
         # rays one launch processed, and the kernel's own algorithmic GB/s
-        v["rays_per_launch"] = n * steps * PASSES.get(k, 1) / v["launches"]
+        v["rays_per_launch"] = n * steps * (PASSES.get(k, 1) if mode == "fwd+bwd" else 1) / v["launches"]
         v["achieved_gbs"] = ALG_BYTES[k] * v["rays_per_launch"] / (v["ms_per_launch"] * 1e-3) / 1e9
     dom = max(kern, key=lambda k: kern[k]["ms_total"])
     alg = ALG_BYTES[dom]

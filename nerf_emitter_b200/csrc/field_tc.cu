@@ -68,17 +68,25 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
 
 // make this thread's A-operand writes visible to the tensor core, then let one thread issue the layer
 template <int N, int K>
-__device__ __forceinline__ void run_layer(TcSmem* sm, const uint8_t* b, uint32_t tmem, uint32_t& phase, int tid) {
+__device__ __forceinline__ void run_layer(TcSmem* sm, const uint8_t* b, uint32_t tmem, uint32_t& phase, int tid,
+                                          uint8_t* keep = nullptr, uint32_t keep_bytes = 0, uint64_t policy = 0) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
   __syncthreads();
   if (tid == 0) {
     tc::tc_fence_after();
     tc::issue_layer<N, K>(tmem, sm->a, b, &sm->mbar);
+    if (keep) {
+      // adjoint-seed mode: the A operand (= this layer's input rows, already in the tile layout) goes to the
+      // workspace through the TMA engine; the operand buffer is reused once the engine has read it
+      tc::bulk_s2g(keep, sm->a, keep_bytes, policy);
+      tc::bulk_wait_read();
+    }
   }
   tc::mbar_wait(&sm->mbar, phase);
   phase ^= 1u;
   tc::tc_fence_after();
+  if (keep) __syncthreads();
 }
 
 // MODE 0: forward.  MODE 1: first pass of the backward (same forward, then the per-ray composite adjoint).
@@ -128,6 +136,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   const uint32_t tmem = sm->tmem_slot;
   const uint32_t taddr = tmem + ((uint32_t)(wid * 32) << 16);   // this warp's 32 TMEM lanes
   uint32_t phase = 0;
+  const uint64_t policy = MODE == 1 ? tc::l2_evict_first_policy() : 0;
 
   const int64_t n_groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
@@ -157,6 +166,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
       for (int k = 0; k < 3; ++k) x[k] = sample_pos(sm->ray_o[rr * 3 + k], sm->ray_d[rr * 3 + k], tsum);
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
+      const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
       // ---- hash encoding: 4 levels = 8 values = one 16-byte K-chunk of this thread's A row ------------
 #pragma unroll 1
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
@@ -177,8 +187,6 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, l0 >> 2)) = make_uint4(w[0], w[1], w[2], w[3]);
         if (MODE == 1 && A.enc_tiles) {
           // keep the row and its Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles)
-          const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
-          __stcs(reinterpret_cast<uint4*>(A.enc_tiles + tile_id * 8192) + (l0 >> 2) * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
           uint32_t wj[12];
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -196,11 +204,11 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       }
       // adjoint-seed mode keeps the activations (fp16 operand rows) for k_field_backward_tc
       uint8_t* act = nullptr;
-      if (MODE == 1 && A.act_tiles) act = A.act_tiles + (g * (kGroupSamples / kTileM) + tile) * 57344;
+      if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * 57344;
       // ---- base MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32>(sm, sm->b1, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_b0, sm->a, tid, act ? reinterpret_cast<uint4*>(act) : nullptr);
-      run_layer<16, 64>(sm, sm->b2, tmem, phase, tid);
+      run_layer<64, 32>(sm, sm->b1, tmem, phase, tid, act ? A.enc_tiles + tile_id * 8192 : nullptr, 8192, policy);
+      epilogue_hidden(taddr, sm->bias_b0, sm->a, tid);
+      run_layer<16, 64>(sm, sm->b2, tmem, phase, tid, act, 16384, policy);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
@@ -216,7 +224,6 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-          if (act) __stcs(reinterpret_cast<uint4*>(act + 16384) + hh * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
         }
         float gfe[16];
 #pragma unroll
@@ -227,15 +234,14 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
           for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
           *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-          if (act) __stcs(reinterpret_cast<uint4*>(act + 16384) + (2 + hh) * 128 + tid, make_uint4(w[0], w[1], w[2], w[3]));
         }
       }
       // ---- head MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32>(sm, sm->b3, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_h0, sm->a, tid, act ? reinterpret_cast<uint4*>(act + 24576) : nullptr);
-      run_layer<64, 64>(sm, sm->b4, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_h1, sm->a, tid, act ? reinterpret_cast<uint4*>(act + 40960) : nullptr);
-      run_layer<16, 64>(sm, sm->b5, tmem, phase, tid);
+      run_layer<64, 32>(sm, sm->b3, tmem, phase, tid, act ? act + 16384 : nullptr, 8192, policy);
+      epilogue_hidden(taddr, sm->bias_h0, sm->a, tid);
+      run_layer<64, 64>(sm, sm->b4, tmem, phase, tid, act ? act + 24576 : nullptr, 16384, policy);
+      epilogue_hidden(taddr, sm->bias_h1, sm->a, tid);
+      run_layer<16, 64>(sm, sm->b5, tmem, phase, tid, act ? act + 40960 : nullptr, 16384, policy);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
