@@ -99,7 +99,15 @@ typedef struct NemitRays {
                             deterministic bins (ray_samplers.py:107-117, 323-333). The host draws
                             them from the samplers' own generators. */
   float anneal;          /* ProposalNetworkSampler._anneal (ray_samplers.py:609); 1.0 = no-op */
+  int32_t layout;        /* NEMIT_RAYS_MITSUBA_3N (0, default): o, v as above, what the dr.CustomOp passes;
+                            NEMIT_RAYS_NERF_N3: o, v are RayBundle.origins / .directions, (N,3) rows already in NeRF
+                            coordinates (NS/cameras/rays.py:170-200), i.e. the model-level entry points
+                            get_rgb_for_camera_ray_bundle / forward_grad_for_camera_ray_bundle /
+                            backward_for_camera_ray_bundle (NS/models/base_model.py:290-344,
+                            NS/pipelines/mitsuba_sdf.py:1144-1219); tangents and ray gradients then use (N,3) too */
 } NemitRays;
+#define NEMIT_RAYS_MITSUBA_3N 0
+#define NEMIT_RAYS_NERF_N3 1
 
 /* Optional per-level outputs of the proposal loop, for parity tests and for
  * ProposalNetworkSampler's return value (ray_samplers.py:584-626). Any pointer may be NULL. */
@@ -183,6 +191,46 @@ int nemit_backward(NemitHandle* h, const NemitRays* rays, const float* grad_rgb,
  * x (n,3) in [0,1]; out (n, 2*num_levels). which: 0 = main grid, 1/2 = proposal grids. */
 int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, int64_t n, float* out,
                       void* stream);
+
+/* ---- component-level drop-ins (SURVEY.md 8b "Model-side API kept intact"): what the nerfstudio modules'
+ * forward() dispatches to when a module is called on its own, outside the fused emitter query ---- */
+
+/* HashEncoding.forward for any grid / table (NS/field_components/encodings.py:341-382): x (n,3) in [0,1],
+ * table (num_levels << log2_table_size, 2), out (n, 2*num_levels). */
+int nemit_hash_encode_grid(const NemitGrid* grid, const float* table, const float* x, int64_t n, float* out,
+                           void* stream);
+
+/* SHEncoding.forward, torch path (NS/field_components/encodings.py:708-716 -> components_from_spherical_harmonics,
+ * NS/utils/math.py:27-90): d (n,3), out (n, levels^2), levels in 1..4. */
+int nemit_sh_encode(const float* d, int64_t n, int32_t levels, float* out, void* stream);
+
+/* MLP.forward, torch path (NS/field_components/mlp.py:163-183): nn.Linear layers in torch (out,in) layout,
+ * `activation` between layers and `out_activation` after the last (0 = none, 1 = ReLU); widths <= 64. */
+#define NEMIT_MLP_MAX_LAYERS 8
+#define NEMIT_MLP_MAX_WIDTH 64
+typedef struct NemitMlp {
+  int32_t in_dim;
+  int32_t num_layers;
+  int32_t out_dim[NEMIT_MLP_MAX_LAYERS];
+  const float* weight[NEMIT_MLP_MAX_LAYERS];   /* (out_dim[l], in) */
+  const float* bias[NEMIT_MLP_MAX_LAYERS];     /* (out_dim[l]) or NULL */
+  int32_t activation;
+  int32_t out_activation;
+} NemitMlp;
+int nemit_mlp(const NemitMlp* mlp, const float* x, int64_t n, float* out, void* stream);
+
+/* Field.density_fn (NS/fields/base_field.py:49-69) on explicit positions (n,3) in NeRF coordinates:
+ * which = 0: NerfactoField.get_density (NS/fields/nerfacto_field.py:228-256), geo_or_null (n,15) receives the
+ * geometry features; which = 1/2: HashMLPDensityField.get_density (NS/fields/density_fields.py:95-122). */
+int nemit_density_fn(NemitHandle* h, int32_t which, const float* positions, int64_t n, float* density,
+                     float* geo_or_null, void* stream);
+
+/* NerfactoField.forward(ray_samples) = get_density + get_outputs (NS/fields/base_field.py:124-143,
+ * NS/fields/nerfacto_field.py:228-334) on explicit sample positions and directions (n,3):
+ * density (n), rgb (n,3) (SafeExp output, HDR).  training selects the appearance row camera_idx, otherwise
+ * the mean embedding (nerfacto_field.py:272-285). */
+int nemit_field_samples(NemitHandle* h, const float* positions, const float* directions, int64_t n,
+                        int32_t camera_idx, int32_t training, float* density, float* rgb, void* stream);
 
 /* vMF-mixture emitter: VonMisesFisherEmitter.sample_direction / pdf_direction
  * (DS/emitters/vMF.py:24-81).  lobes: position (K,3), weight (K) unnormalised, std (K).

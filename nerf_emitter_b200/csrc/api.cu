@@ -266,13 +266,15 @@ static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who)
   if (r->training && (r->camera_idx < 0 || r->camera_idx >= h->cfg.num_images))
     return fail(NEMIT_E_INVALID, "%s: camera_idx outside the appearance embedding", who);
   if (!(r->anneal > 0.f)) return fail(NEMIT_E_INVALID, "%s: anneal must be > 0", who);
+  if (r->layout != NEMIT_RAYS_MITSUBA_3N && r->layout != NEMIT_RAYS_NERF_N3)
+    return fail(NEMIT_E_INVALID, "%s: unknown ray layout", who);
   return NEMIT_OK;
 }
 
 static void fill_ray_args(RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
   A.o = r->o; A.v = r->v; A.near_per_ray = r->near_per_ray; A.near_scalar = r->near_scalar;
   A.n_total = r->n; A.ray_offset = off; A.n = n; A.training = r->training; A.camera_idx = r->camera_idx;
-  A.jitter = r->jitter; A.anneal = r->anneal;
+  A.jitter = r->jitter; A.anneal = r->anneal; A.nerf_layout = r->layout == NEMIT_RAYS_NERF_N3;
 }
 
 static void fill_sample_args(const NemitHandle* h, SampleArgs& S, const NemitRays* r, int64_t off, int64_t n) {
@@ -373,6 +375,86 @@ extern "C" int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, 
   const float* t = which == 0 ? h->P.main_table : h->P.prop_table[which - 1];
   cudaError_t e = launch_hash_encode(G, reinterpret_cast<const float2*>(t), x, n, out, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "k_hash_encode");
+  h->launches++;
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// component-level drop-ins (components.cu)
+// ---------------------------------------------------------------------------------------------
+extern "C" int nemit_hash_encode_grid(const NemitGrid* grid, const float* table, const float* x, int64_t n, float* out,
+                                      void* stream) {
+  if (!grid || n < 0 || (n > 0 && (!table || !x || !out))) return fail(NEMIT_E_INVALID, "nemit_hash_encode_grid: null argument%s");
+  if (grid->num_levels < 1 || grid->num_levels > NEMIT_MAX_LEVELS || grid->log2_table_size < 1 || grid->log2_table_size > 31)
+    return fail(NEMIT_E_INVALID, "nemit_hash_encode_grid: 1..16 levels and 2^1..2^31 table entries per level%s");
+  GridDev G;
+  grid_to_dev(*grid, G);
+  cudaError_t e = launch_hash_encode(G, reinterpret_cast<const float2*>(table), x, n, out, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_hash_encode");
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_sh_encode(const float* d, int64_t n, int32_t levels, float* out, void* stream) {
+  if (n < 0 || (n > 0 && (!d || !out))) return fail(NEMIT_E_INVALID, "nemit_sh_encode: null argument%s");
+  if (levels < 1 || levels > 4) return fail(NEMIT_E_INVALID, "nemit_sh_encode: levels must be in 1..4%s");
+  cudaError_t e = launch_sh_encode(d, n, levels, out, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_sh_encode");
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_mlp(const NemitMlp* mlp, const float* x, int64_t n, float* out, void* stream) {
+  if (!mlp || n < 0 || (n > 0 && (!x || !out))) return fail(NEMIT_E_INVALID, "nemit_mlp: null argument%s");
+  if (mlp->num_layers < 1 || mlp->num_layers > NEMIT_MLP_MAX_LAYERS || mlp->in_dim < 1 || mlp->in_dim > NEMIT_MLP_MAX_WIDTH)
+    return fail(NEMIT_E_INVALID, "nemit_mlp: 1..8 layers, widths 1..64%s");
+  MlpDev L;
+  memset(&L, 0, sizeof(L));
+  L.in_dim = mlp->in_dim; L.num_layers = mlp->num_layers;
+  L.activation = mlp->activation; L.out_activation = mlp->out_activation;
+  if ((L.activation | L.out_activation) & ~1) return fail(NEMIT_E_INVALID, "nemit_mlp: activation must be 0 (none) or 1 (ReLU)%s");
+  for (int l = 0; l < mlp->num_layers; ++l) {
+    if (mlp->out_dim[l] < 1 || mlp->out_dim[l] > NEMIT_MLP_MAX_WIDTH) return fail(NEMIT_E_INVALID, "nemit_mlp: 1..8 layers, widths 1..64%s");
+    if (!mlp->weight[l]) return fail(NEMIT_E_INVALID, "nemit_mlp: null weight%s");
+    L.out_dim[l] = mlp->out_dim[l]; L.weight[l] = mlp->weight[l]; L.bias[l] = mlp->bias[l];
+  }
+  cudaError_t e = launch_mlp(L, x, n, out, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_mlp");
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_density_fn(NemitHandle* h, int32_t which, const float* positions, int64_t n, float* density,
+                                float* geo_or_null, void* stream) {
+  if (!h || n < 0 || (n > 0 && (!positions || !density))) return fail(NEMIT_E_INVALID, "nemit_density_fn: null argument%s");
+  if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_density_fn: parameters not bound%s");
+  if (which < 0 || which > 2) return fail(NEMIT_E_INVALID, "nemit_density_fn: which must be 0, 1 or 2%s");
+  cudaSetDevice(h->device);
+  cudaError_t e;
+  if (which == 0) {
+    FieldParams P;
+    fill_field_params(h->P, P);
+    e = launch_field_samples(h->M, P, positions, nullptr, n, 0, 0, density, geo_or_null, nullptr, (cudaStream_t)stream);
+  } else {
+    const int i = which - 1;
+    e = launch_prop_density(h->M, h->M.prop_grid[i], reinterpret_cast<const float2*>(h->P.prop_table[i]), h->P.prop_w0[i],
+                            h->P.prop_b0[i], h->P.prop_w1[i], h->P.prop_b1[i], positions, n, density, (cudaStream_t)stream);
+  }
+  if (e != cudaSuccess) return cuda_fail(e, "nemit_density_fn");
+  h->launches++;
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_field_samples(NemitHandle* h, const float* positions, const float* directions, int64_t n,
+                                   int32_t camera_idx, int32_t training, float* density, float* rgb, void* stream) {
+  if (!h || n < 0 || (n > 0 && (!positions || !directions || !density || !rgb)))
+    return fail(NEMIT_E_INVALID, "nemit_field_samples: null argument%s");
+  if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_field_samples: parameters not bound%s");
+  if (training && (camera_idx < 0 || camera_idx >= h->cfg.num_images))
+    return fail(NEMIT_E_INVALID, "nemit_field_samples: camera_idx outside the appearance embedding%s");
+  cudaSetDevice(h->device);
+  FieldParams P;
+  fill_field_params(h->P, P);
+  cudaError_t e = launch_field_samples(h->M, P, positions, directions, n, training, camera_idx, density, nullptr, rgb,
+                                       (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_field_samples");
   h->launches++;
   return NEMIT_OK;
 }

@@ -152,7 +152,7 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
     const int si = valid ? (int)(s % kS2) : 0;
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, t0 = 0.f, t1 = 0.f;
     if (valid) {
-      load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, M.scene_scale, o, d);
+      load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, ray_scale(M, A), o, d);
       t0 = A.t_edges2[rr * (kS2 + 1) + si];
       t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
     }
@@ -338,6 +338,19 @@ __global__ void k_finalize_ray_grads(const __grid_constant__ ModelDev M, const _
     const float* g = A.ray_grad + r * 6;
     const int64_t R = A.ray_offset + r;
     const float nr = A.near_per_ray ? A.near_per_ray[R] : A.near_scalar;
+    if (A.nerf_layout) {
+      // backward_for_camera_ray_bundle leaves (N,3) gradients in ray_bundle.origins.grad / .directions.grad
+      // (NS/pipelines/mitsuba_sdf.py:1144-1219), NeRF coordinates, inf/nan scrubbed (:1206-1214)
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        float a = g[k], b = g[3 + k];
+        if (!isfinite(a)) a = 0.f;
+        if (!isfinite(b)) b = 0.f;
+        A.grad_o[R * 3 + k] = a;
+        A.grad_v[R * 3 + k] = b + nr * a;
+      }
+      continue;
+    }
     // nerf (x,y,z) = mitsuba (z,x,y):  g_mi[0] = g_nerf[1], g_mi[1] = g_nerf[2], g_mi[2] = g_nerf[0]
     float go[3] = {g[1], g[2], g[0]}, gv[3] = {g[4], g[5], g[3]};
 #pragma unroll

@@ -216,7 +216,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, t0 = 0.f, t1 = 0.f;
     float4 seed = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
-      load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, M.scene_scale, o, d);
+      load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, ray_scale(M, A), o, d);
       t0 = A.t_edges2[rr * (kS2 + 1) + si];
       t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
       seed = __ldcs(A.seeds4 + s);

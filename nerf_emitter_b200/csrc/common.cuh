@@ -76,6 +76,12 @@ __device__ __forceinline__ void load_ray(const float* __restrict__ o, const floa
                                          const float* __restrict__ near_per_ray, float near_scalar,
                                          int64_t n, int64_t r, float scene_scale, float oo[3], float dd[3]) {
   float nr = near_per_ray ? near_per_ray[r] : near_scalar;
+  if (scene_scale == 0.f) {
+    // NEMIT_RAYS_NERF_N3 (kernels.h ray_scale): RayBundle.origins / .directions, (N,3) rows already in NeRF coordinates
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { dd[k] = v[r * 3 + k]; oo[k] = add_rn(o[r * 3 + k], mul_rn(nr, dd[k])); }
+    return;
+  }
   float vm[3] = {v[r], v[n + r], v[2 * n + r]};
   float om[3];
 #pragma unroll

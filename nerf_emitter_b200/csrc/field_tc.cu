@@ -146,7 +146,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
     if (tid < kRaysPerGroup) {
       float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
       if (tid < rays_here) load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r0 + tid,
-                                    M.scene_scale, o, d);
+                                    ray_scale(M, A), o, d);
 #pragma unroll
       for (int k = 0; k < 3; ++k) { sm->ray_o[tid * 3 + k] = o[k]; sm->ray_d[tid * 3 + k] = d[k]; }
     }

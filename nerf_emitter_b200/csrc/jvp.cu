@@ -69,16 +69,22 @@ k_field_jvp(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArg
       float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, dot[3] = {0.f, 0.f, 0.f}, ddt[3] = {0.f, 0.f, 0.f};
       if (tid < rays_here) {
         const int64_t R = A.ray_offset + r0 + tid;
-        load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, R, M.scene_scale, o, d);
+        load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, R, ray_scale(M, A), o, d);
         const float nr = A.near_per_ray ? A.near_per_ray[R] : A.near_scalar;
         float dom[3], dvm[3];
+        if (A.nerf_layout) {
+          // forward_grad_for_camera_ray_bundle (NS/models/base_model.py:315-344): (N,3) tangents in NeRF coordinates
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          dvm[k] = A.d_v[k * A.n_total + R];
-          dom[k] = 2.f * M.scene_scale * (A.d_o[k * A.n_total + R] + nr * dvm[k]);   // nerf_emitter_op.py:69
+          for (int k = 0; k < 3; ++k) { ddt[k] = A.d_v[R * 3 + k]; dot[k] = A.d_o[R * 3 + k] + nr * ddt[k]; }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            dvm[k] = A.d_v[k * A.n_total + R];
+            dom[k] = 2.f * M.scene_scale * (A.d_o[k * A.n_total + R] + nr * dvm[k]);   // nerf_emitter_op.py:69
+          }
+          dot[0] = dom[2]; dot[1] = dom[0]; dot[2] = dom[1];
+          ddt[0] = dvm[2]; ddt[1] = dvm[0]; ddt[2] = dvm[1];
         }
-        dot[0] = dom[2]; dot[1] = dom[0]; dot[2] = dom[1];
-        ddt[0] = dvm[2]; ddt[1] = dvm[0]; ddt[2] = dvm[1];
       }
 #pragma unroll
       for (int k = 0; k < 3; ++k) {

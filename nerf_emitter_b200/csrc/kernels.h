@@ -18,7 +18,10 @@ struct RayArgs {
   int camera_idx;
   const float* jitter;   // (n_total,3) or null
   float anneal;
+  int nerf_layout;       // NemitRays.layout: 0 = (3,N) Mitsuba unit cube, 1 = (N,3) NeRF coordinates (also for tangents / ray grads)
 };
+// the scene_scale argument of load_ray; 0 selects the (N,3) NeRF-coordinate layout
+__host__ __device__ inline float ray_scale(const ModelDev& M, const RayArgs& A) { return A.nerf_layout ? 0.f : M.scene_scale; }
 
 struct SampleArgs : RayArgs {
   const float2* prop_table[2];
@@ -121,6 +124,23 @@ struct FinalizeArgs : RayArgs {
   float* grad_v;
 };
 
+// generic small MLP (component drop-in), torch (out,in) weights
+struct MlpDev {
+  int in_dim, num_layers;
+  int out_dim[NEMIT_MLP_MAX_LAYERS];
+  const float* weight[NEMIT_MLP_MAX_LAYERS];
+  const float* bias[NEMIT_MLP_MAX_LAYERS];
+  int activation, out_activation;
+};
+
+cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const float* pos, const float* dir, int64_t n,
+                                 int training, int camera_idx, float* density, float* geo, float* rgb,
+                                 cudaStream_t stream);
+cudaError_t launch_prop_density(const ModelDev& M, const GridDev& G, const float2* table, const float* w0,
+                                const float* b0, const float* w1, const float* b1, const float* pos, int64_t n,
+                                float* density, cudaStream_t stream);
+cudaError_t launch_sh_encode(const float* d, int64_t n, int levels, float* out, cudaStream_t stream);
+cudaError_t launch_mlp(const MlpDev& L, const float* x, int64_t n, float* out, cudaStream_t stream);
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast = false);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);

@@ -226,7 +226,7 @@ k_prop_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Prop
   for (int64_t r = (int64_t)blockIdx.x * kPbWarps + wid; r < A.n; r += (int64_t)gridDim.x * kPbWarps) {
     RayCtx R;
     const int64_t rg = A.ray_offset + r;
-    load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, rg, M.scene_scale, R.o, R.d);
+    load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, rg, ray_scale(M, A), R.o, R.d);
     const float near = A.training ? M.near_plane : 0.f;
     R.s_near = spacing_fwd(near);
     R.s_far = spacing_fwd(M.far_plane);

@@ -32,7 +32,7 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
 #pragma unroll 1
   for (int64_t r = (int64_t)blockIdx.x * kWarpsPerCta + wid; r < A.n; r += (int64_t)gridDim.x * kWarpsPerCta) {
     RayCtx R;
-    load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r, M.scene_scale, R.o, R.d);
+    load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r, ray_scale(M, A), R.o, R.d);
     const float near = A.training ? M.near_plane : 0.f;      // NearFarCollider, scene_colliders.py:217-222
     R.s_near = spacing_fwd(near);
     R.s_far = spacing_fwd(M.far_plane);

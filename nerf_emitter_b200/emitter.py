@@ -186,11 +186,14 @@ class NerfEmitter:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _rays(self, o3n, v3n, near, camera_idx, jitter) -> L.NemitRays:
-        n = o3n.shape[1]
-        _check(o3n, (3, n), "o")
-        _check(v3n, (3, n), "v")
+    def _rays(self, o3n, v3n, near, camera_idx, jitter, nerf_layout: bool = False) -> L.NemitRays:
+        """nerf_layout: o, v are RayBundle.origins / .directions, (N,3) rows in NeRF coordinates (NEMIT_RAYS_NERF_N3)
+        instead of the CustomOp's (3,N) Mitsuba unit-cube arrays."""
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        _check(o3n, (n, 3) if nerf_layout else (3, n), "o")
+        _check(v3n, (n, 3) if nerf_layout else (3, n), "v")
         R = L.NemitRays()
+        R.layout = int(nerf_layout)
         R.o, R.v, R.n = o3n.data_ptr(), v3n.data_ptr(), n
         self._keep = [o3n, v3n]
         if isinstance(near, torch.Tensor):
@@ -233,10 +236,10 @@ class NerfEmitter:
 
     # -- the three modes -------------------------------------------------------------------
     def render(self, o3n: torch.Tensor, v3n: torch.Tensor, near=0.0, camera_idx: int = 0, jitter=None,
-               return_aux: bool = False):
+               return_aux: bool = False, nerf_layout: bool = False):
         """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> rgb (N,3)."""
-        n = o3n.shape[1]
-        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
         rgb = torch.empty(n, 3, device=self.device, dtype=torch.float32)
         ws = self._workspace(n)
         if not return_aux:
@@ -251,11 +254,12 @@ class NerfEmitter:
         aux["accumulation"] = acc
         return rgb, aux
 
-    def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None, edges_only: bool = False):
+    def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None, edges_only: bool = False,
+                      nerf_layout: bool = False):
         """ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) for emitter rays.
         edges_only: write just the final 49 euclidean edges (what the field kernel consumes)."""
-        n = o3n.shape[1]
-        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
         if edges_only:
             aux = dict(t_edges2=torch.empty(n, self.spec.num_nerf_samples + 1, device=self.device))
             LO = L.NemitLevelsOut()
@@ -267,12 +271,12 @@ class NerfEmitter:
                 "nemit_sample_levels")
         return aux
 
-    def jvp(self, o3n, v3n, do3n, dv3n, near=0.0, camera_idx: int = 0, jitter=None):
+    def jvp(self, o3n, v3n, do3n, dv3n, near=0.0, camera_idx: int = 0, jitter=None, nerf_layout: bool = False):
         """NeRFEmitterOp.ns_forward_ray (nerf_emitter_op.py:60-90): tangents (3,N) -> d_rgb (N,3)."""
-        n = o3n.shape[1]
-        R = self._rays(o3n, v3n, near, camera_idx, jitter)
-        _check(do3n, (3, n), "d_o")
-        _check(dv3n, (3, n), "d_v")
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
+        _check(do3n, tuple(o3n.shape), "d_o")
+        _check(dv3n, tuple(o3n.shape), "d_v")
         out = torch.empty(n, 3, device=self.device, dtype=torch.float32)
         ws = self._workspace(n)
         L.check(self.lib.nemit_jvp(self._h, C.byref(R), _ptr(do3n), _ptr(dv3n), _ptr(out), _ptr(ws), ws.numel(),
@@ -280,16 +284,17 @@ class NerfEmitter:
         return out
 
     def backward(self, o3n, v3n, grad_rgb, near=0.0, camera_idx: int = 0, jitter=None,
-                 chunk_rays: Optional[int] = None, loss_scale: float = 1.0, proposal_requires_grad: bool = True):
+                 chunk_rays: Optional[int] = None, loss_scale: float = 1.0, proposal_requires_grad: bool = True,
+                 nerf_layout: bool = False):
         """NeRFEmitterOp.ns_backward_ray (nerf_emitter_op.py:92-117): returns (grad_o, grad_v) as (3,N);
         parameter gradients are accumulated into the bound ``grads``."""
         if not self.grads:
             self.bind_grads()
-        n = o3n.shape[1]
-        R = self._rays(o3n, v3n, near, camera_idx, jitter)
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
         _check(grad_rgb, (n, 3), "grad_rgb")
-        go = torch.empty(3, n, device=self.device, dtype=torch.float32)
-        gv = torch.empty(3, n, device=self.device, dtype=torch.float32)
+        go = torch.empty_like(o3n)
+        gv = torch.empty_like(o3n)
         ws = self._workspace(n)
         L.check(self.lib.nemit_backward(self._h, C.byref(R), _ptr(grad_rgb), int(chunk_rays or n), float(loss_scale),
                                         int(proposal_requires_grad), _ptr(go), _ptr(gv), _ptr(ws), ws.numel(),
@@ -320,6 +325,34 @@ class NerfEmitter:
         out = torch.empty(n, g.num_levels * g.features_per_level, device=self.device, dtype=torch.float32)
         L.check(self.lib.nemit_hash_encode(self._h, which, _ptr(x), n, _ptr(out), self._stream()), "nemit_hash_encode")
         return out
+
+    def density_fn(self, positions: torch.Tensor, which: int = 0, return_geo: bool = False):
+        """Field.density_fn (NS/fields/base_field.py:49-69) on (n,3) NeRF-coordinate positions: which = 0 the main
+        field (nerfacto_field.py:228-256), 1/2 the proposal fields (density_fields.py:95-122).  -> (n,1)."""
+        shape = positions.shape[:-1]
+        x = positions.reshape(-1, 3).contiguous()
+        n = x.shape[0]
+        _check(x, (n, 3), "positions")
+        den = torch.empty(n, device=self.device, dtype=torch.float32)
+        geo = torch.empty(n, self.spec.geo_feat_dim, device=self.device) if (return_geo and which == 0) else None
+        L.check(self.lib.nemit_density_fn(self._h, int(which), _ptr(x), n, _ptr(den), _ptr(geo), self._stream()),
+                "nemit_density_fn")
+        den = den.view(*shape, 1)
+        return (den, geo.view(*shape, -1)) if geo is not None else den
+
+    def field_samples(self, positions: torch.Tensor, directions: torch.Tensor, camera_idx: int = 0):
+        """NerfactoField.forward on explicit samples: positions, directions (...,3) -> density (...,1), rgb (...,3)."""
+        shape = positions.shape[:-1]
+        x = positions.reshape(-1, 3).contiguous()
+        d = directions.reshape(-1, 3).contiguous()
+        n = x.shape[0]
+        _check(x, (n, 3), "positions")
+        _check(d, (n, 3), "directions")
+        den = torch.empty(n, device=self.device, dtype=torch.float32)
+        rgb = torch.empty(n, 3, device=self.device, dtype=torch.float32)
+        L.check(self.lib.nemit_field_samples(self._h, _ptr(x), _ptr(d), n, int(camera_idx), int(self.training),
+                                             _ptr(den), _ptr(rgb), self._stream()), "nemit_field_samples")
+        return den.view(*shape, 1), rgb.view(*shape, 3)
 
     def profile(self, on: bool = True):
         """Per-kernel CUDA-event timing inside the library (on the launching stream)."""

@@ -46,12 +46,22 @@ class NemitParams(C.Structure):
 class NemitRays(C.Structure):
     _fields_ = [("o", C.c_void_p), ("v", C.c_void_p), ("near_per_ray", C.c_void_p), ("near_scalar", C.c_float),
                 ("n", C.c_int64), ("camera_idx", C.c_int32), ("training", C.c_int32), ("jitter", C.c_void_p),
-                ("anneal", C.c_float)]
+                ("anneal", C.c_float), ("layout", C.c_int32)]
 
 
 class NemitLevelsOut(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in
                 ["weights0", "weights1", "s_edges1", "s_edges2", "t_edges2", "inds1", "inds2", "weights2"]]
+
+
+MLP_MAX_LAYERS = 8
+MLP_MAX_WIDTH = 64
+
+
+class NemitMlp(C.Structure):
+    _fields_ = [("in_dim", C.c_int32), ("num_layers", C.c_int32), ("out_dim", C.c_int32 * MLP_MAX_LAYERS),
+                ("weight", C.c_void_p * MLP_MAX_LAYERS), ("bias", C.c_void_p * MLP_MAX_LAYERS),
+                ("activation", C.c_int32), ("out_activation", C.c_int32)]
 
 
 class NemitVmfLobes(C.Structure):
@@ -78,6 +88,12 @@ SYMBOLS = {
     "nemit_backward": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_hash_encode": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "nemit_hash_encode_grid": (C.c_int, [C.POINTER(NemitGrid), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "nemit_sh_encode": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "nemit_mlp": (C.c_int, [C.POINTER(NemitMlp), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "nemit_density_fn": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nemit_field_samples": (C.c_int, [_H, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                      C.c_void_p, C.c_void_p]),
     "nemit_vmf_sample": (C.c_int, [C.POINTER(NemitVmfLobes), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                    C.c_void_p, C.c_void_p]),
     "nemit_vmf_pdf": (C.c_int, [C.POINTER(NemitVmfLobes), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
