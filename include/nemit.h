@@ -192,6 +192,15 @@ int nemit_backward(NemitHandle* h, const NemitRays* rays, const float* grad_rgb,
 int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, int64_t n, float* out,
                       void* stream);
 
+/* Light-point-cloud pass: SdfNerfactoModel.get_point_lights (NS/models/sdf_nerfacto.py:189-212) =
+ * proposal sampling + calc_brightness_grad (NS/models/nerfacto.py:547-573) + DepthRenderer("contrib")
+ * (NS/model_components/renderers.py:389-397).  rgb_weights: 3 HOST floats (0.299, 0.587, 0.114 in the reference);
+ * rgb (N,3) composited radiance; depth (N) = midpoint of the sample with the largest weight * luminance;
+ * brightness_grad = d sum(rgb * rgb_weights) / d origins in the rays' own layout ((3,N) or (N,3)), t^2 gradient
+ * scaling applied as in the reference's reverse mode.  No parameter gradient is touched. */
+int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const float* rgb_weights, float* rgb, float* depth,
+                       float* brightness_grad, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- component-level drop-ins (SURVEY.md 8b "Model-side API kept intact"): what the nerfstudio modules'
  * forward() dispatches to when a module is called on its own, outside the fused emitter query ---- */
 

@@ -622,6 +622,85 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
 }
 
 // ---------------------------------------------------------------------------------------------
+// light-point-cloud pass: SdfNerfactoModel.get_point_lights (NS/models/sdf_nerfacto.py:189-212)
+// ---------------------------------------------------------------------------------------------
+extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const float* rgb_weights, float* rgb,
+                                  float* depth, float* brightness_grad, void* workspace, size_t workspace_bytes,
+                                  void* stream) {
+  int rc = check_rays(h, rays, "nemit_point_lights");
+  if (rc) return rc;
+  if (rays->n == 0) return NEMIT_OK;
+  if (!rgb_weights || !rgb || !depth || !brightness_grad) return fail(NEMIT_E_INVALID, "nemit_point_lights: null argument%s");
+  WsLayout L = ws_layout(rays->n);
+  if (!workspace || workspace_bytes < L.total)
+    return fail(NEMIT_E_WORKSPACE, "nemit_point_lights: workspace too small%s (need %lld bytes)", "", (long long)L.total);
+  cudaSetDevice(h->device);
+  char* ws = static_cast<char*>(workspace);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  ModelDev M = h->M;
+  M.distortion_mult = 0.f;           // the objective is the brightness alone (nerfacto.py:562-568): no regularisers
+  const bool tc = h->precision == NEMIT_PRECISION_FP16_TC;
+  for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
+    int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
+    float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
+    float* s_edges = reinterpret_cast<float*>(ws + L.s_edges2);
+    float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
+    float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
+    float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
+    float* g_absmax = reinterpret_cast<float*>(ws + L.g_absmax);
+    SampleArgs S;
+    fill_sample_args(h, S, rays, off, n);
+    S.t_edges2 = t_edges;
+    S.s_edges2 = s_edges;
+    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(M, S, st, h->sampler == NEMIT_SAMPLER_FAST); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    FieldArgs F;
+    memset(&F, 0, sizeof(F));
+    fill_ray_args(F, rays, off, n);
+    fill_field_params(h->P, F.P);
+    F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.reg_chunk = rays->n;
+    F.point_lights = 1;
+    for (int k = 0; k < 3; ++k) F.lum_w[k] = rgb_weights[k];
+    F.rgb = rgb + off * 3; F.depth = depth + off;
+    if (tc) {
+      if ((e = cudaMemsetAsync(g_absmax, 0, sizeof(float), st)) != cudaSuccess) return cuda_fail(e, "memset g_absmax");
+      F.g_absmax = g_absmax;
+      F.enc_tiles = reinterpret_cast<uint8_t*>(ws + L.enc_tiles);
+      F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
+      F.act_tiles = reinterpret_cast<uint8_t*>(ws + L.act_tiles);
+      F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(M, F, st); });
+    } else {
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(M, F, st); });
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
+    if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
+    FieldBwdArgs B;
+    memset(&B, 0, sizeof(B));       // B.G stays null: ray gradients only
+    fill_ray_args(B, rays, off, n);
+    fill_field_params(h->P, B.P);
+    B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = 1.f;
+    if (tc) {
+      B.g_absmax = g_absmax;
+      B.enc_tiles = reinterpret_cast<const uint8_t*>(ws + L.enc_tiles);
+      B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
+      B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
+      B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(M, B, st); });
+    } else {
+      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(M, B, st); });
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "k_field_backward");
+    FinalizeArgs Z;
+    memset(&Z, 0, sizeof(Z));
+    fill_ray_args(Z, rays, off, n);
+    Z.ray_grad = ray_grad; Z.grad_o = brightness_grad; Z.grad_v = nullptr;
+    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
+  }
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // vMF mixture (DS/emitters/vMF.py)
 // ---------------------------------------------------------------------------------------------
 static int check_lobes(const NemitVmfLobes* l, const char* who) {

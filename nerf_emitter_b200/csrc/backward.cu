@@ -254,8 +254,10 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
           float cw[8];
           corner_weights(cell[j], cw);
           const float gxs = g.x * A.loss_scale, gys = g.y * A.loss_scale;
+          if (A.G.main_table) {        // null in the ray-gradient-only pass (nemit_point_lights)
 #pragma unroll
-          for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell[j].idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+            for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell[j].idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+          }
           if (sel) {
             float2 dx, dy, dz;
             blend_cell_grad(v[j], cell[j], dx, dy, dz);
@@ -283,6 +285,7 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
 
   // ---- flush this CTA's weight-gradient accumulators (torch layouts, GradScaler scale applied) ------
   __syncthreads();
+  if (!A.G.main_table) return;
   const float ls = A.loss_scale;
   const FieldWeightsSmem& D = sm->dW;
   for (int i = tid; i < kHidden * kMainEnc; i += 128) { int n = i / kMainEnc, k = i % kMainEnc; atomicAdd(A.G.base_w0 + i, ls * D.base_w0[k * kHidden + n]); }
@@ -347,7 +350,7 @@ __global__ void k_finalize_ray_grads(const __grid_constant__ ModelDev M, const _
         if (!isfinite(a)) a = 0.f;
         if (!isfinite(b)) b = 0.f;
         A.grad_o[R * 3 + k] = a;
-        A.grad_v[R * 3 + k] = b + nr * a;
+        if (A.grad_v) A.grad_v[R * 3 + k] = b + nr * a;
       }
       continue;
     }
@@ -360,7 +363,7 @@ __global__ void k_finalize_ray_grads(const __grid_constant__ ModelDev M, const _
       if (!isfinite(a)) a = 0.f;
       if (!isfinite(b)) b = 0.f;
       A.grad_o[k * A.n_total + R] = a - nr * b;
-      A.grad_v[k * A.n_total + R] = b;
+      if (A.grad_v) A.grad_v[k * A.n_total + R] = b;
     }
   }
 }

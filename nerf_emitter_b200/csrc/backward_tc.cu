@@ -321,7 +321,9 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           // differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
           const float xs = mul_rn(p[0], sc);
           const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
-          if (pair) {
+          if (!A.G.main_table) {
+            // ray-gradient-only pass (nemit_point_lights): no parameter gradients
+          } else if (pair) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               const uint32_t ia = cell.idx[2 * q], ib = cell.idx[2 * q + 1];
@@ -360,7 +362,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   }
 
   // ---- flush this half's weight-gradient accumulators (torch layouts, loss scale applied) ---------------
-  if (!first) {
+  if (!first && A.G.main_table) {
     tc::tc_fence_before();
     half_sync(half);
     tc::tc_fence_after();

@@ -183,6 +183,30 @@ __device__ __forceinline__ float2 blend_cell(const float2 v[8], const LevelCell&
 
 __device__ __forceinline__ float2 ldg_f2(const float2* __restrict__ t, uint32_t i) { return __ldg(t + i); }
 
+// The 8 corner entries of one cell.  The x-neighbours (ceil x, floor x) of a (y, z) pair hash to indices that differ
+// in bit 0 only whenever floor x is even, i.e. they are one aligned 16-byte pair of the table: those lanes fetch the pair
+// with ONE 128-bit load, the others with two 64-bit loads, predicated per lane into the same four registers.  An
+// L1-missing lane-load costs 1.0 SM-cycle whatever its width and an L1-hitting one 0.34 (tools/gather_bench.cu,
+// profiles/r1_gather_bench.txt), so this removes a quarter of the pair cost on half of the pairs.
+__device__ __forceinline__ void gather_cell(const float2* __restrict__ t, const LevelCell& c, float2 v[8]) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint32_t ic = c.idx[2 * q], il = c.idx[2 * q + 1];       // ceil-x corner, floor-x corner
+    const uint32_t pair = (ic ^ il) == 1u;
+    float2 a, b;                 // pair: (a, b) = (even entry, odd entry); otherwise (floor corner, ceil corner)
+    if (pair) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(t + (il & ~1u)));
+      a = make_float2(w.x, w.y); b = make_float2(w.z, w.w);
+    } else {
+      a = __ldg(t + il); b = __ldg(t + ic);
+    }
+    const float a0 = a.x, a1 = a.y, b0 = b.x, b1 = b.y;
+    const bool swap = pair && (il & 1u);
+    v[2 * q + 1] = swap ? make_float2(b0, b1) : make_float2(a0, a1);
+    v[2 * q] = swap ? make_float2(a0, a1) : make_float2(b0, b1);
+  }
+}
+
 // torch.nan_to_num defaults: nan -> 0, +inf -> FLT_MAX, -inf -> -FLT_MAX
 __device__ __forceinline__ float nan_to_num(float x) {
   if (isnan(x)) return 0.f;

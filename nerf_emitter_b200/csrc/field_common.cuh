@@ -222,7 +222,39 @@ __device__ __forceinline__ float composite_adjoint_ray(const ModelDev& M, const 
   }
   const float bg = 1.f - acc;
   const int64_t rg = A.ray_offset + r;
-  float gb[3] = {A.grad_rgb[rg * 3 + 0], A.grad_rgb[rg * 3 + 1], A.grad_rgb[rg * 3 + 2]};
+  float gb[3];
+  if (A.point_lights) {
+    // brightness = sum(rgb * rgb_weights): the seed is the weight vector itself (nerfacto.py:562-568).  The pass also
+    // returns the composite (renderer_rgb, clamp / nan_to_num in eval mode as in the forward) and the depth of the sample
+    // with the largest weight * luminance(field_rgb) ("contrib" DepthRenderer, renderers.py:389-397; first index on ties)
+    gb[0] = A.lum_w[0]; gb[1] = A.lum_w[1]; gb[2] = A.lum_w[2];
+    float best = -INFINITY;
+    int best_i = kS2;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      int si = k * 32 + lane;
+      if (si < kS2) {
+        const float lum = rgb[si * 3 + 0] * A.lum_w[0] + rgb[si * 3 + 1] * A.lum_w[1] + rgb[si * 3 + 2] * A.lum_w[2];
+        const float cv = w[k] * lum;
+        if (cv > best || (cv == best && si < best_i)) { best = cv; best_i = si; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, best_i, o);
+      if (ob > best || (ob == best && oi < best_i)) { best = ob; best_i = oi; }
+    }
+    if (lane == 0) {
+      if (best_i >= kS2) best_i = 0;       // all-NaN contributions
+      float pr = cr + last[0] * bg, pg = cg + last[1] * bg, pb = cb + last[2] * bg;
+      if (eval) { pr = fmaxf(pr, 0.f); pg = fmaxf(pg, 0.f); pb = fmaxf(pb, 0.f); }
+      A.rgb[r * 3 + 0] = pr; A.rgb[r * 3 + 1] = pg; A.rgb[r * 3 + 2] = pb;
+      A.depth[r] = (t_edge[best_i] + t_edge[best_i + 1]) * 0.5f;
+    }
+  } else {
+    gb[0] = A.grad_rgb[rg * 3 + 0]; gb[1] = A.grad_rgb[rg * 3 + 1]; gb[2] = A.grad_rgb[rg * 3 + 2];
+  }
   if (eval) {   // clamp(min=0) passes the gradient where the composite is >= 0
     if (!(cr + last[0] * bg >= 0.f)) gb[0] = 0.f;
     if (!(cg + last[1] * bg >= 0.f)) gb[1] = 0.f;

@@ -175,8 +175,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           level_cell(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
-#pragma unroll
-          for (int c = 0; c < 8; ++c) v[j][c] = ldg_f2(A.P.main_table, cell[j].idx[c]);
+          gather_cell(A.P.main_table, cell[j], v[j]);
         }
         uint32_t w[4];
 #pragma unroll

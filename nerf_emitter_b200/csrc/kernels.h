@@ -81,6 +81,12 @@ struct FieldArgs : RayArgs {
   // d loss / d (rgb pre-activation xyz, density pre-activation w) per sample, i.e. the seeds with the SafeExp /
   // trunc_exp derivatives and the selector already applied (written instead of g_sigma / g_rgbs when set)
   float4* seeds4;
+  // light-point-cloud pass (SdfNerfactoModel.get_point_lights, NS/models/sdf_nerfacto.py:189-212): the adjoint seed is
+  // the same luminance weight vector for every ray (calc_brightness_grad, NS/models/nerfacto.py:547-573), the pass also
+  // writes the composited rgb and the "contrib" depth (DepthRenderer, NS/model_components/renderers.py:389-397)
+  int point_lights;
+  float lum_w[3];
+  float* depth;            // (n)
 };
 
 // gradient accumulators in the torch parameter layouts (atomically accumulated)

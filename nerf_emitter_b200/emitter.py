@@ -301,6 +301,21 @@ class NerfEmitter:
                                         self._stream()), "nemit_backward")
         return go, gv
 
+    def point_lights(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None, rgb_weights=(0.299, 0.587, 0.114),
+                     nerf_layout: bool = False):
+        """SdfNerfactoModel.get_point_lights (NS/models/sdf_nerfacto.py:189-212): {rgb (N,3), depth (N,1) of the sample
+        with the largest weight * luminance, brightness_grad = d luminance / d origins (layout of ``o3n``)}."""
+        n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
+        rgb = torch.empty(n, 3, device=self.device, dtype=torch.float32)
+        depth = torch.empty(n, 1, device=self.device, dtype=torch.float32)
+        bg = torch.empty_like(o3n)
+        ws = self._workspace(n)
+        w = (C.c_float * 3)(*[float(x) for x in rgb_weights])
+        L.check(self.lib.nemit_point_lights(self._h, C.byref(R), w, _ptr(rgb), _ptr(depth), _ptr(bg), _ptr(ws), ws.numel(),
+                                            self._stream()), "nemit_point_lights")
+        return {"rgb": rgb, "depth": depth, "brightness_grad": bg}
+
     def render_host(self, o_host: torch.Tensor, v_host: torch.Tensor, rgb_host: torch.Tensor, near: float = 0.0,
                     camera_idx: int = 0):
         """End-to-end call with pinned HOST buffers (nemit_forward_host): H2D, forward, D2H on the stream."""

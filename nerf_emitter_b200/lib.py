@@ -88,6 +88,8 @@ SYMBOLS = {
     "nemit_backward": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_hash_encode": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "nemit_point_lights": (C.c_int, [_H, C.POINTER(NemitRays), C.POINTER(C.c_float), C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_hash_encode_grid": (C.c_int, [C.POINTER(NemitGrid), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_sh_encode": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_mlp": (C.c_int, [C.POINTER(NemitMlp), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),

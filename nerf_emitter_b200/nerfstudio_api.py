@@ -444,6 +444,14 @@ class SdfNerfactoModel(nn.Module):
 
     forward_grad = forward_grad_for_camera_ray_bundle
 
+    @torch.no_grad()
+    def get_point_lights(self, ray_bundle: RayBundle, jitter=None) -> Dict[str, torch.Tensor]:
+        """sdf_nerfacto.py:189-212: {"rgb", "depth" (contrib), "brightness_grad"} for the light point cloud
+        (NS/model_components/output_light_pc.py:74-173)."""
+        E = self._emitter()
+        return E.point_lights(_cuda_f32(ray_bundle.origins, "origins"), _cuda_f32(ray_bundle.directions, "directions"),
+                              camera_idx=ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
+
     def backward_for_camera_ray_bundle(self, camera_ray_bundle: RayBundle, grad_out: torch.Tensor, jitter=None,
                                        loss_scale: float = 1.0) -> None:
         """MitsubaSdfPipeline.backward_for_camera_ray_bundle (mitsuba_sdf.py:1144-1219): accumulates into

@@ -482,3 +482,28 @@ class OracleEmitter:
         finally:
             self.P = saved
         return go.t().contiguous(), gv.t().contiguous(), grads, rgb.detach()
+
+    def point_lights(self, o3n, v3n, near=0.0, camera_idx=0, jitter=None, rgb_weights=(0.299, 0.587, 0.114)):
+        """SdfNerfactoModel.get_point_lights (nerfstudio/models/sdf_nerfacto.py:189-212) =
+        proposal sampling (no grad) + NerfactoModel.calc_brightness_grad (nerfstudio/models/nerfacto.py:547-573:
+        field + t^2 gradient scaling + get_weights + RGBRenderer, brightness = sum(rgb * rgb_weights),
+        autograd.grad w.r.t. ray_bundle.origins with the samples' directions NOT carrying the origin) +
+        DepthRenderer(method="contrib") (nerfstudio/model_components/renderers.py:389-397).
+        Returns rgb (N,3), depth (N,1), brightness_grad (N,3) in NeRF coordinates (d / d ray_bundle.origins)."""
+        wts = torch.tensor(rgb_weights, dtype=torch.float32)
+        o = o3n.t().contiguous()
+        v = v3n.t().contiguous()
+        o, d = rays_mi_to_nerf(o + near * v, v, self.scene_scale)
+        o = o.detach().requires_grad_(True)
+        lv = self._levels(o.detach(), d, jitter)
+        t_edges = lv["t_edges"][2]
+        rgb, w, _, rgb_s = main_stage(self.P, self.spec, o, d, t_edges, self.aabb, training=self.training,
+                                      camera_idx=camera_idx, disable_inside_aabb=self.disable_inside_aabb)
+        brightness = torch.sum(rgb * wts, dim=-1, keepdim=True)
+        (grad,) = torch.autograd.grad(brightness, o, grad_outputs=torch.ones_like(brightness))
+        lum = torch.sum(rgb_s.detach() * wts, dim=-1, keepdim=True)
+        steps = (t_edges[..., :-1, None] + t_edges[..., 1:, None]) / 2
+        contrib = torch.sum(w.detach() * lum, dim=-1)
+        idx = torch.max(contrib, dim=-1, keepdim=True).indices
+        depth = torch.gather(steps[..., 0], dim=-1, index=idx)
+        return {"rgb": rgb.detach(), "depth": depth, "brightness_grad": grad, "contrib": contrib}

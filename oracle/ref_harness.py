@@ -197,6 +197,28 @@ class ReferenceEmitter:
         return go.t().contiguous(), gv.t().contiguous(), grads, rgb.detach()
 
 
+def reference_point_lights(R: "ReferenceEmitter", o3n, v3n, near=0.0, camera_idx=0, rgb_weights=(0.299, 0.587, 0.114)):
+    """SdfNerfactoModel.get_point_lights (nerfstudio/models/sdf_nerfacto.py:189-212) with the reference's own field,
+    sampler, renderers (RGBRenderer, DepthRenderer("contrib")) and autograd; only the glue of get_point_lights /
+    calc_brightness_grad (nerfstudio/models/nerfacto.py:547-573) is restated (un-importable file)."""
+    ns = R.ns
+    wts = torch.tensor(rgb_weights, dtype=torch.float32)
+    o = o3n.t().contiguous() + near * v3n.t().contiguous()
+    rb = R.collider(R.get_ray_bundle(o, v3n.t().contiguous(), camera_idx))
+    with torch.no_grad():
+        rs, _, _ = R.sampler(rb, density_fns=R._density_fns())
+    with torch.enable_grad():
+        rb.origins.requires_grad = True
+        rs.frustums.origins = rb.origins.unsqueeze(-2).expand_as(rs.frustums.origins)
+        rs.frustums.directions = rb.directions.unsqueeze(-2).expand_as(rs.frustums.directions)
+        rgb, weights, out = R._field_and_render(rs)
+        brightness = torch.sum(rgb * wts, dim=-1, keepdim=True)
+        (grad,) = torch.autograd.grad(brightness, rb.origins, grad_outputs=torch.ones_like(brightness))
+    lum = torch.sum(out[ns.FieldHeadNames.RGB] * wts, dim=-1, keepdim=True)
+    depth = ns.renderers.DepthRenderer(method="contrib")(weights=weights.detach(), ray_samples=rs, values=lum.detach())
+    return {"rgb": rgb.detach(), "depth": depth.detach(), "brightness_grad": grad.detach()}
+
+
 class _PatchedRand:
     """Feeds explicit per-ray jitter (3 tensors (N,1): level 0, pdf 1, pdf 2) to the samplers in
     training mode instead of their private generators (ray_samplers.py:107-117, 323-333)."""

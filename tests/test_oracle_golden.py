@@ -71,3 +71,18 @@ def test_known_answer_sh_orthonormal():
     sh = sh16(d)
     gram = (sh.t() @ sh) / N * 4 * torch.pi
     assert torch.allclose(gram, torch.eye(16), atol=1e-2)
+
+
+@pytest.mark.parametrize("case", ["point_lights_stress", "point_lights_default_init"])
+def test_point_lights_oracle_matches_reference_golden(case, spec, params_factory):
+    """Light-point-cloud pass (sdf_nerfacto.py:189-212) against vectors frozen from the reference's own classes
+    (oracle/make_golden_point_lights.py)."""
+    import numpy as np
+    from helpers import T, load_golden, rel_err
+    from oracle.nerfacto_oracle import OracleEmitter
+    G = load_golden(case)
+    O = OracleEmitter(params_factory(int(G["param_seed"]), float(G["table_scale"])), spec)
+    out = O.point_lights(T(G["o"]), T(G["v"]))
+    assert rel_err(out["rgb"], G["rgb"]) < 1e-6
+    assert np.array_equal(out["depth"].numpy(), G["depth"])
+    assert rel_err(out["brightness_grad"], G["brightness_grad"]) < 1e-5

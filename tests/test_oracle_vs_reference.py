@@ -44,3 +44,17 @@ def test_grid_scalings_match_reference(spec):
         enc = ns.encodings.HashEncoding(num_levels=g.num_levels, min_res=g.base_res, max_res=g.max_res,
                                         log2_hashmap_size=4, implementation="torch")
         assert [float(x) for x in enc.scalings] == g.scalings()
+
+
+def test_point_lights_oracle_equals_reference_live(spec, params_factory):
+    """get_point_lights (sdf_nerfacto.py:189-212): rgb, contrib depth and d luminance / d origins."""
+    from oracle.nerfacto_oracle import OracleEmitter
+    from oracle.ref_harness import ReferenceEmitter, reference_point_lights
+    P = params_factory(0, 1e3)
+    R = ReferenceEmitter(P, spec)
+    O = OracleEmitter(P, spec)
+    o, v, _ = make_rays(200, seed=21)
+    a = reference_point_lights(R, o, v)
+    b = O.point_lights(o, v)
+    assert torch.equal(a["rgb"], b["rgb"]) and torch.equal(a["depth"], b["depth"])
+    assert rel_err(b["brightness_grad"], a["brightness_grad"]) < 1e-5
