@@ -201,6 +201,24 @@ int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, int64_t n, 
 int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const float* rgb_weights, float* rgb, float* depth,
                        float* brightness_grad, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Optimizer step on the bound parameters / gradients: Optimizers.optimizer_scaler_step_all
+ * (NS/engine/optimizers.py:122-137, called from NS/engine/trainer.py:517-537) for the two parameter groups of
+ * NS/models/nerfacto.py:313-317 with the hyper-parameters of NS/configs/method_configs.py:331-342:
+ * GradScaler.unscale_ (grad / grad_scale + non-finite check) -> clip_grad_norm_(group, max_norm) ->
+ * clip_grad_value_(group, max_value) -> torch.optim.Adam step (skipped when a non-finite gradient was found),
+ * in place on the borrowed tensors.  exp_avg / exp_avg_sq: Adam state in the parameter layouts (caller-owned,
+ * zero-initialised); step: 1-based step count of this update; lr: the scheduler's current value
+ * (NS/engine/schedulers.py:156-193); max_norm / max_value <= 0 disable the clip; zero_grads != 0 clears the
+ * gradients in the same pass (optimizer.zero_grad).  stats_or_null: device float[4] = {sum g^2 fields,
+ * sum g^2 proposal_networks, non-finite flag, 0} for GradScaler.update / logging. */
+typedef struct NemitAdamGroup {
+  double lr, beta1, beta2, eps;   /* python floats in torch.optim.Adam: 1 - beta is formed in double, as torch does */
+  float max_norm, max_value;
+} NemitAdamGroup;
+int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const NemitParams* exp_avg_sq,
+                    const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t step,
+                    float grad_scale, int32_t zero_grads, float* stats_or_null, void* stream);
+
 /* ---- component-level drop-ins (SURVEY.md 8b "Model-side API kept intact"): what the nerfstudio modules'
  * forward() dispatches to when a module is called on its own, outside the fused emitter query ---- */
 

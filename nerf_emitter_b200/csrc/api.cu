@@ -1,5 +1,6 @@
 // api.cu - the C ABI of libnerfemitter.so (include/nemit.h): handle, argument checks, chunking,
 // workspace carving, kernel launches.  No torch types, no allocation of parameter memory.
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -30,6 +31,7 @@ struct NemitHandle {
   const float* lin0;
   const float* u1;
   const float* u2;
+  double* opt_stats;        // 4 doubles of optimizer-step scratch (tail of tables_dev)
   bool params_bound, grads_bound;
   NemitParams P, G;
   int64_t launches;
@@ -144,7 +146,7 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   h->M.interlevel_mult = cfg->interlevel_mult;
   h->M.distortion_mult = cfg->distortion_mult;
   const int n0 = kS0 + 1, n1 = kS1 + 1, n2 = kS2 + 1;
-  if ((e = cudaMalloc(&h->tables_dev, sizeof(float) * (n0 + n1 + n2))) != cudaSuccess) {
+  if ((e = cudaMalloc(&h->tables_dev, sizeof(float) * (n0 + n1 + n2 + 9))) != cudaSuccess) {
     delete h;
     return cuda_fail(e, "cudaMalloc(sampler tables)");
   }
@@ -155,6 +157,7 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   h->lin0 = h->tables_dev;
   h->u1 = h->tables_dev + n0;
   h->u2 = h->tables_dev + n0 + n1;
+  h->opt_stats = reinterpret_cast<double*>(h->tables_dev + ((n0 + n1 + n2 + 1) & ~1));   // 8-byte aligned tail
   *out = h;
   return NEMIT_OK;
 }
@@ -697,6 +700,65 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     Z.ray_grad = ray_grad; Z.grad_o = brightness_grad; Z.grad_v = nullptr;
     if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// optimizer step (optim.cu)
+// ---------------------------------------------------------------------------------------------
+extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const NemitParams* exp_avg_sq,
+                               const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t step,
+                               float grad_scale, int32_t zero_grads, float* stats_or_null, void* stream) {
+  if (!h || !exp_avg || !exp_avg_sq || !fields || !proposal_networks) return fail(NEMIT_E_INVALID, "nemit_adam_step: null argument%s");
+  if (!h->params_bound || !h->grads_bound) return fail(NEMIT_E_UNBOUND, "nemit_adam_step: parameters and gradients must be bound%s");
+  if (!params_complete(exp_avg) || !params_complete(exp_avg_sq)) return fail(NEMIT_E_INVALID, "nemit_adam_step: an optimizer-state pointer is null%s");
+  if (step < 1) return fail(NEMIT_E_INVALID, "nemit_adam_step: step counts from 1%s");
+  if (!(grad_scale > 0.f)) return fail(NEMIT_E_INVALID, "nemit_adam_step: grad_scale must be > 0%s");
+  cudaSetDevice(h->device);
+  const NemitConfig& c = h->cfg;
+  const int64_t main_n = ((int64_t)c.main_grid.num_levels << c.main_grid.log2_table_size) * 2;
+  const int64_t enc = c.main_grid.num_levels * 2, hd = c.hidden_dim, head_in = 16 + c.geo_feat_dim + c.appearance_dim;
+  const int64_t numel_main[12] = {main_n, hd * enc, hd, (1 + c.geo_feat_dim) * hd, 1 + c.geo_feat_dim, hd * head_in, hd,
+                                  hd * hd, hd, 3 * hd, 3, (int64_t)c.num_images * c.appearance_dim};
+  OptimArgs A;
+  memset(&A, 0, sizeof(A));
+  float* const* P = reinterpret_cast<float* const*>(&h->P);
+  float* const* G = reinterpret_cast<float* const*>(&h->G);
+  float* const* M1 = reinterpret_cast<float* const*>(exp_avg);
+  float* const* M2 = reinterpret_cast<float* const*>(exp_avg_sq);
+  int t = 0;
+  for (int i = 0; i < 12; ++i, ++t) {
+    A.param[t] = P[i]; A.grad[t] = G[i]; A.exp_avg[t] = M1[i]; A.exp_avg_sq[t] = M2[i]; A.numel[t] = numel_main[i]; A.group[t] = 0;
+  }
+  // NemitParams tail: prop_table[2], prop_w0[2], prop_b0[2], prop_w1[2], prop_b1[2]
+  for (int f = 0; f < 5; ++f)
+    for (int i = 0; i < 2; ++i, ++t) {
+      const NemitGrid& g = c.prop_grid[i];
+      const int64_t pe = g.num_levels * 2, ph = c.prop_hidden_dim;
+      const int64_t nn[5] = {((int64_t)g.num_levels << g.log2_table_size) * 2, ph * pe, ph, ph, 1};
+      const int k = 12 + f * 2 + i;
+      A.param[t] = P[k]; A.grad[t] = G[k]; A.exp_avg[t] = M1[k]; A.exp_avg_sq[t] = M2[k]; A.numel[t] = nn[f]; A.group[t] = 1;
+    }
+  A.num_tensors = t;
+  const NemitAdamGroup* src[2] = {fields, proposal_networks};
+  for (int g = 0; g < 2; ++g) {
+    const NemitAdamGroup& s = *src[g];
+    if (!(s.beta1 >= 0.0 && s.beta1 < 1.0 && s.beta2 >= 0.0 && s.beta2 < 1.0 && s.eps >= 0.0))
+      return fail(NEMIT_E_INVALID, "nemit_adam_step: betas must be in [0,1) and eps >= 0%s");
+    OptimGroup& d = A.grp[g];
+    d.beta1 = (float)s.beta1; d.beta2 = (float)s.beta2; d.eps = (float)s.eps; d.max_norm = s.max_norm; d.max_value = s.max_value;
+    d.omb1 = (float)(1.0 - s.beta1); d.omb2 = (float)(1.0 - s.beta2);
+    const double bc1 = 1.0 - pow(s.beta1, (double)step), bc2 = 1.0 - pow(s.beta2, (double)step);
+    d.step_size = (float)(s.lr / bc1);
+    d.bc2_sqrt = (float)sqrt(bc2);
+  }
+  A.inv_scale = 1.f / grad_scale;
+  A.zero_grads = zero_grads;
+  A.stats = h->opt_stats;
+  A.stats_out = stats_or_null;
+  cudaError_t e = launch_adam_step(A, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_adam_step");
+  h->launches += 2;
   return NEMIT_OK;
 }
 

@@ -139,6 +139,31 @@ struct MlpDev {
   int activation, out_activation;
 };
 
+// optimizer step over the borrowed tensors (optim.cu)
+constexpr int kOptMaxTensors = 24;
+struct OptimGroup {
+  float beta1, beta2, eps, max_norm, max_value;
+  float omb1, omb2;     // (float)(1 - beta) with the subtraction in double, like torch's python-float arithmetic
+  float step_size;      // lr / (1 - beta1^step)
+  float bc2_sqrt;       // sqrt(1 - beta2^step)
+};
+struct OptimArgs {
+  int num_tensors;
+  float* param[kOptMaxTensors];
+  float* grad[kOptMaxTensors];
+  float* exp_avg[kOptMaxTensors];
+  float* exp_avg_sq[kOptMaxTensors];
+  int64_t numel[kOptMaxTensors];
+  int64_t chunk_end[kOptMaxTensors];   // filled by the launcher
+  int group[kOptMaxTensors];           // 0 = fields, 1 = proposal_networks
+  OptimGroup grp[2];
+  float inv_scale;                     // 1 / GradScaler scale
+  int zero_grads;
+  double* stats;                       // device scratch (4): sum g^2 per group, non-finite flag, pad
+  float* stats_out;                    // optional user copy as float[4]
+};
+cudaError_t launch_adam_step(OptimArgs& A, cudaStream_t stream);
+
 cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const float* pos, const float* dir, int64_t n,
                                  int training, int camera_idx, float* density, float* geo, float* rgb,
                                  cudaStream_t stream);

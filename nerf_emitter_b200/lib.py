@@ -64,6 +64,10 @@ class NemitMlp(C.Structure):
                 ("activation", C.c_int32), ("out_activation", C.c_int32)]
 
 
+class NemitAdamGroup(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ["lr", "beta1", "beta2", "eps"]] + [("max_norm", C.c_float), ("max_value", C.c_float)]
+
+
 class NemitVmfLobes(C.Structure):
     _fields_ = [("position", C.c_void_p), ("weight", C.c_void_p), ("std", C.c_void_p), ("num_lobes", C.c_int32)]
 
@@ -90,6 +94,8 @@ SYMBOLS = {
     "nemit_hash_encode": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_point_lights": (C.c_int, [_H, C.POINTER(NemitRays), C.POINTER(C.c_float), C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_adam_step": (C.c_int, [_H, C.POINTER(NemitParams), C.POINTER(NemitParams), C.POINTER(NemitAdamGroup),
+                                  C.POINTER(NemitAdamGroup), C.c_int64, C.c_float, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_hash_encode_grid": (C.c_int, [C.POINTER(NemitGrid), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_sh_encode": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_mlp": (C.c_int, [C.POINTER(NemitMlp), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
