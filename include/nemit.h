@@ -219,6 +219,36 @@ int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const NemitParam
                     const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t step,
                     float grad_scale, int32_t zero_grads, float* stats_or_null, void* stream);
 
+/* Headless spherical-sensor bake of the emitter radiance (BASELINE config 5): SphericalCamera.sample_ray
+ * (DS/sensors/spherical_sensor.py:19-44 with assets/sensors/spherical_sensor.xml: to_world = translate, near_clip,
+ * hdrfilm rgba with a gaussian rfilter of stddev 0.25) -> nemit_forward -> film accumulation -> develop, all on the
+ * device.  Film samples are numbered pixel-major: sample s of pixel (x,y) has index (y*width + x)*spp + s. */
+typedef struct NemitSphericalSensor {
+  float origin[3];       /* to_world translation, Mitsuba unit-cube coordinates (0.5,0.5,0.5 in the reference XML) */
+  float near_clip;
+  int32_t width, height; /* film size */
+  int32_t spp;           /* samples per pixel */
+  uint32_t seed;         /* sub-pixel positions come from a counter-based RNG unless `jitter` is given */
+} NemitSphericalSensor;
+#define NEMIT_FILTER_BOX 0
+#define NEMIT_FILTER_GAUSSIAN 1
+/* rays of film samples [first, first+n): o, v (3,n) in the CustomOp layout, pos (n,2) film positions in pixels;
+ * jitter_or_null (n,2) in [0,1) replaces the RNG (parity tests) */
+int nemit_spherical_rays(const NemitSphericalSensor* s, int64_t first, int64_t n, const float* jitter_or_null,
+                         float* o, float* v, float* pos, void* stream);
+/* accum (height,width,4) += (w*rgb, w) for n samples; box: w = 1 in the pixel containing the sample; gaussian:
+ * separable exp(-x^2/(2 s^2)) - exp(-r^2/(2 s^2)), r = 4 s, over the pixel centres within r */
+int nemit_film_accumulate(int32_t width, int32_t height, int32_t filter, float stddev, const float* pos,
+                          const float* rgb, int64_t n, float* accum, void* stream);
+/* rgba (height,width,4) = (rgb / weight, 1) */
+int nemit_film_develop(int32_t width, int32_t height, const float* accum, float* rgba, void* stream);
+/* the whole bake for film rows [row_begin,row_end) (a rank's shard) into a zero-initialised full-size accum;
+ * ranks sum their accum buffers, then develop.  workspace >= nemit_bake_workspace_bytes(h). */
+size_t nemit_bake_workspace_bytes(const NemitHandle* h);
+int nemit_bake_envmap(NemitHandle* h, const NemitSphericalSensor* s, int32_t filter, float stddev, int32_t row_begin,
+                      int32_t row_end, int32_t camera_idx, float* accum, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
 /* ---- component-level drop-ins (SURVEY.md 8b "Model-side API kept intact"): what the nerfstudio modules'
  * forward() dispatches to when a module is called on its own, outside the fused emitter query ---- */
 

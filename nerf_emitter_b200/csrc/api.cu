@@ -763,6 +763,80 @@ extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const
 }
 
 // ---------------------------------------------------------------------------------------------
+// spherical-sensor bake (bake.cu)
+// ---------------------------------------------------------------------------------------------
+static int check_sensor(const NemitSphericalSensor* s, const char* who) {
+  if (!s) return fail(NEMIT_E_INVALID, "%s: null sensor", who);
+  if (s->width < 1 || s->height < 1 || s->spp < 1) return fail(NEMIT_E_INVALID, "%s: film size and spp must be >= 1", who);
+  if ((int64_t)s->width * s->height * s->spp >= ((int64_t)1 << 31)) return fail(NEMIT_E_INVALID, "%s: more than 2^31 film samples", who);
+  return NEMIT_OK;
+}
+static void fill_spherical(SphericalArgs& A, const NemitSphericalSensor* s, int64_t first, int64_t n, const float* jitter,
+                           float* o, float* v, float* pos) {
+  memset(&A, 0, sizeof(A));
+  for (int k = 0; k < 3; ++k) A.origin[k] = s->origin[k];
+  A.near_clip = s->near_clip; A.width = s->width; A.height = s->height; A.spp = s->spp; A.seed = s->seed;
+  A.first = first; A.n = n; A.jitter = jitter; A.o = o; A.v = v; A.pos = pos;
+}
+extern "C" int nemit_spherical_rays(const NemitSphericalSensor* s, int64_t first, int64_t n, const float* jitter_or_null,
+                                    float* o, float* v, float* pos, void* stream) {
+  int rc = check_sensor(s, "nemit_spherical_rays");
+  if (rc) return rc;
+  if (first < 0 || n < 0 || first + n > (int64_t)s->width * s->height * s->spp) return fail(NEMIT_E_INVALID, "nemit_spherical_rays: sample range outside the film%s");
+  if (n > 0 && (!o || !v || !pos)) return fail(NEMIT_E_INVALID, "nemit_spherical_rays: null output%s");
+  SphericalArgs A;
+  fill_spherical(A, s, first, n, jitter_or_null, o, v, pos);
+  cudaError_t e = launch_spherical_rays(A, (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_spherical_rays");
+}
+extern "C" int nemit_film_accumulate(int32_t width, int32_t height, int32_t filter, float stddev, const float* pos,
+                                     const float* rgb, int64_t n, float* accum, void* stream) {
+  if (width < 1 || height < 1 || n < 0 || (n > 0 && (!pos || !rgb || !accum))) return fail(NEMIT_E_INVALID, "nemit_film_accumulate: bad argument%s");
+  if (filter != NEMIT_FILTER_BOX && filter != NEMIT_FILTER_GAUSSIAN) return fail(NEMIT_E_INVALID, "nemit_film_accumulate: unknown filter%s");
+  if (filter == NEMIT_FILTER_GAUSSIAN && !(stddev > 0.f)) return fail(NEMIT_E_INVALID, "nemit_film_accumulate: stddev must be > 0%s");
+  FilmArgs A;
+  memset(&A, 0, sizeof(A));
+  A.width = width; A.height = height; A.filter = filter; A.stddev = stddev; A.pos = pos; A.rgb = rgb; A.n = n;
+  A.accum = reinterpret_cast<float4*>(accum);
+  cudaError_t e = launch_film_accumulate(A, (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_film_accumulate");
+}
+extern "C" int nemit_film_develop(int32_t width, int32_t height, const float* accum, float* rgba, void* stream) {
+  if (width < 1 || height < 1 || !accum || !rgba) return fail(NEMIT_E_INVALID, "nemit_film_develop: bad argument%s");
+  cudaError_t e = launch_film_develop((int64_t)width * height, accum, rgba, (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_film_develop");
+}
+extern "C" size_t nemit_bake_workspace_bytes(const NemitHandle* h) {
+  (void)h;
+  return ws_layout(kChunkRays).total + align_up(sizeof(float) * 11 * (size_t)kChunkRays);
+}
+extern "C" int nemit_bake_envmap(NemitHandle* h, const NemitSphericalSensor* s, int32_t filter, float stddev,
+                                 int32_t row_begin, int32_t row_end, int32_t camera_idx, float* accum, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  int rc = check_sensor(s, "nemit_bake_envmap");
+  if (rc) return rc;
+  if (!h || !accum) return fail(NEMIT_E_INVALID, "nemit_bake_envmap: null argument%s");
+  if (row_begin < 0 || row_end > s->height || row_begin > row_end) return fail(NEMIT_E_INVALID, "nemit_bake_envmap: bad row range%s");
+  if (!workspace || workspace_bytes < nemit_bake_workspace_bytes(h)) return fail(NEMIT_E_WORKSPACE, "nemit_bake_envmap: workspace too small%s");
+  char* ws = static_cast<char*>(workspace);
+  const size_t fwd_bytes = ws_layout(kChunkRays).total;
+  float* stage = reinterpret_cast<float*>(ws + fwd_bytes);
+  float *o = stage, *v = stage + 3 * (size_t)kChunkRays, *pos = stage + 6 * (size_t)kChunkRays, *rgb = stage + 8 * (size_t)kChunkRays;
+  const int64_t first = (int64_t)row_begin * s->width * s->spp, last = (int64_t)row_end * s->width * s->spp;
+  for (int64_t off = first; off < last; off += kChunkRays) {
+    const int64_t n = last - off < kChunkRays ? last - off : kChunkRays;
+    if ((rc = nemit_spherical_rays(s, off, n, nullptr, o, v, pos, stream))) return rc;
+    NemitRays R;
+    memset(&R, 0, sizeof(R));
+    R.o = o; R.v = v; R.n = n; R.near_scalar = 0.f; R.camera_idx = camera_idx; R.training = 0; R.anneal = 1.f;
+    if ((rc = nemit_forward(h, &R, rgb, nullptr, nullptr, workspace, fwd_bytes, stream))) return rc;
+    if ((rc = nemit_film_accumulate(s->width, s->height, filter, stddev, pos, rgb, n, accum, stream))) return rc;
+    h->launches += 2;
+  }
+  return NEMIT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
 // vMF mixture (DS/emitters/vMF.py)
 // ---------------------------------------------------------------------------------------------
 static int check_lobes(const NemitVmfLobes* l, const char* who) {

@@ -76,22 +76,21 @@ __device__ __forceinline__ void load_ray(const float* __restrict__ o, const floa
                                          const float* __restrict__ near_per_ray, float near_scalar,
                                          int64_t n, int64_t r, float scene_scale, float oo[3], float dd[3]) {
   float nr = near_per_ray ? near_per_ray[r] : near_scalar;
-  if (scene_scale == 0.f) {
-    // NEMIT_RAYS_NERF_N3 (kernels.h ray_scale): RayBundle.origins / .directions, (N,3) rows already in NeRF coordinates
-#pragma unroll
-    for (int k = 0; k < 3; ++k) { dd[k] = v[r * 3 + k]; oo[k] = add_rn(o[r * 3 + k], mul_rn(nr, dd[k])); }
-    return;
-  }
-  float vm[3] = {v[r], v[n + r], v[2 * n + r]};
+  // scene_scale == 0 selects NEMIT_RAYS_NERF_N3 (kernels.h ray_scale): RayBundle.origins / .directions, (N,3) rows already
+  // in NeRF coordinates.  Both layouts issue the same six loads (strides differ), so no load waits behind a branch.
+  const bool nerf = scene_scale == 0.f;
+  const int64_t sr = nerf ? 3 : 1, sk = nerf ? 1 : n;
+  float vm[3] = {v[r * sr], v[r * sr + sk], v[r * sr + 2 * sk]};
+  float x[3] = {o[r * sr], o[r * sr + sk], o[r * sr + 2 * sk]};
   float om[3];
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    float x = add_rn(o[k * n + r], mul_rn(nr, vm[k]));
-    om[k] = mul_rn(sub_rn(mul_rn(x, 2.f), 1.f), scene_scale);
+    x[k] = add_rn(x[k], mul_rn(nr, vm[k]));
+    om[k] = mul_rn(sub_rn(mul_rn(x[k], 2.f), 1.f), scene_scale);
   }
   // matmul with the permutation matrix adds exact zeros; the + 0 translation is exact as well
-  oo[0] = om[2]; oo[1] = om[0]; oo[2] = om[1];
-  dd[0] = vm[2]; dd[1] = vm[0]; dd[2] = vm[1];
+  oo[0] = nerf ? x[0] : om[2]; oo[1] = nerf ? x[1] : om[0]; oo[2] = nerf ? x[2] : om[1];
+  dd[0] = nerf ? vm[0] : vm[2]; dd[1] = nerf ? vm[1] : vm[0]; dd[2] = nerf ? vm[2] : vm[1];
 }
 
 // NS/cameras/rays.py:49-58: pos = o + d*(t0+t1)/2 (evaluated as ((d*(t0+t1))/2) + o)
@@ -189,6 +188,11 @@ __device__ __forceinline__ float2 ldg_f2(const float2* __restrict__ t, uint32_t 
 // L1-missing lane-load costs 1.0 SM-cycle whatever its width and an L1-hitting one 0.34 (tools/gather_bench.cu,
 // profiles/r1_gather_bench.txt), so this removes a quarter of the pair cost on half of the pairs.
 __device__ __forceinline__ void gather_cell(const float2* __restrict__ t, const LevelCell& c, float2 v[8]) {
+#ifdef NEMIT_PLAIN_GATHER
+#pragma unroll
+  for (int q = 0; q < 8; ++q) v[q] = __ldg(t + c.idx[q]);
+  return;
+#endif
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     const uint32_t ic = c.idx[2 * q], il = c.idx[2 * q + 1];       // ceil-x corner, floor-x corner

@@ -164,6 +164,30 @@ struct OptimArgs {
 };
 cudaError_t launch_adam_step(OptimArgs& A, cudaStream_t stream);
 
+// spherical-sensor bake (bake.cu)
+struct SphericalArgs {
+  float origin[3];
+  float near_clip;
+  int width, height, spp;
+  uint32_t seed;
+  int64_t first, n;        // samples [first, first + n) in pixel-major order
+  const float* jitter;     // (n,2) or null -> counter-based RNG
+  float* o;                // (3,n)
+  float* v;                // (3,n)
+  float* pos;              // (n,2) film positions in pixel units
+};
+struct FilmArgs {
+  int width, height, filter;   // filter 0 = box, 1 = gaussian
+  float stddev;
+  const float* pos;        // (n,2)
+  const float* rgb;        // (n,3)
+  int64_t n;
+  float4* accum;           // (H,W) of (sum w rgb, sum w)
+};
+cudaError_t launch_spherical_rays(const SphericalArgs& A, cudaStream_t stream);
+cudaError_t launch_film_accumulate(const FilmArgs& A, cudaStream_t stream);
+cudaError_t launch_film_develop(int64_t n, const float* accum, float* rgba, cudaStream_t stream);
+
 cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const float* pos, const float* dir, int64_t n,
                                  int training, int camera_idx, float* density, float* geo, float* rgb,
                                  cudaStream_t stream);

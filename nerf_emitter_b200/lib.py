@@ -68,6 +68,11 @@ class NemitAdamGroup(C.Structure):
     _fields_ = [(n, C.c_double) for n in ["lr", "beta1", "beta2", "eps"]] + [("max_norm", C.c_float), ("max_value", C.c_float)]
 
 
+class NemitSphericalSensor(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("near_clip", C.c_float), ("width", C.c_int32), ("height", C.c_int32),
+                ("spp", C.c_int32), ("seed", C.c_uint32)]
+
+
 class NemitVmfLobes(C.Structure):
     _fields_ = [("position", C.c_void_p), ("weight", C.c_void_p), ("std", C.c_void_p), ("num_lobes", C.c_int32)]
 
@@ -96,6 +101,14 @@ SYMBOLS = {
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_adam_step": (C.c_int, [_H, C.POINTER(NemitParams), C.POINTER(NemitParams), C.POINTER(NemitAdamGroup),
                                   C.POINTER(NemitAdamGroup), C.c_int64, C.c_float, C.c_int32, C.c_void_p, C.c_void_p]),
+    "nemit_spherical_rays": (C.c_int, [C.POINTER(NemitSphericalSensor), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nemit_film_accumulate": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_int64,
+                                        C.c_void_p, C.c_void_p]),
+    "nemit_film_develop": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nemit_bake_workspace_bytes": (C.c_size_t, [_H]),
+    "nemit_bake_envmap": (C.c_int, [_H, C.POINTER(NemitSphericalSensor), C.c_int32, C.c_float, C.c_int32, C.c_int32,
+                                    C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_hash_encode_grid": (C.c_int, [C.POINTER(NemitGrid), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_sh_encode": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_mlp": (C.c_int, [C.POINTER(NemitMlp), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
