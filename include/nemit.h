@@ -249,6 +249,20 @@ int nemit_bake_envmap(NemitHandle* h, const NemitSphericalSensor* s, int32_t fil
                       int32_t row_end, int32_t camera_idx, float* accum, void* workspace, size_t workspace_bytes,
                       void* stream);
 
+/* Light point cloud -> K spherical Gaussians, the producer of the vMF lobe table.
+ * nemit_compensate_weights: compensate_pc (NS/model_components/output_light_pc.py:176-191): w_i = max(lum_i - mean(lum), 0),
+ * zeroed unless lum_i > threshold (use_threshold != 0); points keep their place, a zero weight removes them from the fit.
+ * nemit_gmm_em_step: one EM iteration of cluster_light's weighted mixture of isotropic normals
+ * (NS/model_components/gmm_cluster_light.py:41-85, pomegranate GeneralMixtureModel + Normal('sphere'); pomegranate is not
+ * in the reference tree: restated as the textbook weighted EM, parity unpinned).  x (n,3), w (n); (mean (k,3), var (k),
+ * prior (k)) in -> out (may not alias); logp_out (1) = sum_i w_i log p(x_i) under the INPUT parameters;
+ * scratch: device, >= (6k + 2) doubles; k <= 128; variances are floored at min_var. */
+int nemit_compensate_weights(const float* lum, int64_t n, float threshold, int32_t use_threshold, float* w,
+                             void* scratch, void* stream);
+int nemit_gmm_em_step(const float* x, const float* w, int64_t n, int32_t k, const float* mean, const float* var,
+                      const float* prior, float min_var, float* mean_out, float* var_out, float* prior_out,
+                      float* logp_out, void* scratch, void* stream);
+
 /* ---- component-level drop-ins (SURVEY.md 8b "Model-side API kept intact"): what the nerfstudio modules'
  * forward() dispatches to when a module is called on its own, outside the fused emitter query ---- */
 

@@ -837,6 +837,31 @@ extern "C" int nemit_bake_envmap(NemitHandle* h, const NemitSphericalSensor* s, 
 }
 
 // ---------------------------------------------------------------------------------------------
+// light point cloud -> spherical-Gaussian mixture (gmm.cu)
+// ---------------------------------------------------------------------------------------------
+extern "C" int nemit_compensate_weights(const float* lum, int64_t n, float threshold, int32_t use_threshold, float* w,
+                                        void* scratch, void* stream) {
+  if (n < 0 || (n > 0 && (!lum || !w)) || !scratch) return fail(NEMIT_E_INVALID, "nemit_compensate_weights: bad argument%s");
+  cudaError_t e = launch_compensate(lum, n, threshold, use_threshold, static_cast<double*>(scratch), w, (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_compensate");
+}
+extern "C" int nemit_gmm_em_step(const float* x, const float* w, int64_t n, int32_t k, const float* mean, const float* var,
+                                 const float* prior, float min_var, float* mean_out, float* var_out, float* prior_out,
+                                 float* logp_out, void* scratch, void* stream) {
+  if (n < 0 || (n > 0 && (!x || !w)) || !mean || !var || !prior || !mean_out || !var_out || !prior_out || !logp_out || !scratch)
+    return fail(NEMIT_E_INVALID, "nemit_gmm_em_step: null argument%s");
+  if (k < 1 || k > 128) return fail(NEMIT_E_INVALID, "nemit_gmm_em_step: 1..128 components%s");
+  if (mean == mean_out || var == var_out || prior == prior_out) return fail(NEMIT_E_INVALID, "nemit_gmm_em_step: outputs may not alias inputs%s");
+  GmmArgs A;
+  memset(&A, 0, sizeof(A));
+  A.x = x; A.w = w; A.n = n; A.k = k; A.mean = mean; A.var = var; A.prior = prior; A.min_var = min_var;
+  A.stats = static_cast<double*>(scratch);
+  A.mean_out = mean_out; A.var_out = var_out; A.prior_out = prior_out; A.logp_out = logp_out;
+  cudaError_t e = launch_gmm_em(A, (cudaStream_t)stream);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_gmm_em");
+}
+
+// ---------------------------------------------------------------------------------------------
 // vMF mixture (DS/emitters/vMF.py)
 // ---------------------------------------------------------------------------------------------
 static int check_lobes(const NemitVmfLobes* l, const char* who) {

@@ -164,6 +164,24 @@ struct OptimArgs {
 };
 cudaError_t launch_adam_step(OptimArgs& A, cudaStream_t stream);
 
+// light point cloud -> spherical-Gaussian mixture (gmm.cu)
+struct GmmArgs {
+  const float* x;        // (n,3)
+  const float* w;        // (n) sample weights (zero = point ignored)
+  int64_t n;
+  int k;
+  const float* mean;     // (k,3) current parameters
+  const float* var;      // (k)   isotropic variances
+  const float* prior;    // (k)
+  float min_var;
+  double* stats;         // (k*6 + 2) scratch
+  float* mean_out; float* var_out; float* prior_out;
+  float* logp_out;       // (1) weighted log-likelihood under the input parameters
+};
+cudaError_t launch_compensate(const float* lum, int64_t n, float threshold, int use_threshold, double* scratch, float* w,
+                              cudaStream_t stream);
+cudaError_t launch_gmm_em(const GmmArgs& A, cudaStream_t stream);
+
 // spherical-sensor bake (bake.cu)
 struct SphericalArgs {
   float origin[3];

@@ -109,6 +109,9 @@ SYMBOLS = {
     "nemit_bake_workspace_bytes": (C.c_size_t, [_H]),
     "nemit_bake_envmap": (C.c_int, [_H, C.POINTER(NemitSphericalSensor), C.c_int32, C.c_float, C.c_int32, C.c_int32,
                                     C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_compensate_weights": (C.c_int, [C.c_void_p, C.c_int64, C.c_float, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nemit_gmm_em_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "nemit_hash_encode_grid": (C.c_int, [C.POINTER(NemitGrid), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_sh_encode": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_mlp": (C.c_int, [C.POINTER(NemitMlp), C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
