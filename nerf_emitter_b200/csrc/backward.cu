@@ -321,12 +321,11 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
 
 cudaError_t launch_field_backward(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(BwdSmem);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
   int64_t ctas = tiles < 148 ? tiles : 148;      // persistent, one CTA per SM (shared-memory limited)

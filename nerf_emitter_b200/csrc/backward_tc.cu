@@ -451,12 +451,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
 cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   const size_t smem = sizeof(BwdTcSmem) + 128;
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_backward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   const int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
   const int64_t pairs = (tiles + 1) / 2;

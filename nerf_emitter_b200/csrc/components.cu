@@ -89,12 +89,11 @@ cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const 
                                  int training, int camera_idx, float* density, float* geo, float* rgb,
                                  cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   const size_t smem = sizeof(SamplesSmem);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_samples, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   const int64_t tiles = (n + kTileM - 1) / kTileM;
   const int64_t ctas = tiles < 148 * 2 ? tiles : 148 * 2;

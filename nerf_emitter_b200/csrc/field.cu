@@ -148,12 +148,11 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
 template <int MODE>
 static cudaError_t launch_field_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(FieldSmem);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_forward<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   int64_t ctas = groups < 148 * 2 ? groups : 148 * 2;     // persistent: 2 CTAs per SM (smem-limited)

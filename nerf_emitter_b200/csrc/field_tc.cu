@@ -312,12 +312,11 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
 template <int MODE>
 static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(TcSmem) + 128;
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   int64_t ctas = groups < 148 * 4 ? groups : 148 * 4;     // persistent: 4 CTAs per SM share the tensor core

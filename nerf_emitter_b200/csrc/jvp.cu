@@ -222,12 +222,11 @@ k_field_jvp(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArg
 
 cudaError_t launch_field_jvp(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(JvpSmem);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_jvp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   int64_t ctas = groups < 148 ? groups : 148;

@@ -4,6 +4,18 @@
 
 namespace nemit {
 
+// "do once per device" latch for per-function attributes (one process may drive several devices through several handles)
+struct DeviceOnce {
+  bool done[64] = {};
+  bool need() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+    if (done[d]) return false;
+    done[d] = true;
+    return true;
+  }
+};
+
 // rays are addressed as (3, n_total) SoA with a chunk [ray_offset, ray_offset + n); every OUTPUT pointer
 // is already offset to the chunk by the host.
 struct RayArgs {

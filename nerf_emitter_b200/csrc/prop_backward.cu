@@ -279,12 +279,11 @@ k_prop_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Prop
 
 cudaError_t launch_prop_backward(const ModelDev& M, const PropBwdArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(PbSmem);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_prop_backward, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t ctas = (A.n + kPbWarps - 1) / kPbWarps;
   const int64_t max_ctas = 148 * 2 * 8;

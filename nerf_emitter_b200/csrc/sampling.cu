@@ -74,12 +74,11 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
 template <class MLP>
 static cudaError_t launch_sample_levels_t(const ModelDev& M, const SampleArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
-  static bool attr_set = false;
+  static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
   size_t smem = sizeof(SampleSmem<MLP>);
-  if (!attr_set) {
+  if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_sample_levels<MLP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   int64_t ctas = (A.n + kWarpsPerCta - 1) / kWarpsPerCta;
   const int64_t max_ctas = 148 * 8 * 16;
