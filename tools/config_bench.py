@@ -7,7 +7,16 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from nerf_emitter_b200 import EmitterModelSpec, NerfEmitter, VmfMixture, make_params
 from nerf_emitter_b200.bake import bake_envmap
-from oracle.vmf_oracle import make_lobes       # synthetic lobe table only, not a checker here
+
+
+def make_lobes(K=64, seed=3):
+    """SURVEY.md 8d config 4 synthetic lobe table: positions U([-1,2]^3), std U(0.05,0.5), weights ~ Dirichlet(1)."""
+    g = torch.Generator().manual_seed(seed)
+    position = torch.rand(K, 3, generator=g) * 3 - 1
+    std = torch.rand(K, generator=g) * 0.45 + 0.05
+    e = -torch.log(torch.rand(K, generator=g))
+    return position, e / e.sum(), std
+
 
 spec = EmitterModelSpec()
 E = NerfEmitter(make_params(spec, 0, 1e3), spec).set_precision("fp16").set_sampler("fast").eval()
