@@ -1,6 +1,7 @@
 // api.cu - the C ABI of libnerfemitter.so (include/nemit.h): handle, argument checks, chunking,
 // workspace carving, kernel launches.  No torch types, no allocation of parameter memory.
 #include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -181,6 +182,9 @@ static bool params_complete(const NemitParams* p) {
 extern "C" int nemit_bind_params(NemitHandle* h, const NemitParams* p) {
   if (!h || !p) return fail(NEMIT_E_INVALID, "nemit_bind_params: null argument%s");
   if (!params_complete(p)) return fail(NEMIT_E_INVALID, "nemit_bind_params: a parameter pointer is null%s");
+  // table rows are fetched as aligned 16-byte pairs, MLP tensors as float4 streams by the optimizer step
+  if (((uintptr_t)p->main_table | (uintptr_t)p->prop_table[0] | (uintptr_t)p->prop_table[1]) & 15)
+    return fail(NEMIT_E_INVALID, "nemit_bind_params: hash tables must be 16-byte aligned%s");
   h->P = *p;
   h->params_bound = true;
   return NEMIT_OK;
@@ -188,6 +192,9 @@ extern "C" int nemit_bind_params(NemitHandle* h, const NemitParams* p) {
 extern "C" int nemit_bind_grads(NemitHandle* h, const NemitParams* g) {
   if (!h || !g) return fail(NEMIT_E_INVALID, "nemit_bind_grads: null argument%s");
   if (!params_complete(g)) return fail(NEMIT_E_INVALID, "nemit_bind_grads: a gradient pointer is null%s");
+  // the table scatter uses red.global.add.v4.f32 on aligned pairs of rows
+  if (((uintptr_t)g->main_table | (uintptr_t)g->prop_table[0] | (uintptr_t)g->prop_table[1]) & 15)
+    return fail(NEMIT_E_INVALID, "nemit_bind_grads: hash-table gradients must be 16-byte aligned%s");
   h->G = *g;
   h->grads_bound = true;
   return NEMIT_OK;
@@ -740,6 +747,10 @@ extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const
       A.param[t] = P[k]; A.grad[t] = G[k]; A.exp_avg[t] = M1[k]; A.exp_avg_sq[t] = M2[k]; A.numel[t] = nn[f]; A.group[t] = 1;
     }
   A.num_tensors = t;
+  for (int i = 0; i < t; ++i)
+    if ((A.numel[i] & 3) == 0 &&
+        (((uintptr_t)A.param[i] | (uintptr_t)A.grad[i] | (uintptr_t)A.exp_avg[i] | (uintptr_t)A.exp_avg_sq[i]) & 15))
+      return fail(NEMIT_E_INVALID, "nemit_adam_step: tensors are streamed as float4 and must be 16-byte aligned%s");
   const NemitAdamGroup* src[2] = {fields, proposal_networks};
   for (int g = 0; g < 2; ++g) {
     const NemitAdamGroup& s = *src[g];

@@ -338,7 +338,13 @@ class ProposalNetworkSampler:
         n = o.shape[0]
         s0 = E._tables[0].to(o.device)[None, :].expand(n, -1)
         if jitter is not None and E.training:
-            raise NotImplementedError("level-0 edges under jitter are not reconstructed on the host")
+            # the kernel's level-0 edges under single jitter (ray_samplers.py:107-117), rebuilt for the returned RaySamples
+            j0 = (torch.cat([j.reshape(n, 1) for j in jitter], dim=1) if isinstance(jitter, (list, tuple)) else jitter)
+            t_rand = j0.to(o.device, torch.float32).reshape(n, -1)[:, :1]
+            centers = (s0[..., 1:] + s0[..., :-1]) / 2.0
+            upper = torch.cat([centers, s0[..., -1:]], -1)
+            lower = torch.cat([s0[..., :1], centers], -1)
+            s0 = lower + (upper - lower) * t_rand
         ray_samples_list = [samples(s0), samples(aux["s_edges1"])]
         weights_list = [aux["weights0"][..., None], aux["weights1"][..., None]]
         return samples(aux["s_edges2"], aux["t_edges2"]), weights_list, ray_samples_list

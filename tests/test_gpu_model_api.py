@@ -139,3 +139,30 @@ def test_ray_bundle_entry_points_equal_the_custom_op_layout(model, spec, params_
         assert rel_err(named[k].grad, gref, floor=1e-12) < 1e-4, k
     assert float(named["field.mlp_base_grid.hash_table"].grad.abs().sum()) > 0
     assert float(named["proposal_networks.0.encoding.hash_table"].grad.abs().sum()) == 0.0
+
+
+def test_sampler_training_mode_with_jitter(model, spec, params_factory):
+    """Training mode with explicit per-ray jitter: returned level-0 / level-1 / final sample edges follow the oracle."""
+    from oracle.nerfacto_oracle import OracleEmitter
+    from nerf_emitter_b200.nerfstudio_api import RayBundle
+    N = 64
+    o3n, v3n, g = make_rays(N, seed=13)
+    o, d = _nerf_rays(o3n, v3n)
+    jit = [torch.rand(N, 1, generator=g) for _ in range(3)]
+    model.train()
+    try:
+        rs, wl, rsl = model.proposal_sampler(RayBundle(origins=o.to(DEV), directions=d.to(DEV)), jitter=jit)
+    finally:
+        model.eval()
+    O = OracleEmitter(params_factory(0, 1e3), spec)
+    O.train(True)
+    _, aux = O.render(o3n, v3n, jitter=jit, return_aux=True)
+    s0 = torch.cat([rsl[0].spacing_starts[..., 0], rsl[0].spacing_ends[:, -1:, 0]], dim=1).cpu()
+    assert rel_err(s0, aux["sdist0"]) < 1e-6
+    s1 = torch.cat([rsl[1].spacing_starts[..., 0], rsl[1].spacing_ends[:, -1:, 0]], dim=1).cpu()
+    assert rel_err(s1, aux["sdist1"]) < 1e-4
+    assert rel_err(wl[0][..., 0].cpu(), aux["weights0"]) < TOL
+    t2 = torch.cat([rs.frustums.starts[..., 0], rs.frustums.ends[:, -1:, 0]], dim=1).cpu()
+    assert rel_err(t2, aux["t_edges2"]) < 1e-3
+    # euclidean edges of level 0 start at the training near plane 0.05 (NearFarCollider), moved inwards by the jitter
+    assert spec.near_plane - 1e-6 <= float(rsl[0].frustums.starts.min()) < spec.near_plane + 0.01
