@@ -131,6 +131,19 @@ int nemit_version(void);
 int nemit_create(const NemitConfig* cfg, int device, NemitHandle** out);
 int nemit_destroy(NemitHandle* h);
 
+/* Which appearance vector a call sees.  Default (no call): the reference without a Rotater, i.e. the camera's row of
+ * field.embedding_appearance in training mode and the mean over rows in eval mode
+ * (NS/fields/nerfacto_field.py:272-285, use_average_appearance_embedding NS/models/nerfacto.py:116).
+ * always_use_camera_indices != 0 is the model built with a Rotater (turntable captures: num_images = number of
+ * rotations and always_use_camera_indices = True, NS/models/nerfacto.py:186-206): the row is used in eval mode too.
+ * rotation_ids_host (num_rotation_ids entries, copied; may be null) is Rotater.rotation_ids: every ray-level entry
+ * maps NemitRays.camera_idx -> rotation_ids[min(camera_idx, num_rotation_ids - 1)] as Rotater.map_rotation_ids does
+ * (NS/field_components/rotater.py:94-100, call sites NS/models/sdf_nerfacto.py:71-72,92-93,127-128,198-199);
+ * nemit_field_samples takes an already mapped index.  use_average_appearance_embedding == 0 gives zeros in eval. */
+int nemit_set_appearance_mode(NemitHandle* h, int32_t always_use_camera_indices,
+                              int32_t use_average_appearance_embedding, const int32_t* rotation_ids_host,
+                              int32_t num_rotation_ids);
+
 /* borrow parameter / gradient pointers (never copied, never freed) */
 int nemit_bind_params(NemitHandle* h, const NemitParams* p);
 int nemit_bind_grads(NemitHandle* h, const NemitParams* g);

@@ -34,6 +34,10 @@ struct NemitHandle {
   const float* u2;
   double* opt_stats;        // 4 doubles of optimizer-step scratch (tail of tables_dev)
   bool params_bound, grads_bound;
+  // nemit_set_appearance_mode
+  int always_use_camera_indices, use_average_embedding;
+  int32_t* rotation_ids;    // host copy of Rotater.rotation_ids, or null
+  int32_t num_rotation_ids;
   NemitParams P, G;
   int64_t launches;
   int precision;
@@ -131,6 +135,7 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   if (!h) return fail(NEMIT_E_INVALID, "nemit_create: out of host memory%s");
   memset(h, 0, sizeof(*h));
   h->device = device;
+  h->use_average_embedding = 1;       // NerfactoModelConfig.use_average_appearance_embedding (NS/models/nerfacto.py:116)
   h->cfg = *cfg;
   h->cfg.lin0_host = h->cfg.u1_host = h->cfg.u2_host = nullptr;
   grid_to_dev(cfg->main_grid, h->M.main_grid);
@@ -167,8 +172,32 @@ extern "C" int nemit_destroy(NemitHandle* h) {
   if (!h) return NEMIT_OK;
   cudaSetDevice(h->device);
   cudaFree(h->tables_dev);
+  free(h->rotation_ids);
   for (int i = 0; i < 2 * 512; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   delete h;
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_set_appearance_mode(NemitHandle* h, int32_t always_use_camera_indices,
+                                         int32_t use_average_appearance_embedding, const int32_t* rotation_ids_host,
+                                         int32_t num_rotation_ids) {
+  if (!h) return fail(NEMIT_E_INVALID, "nemit_set_appearance_mode: null handle%s");
+  if (num_rotation_ids < 0 || (num_rotation_ids > 0 && !rotation_ids_host))
+    return fail(NEMIT_E_INVALID, "nemit_set_appearance_mode: bad rotation id table%s");
+  for (int32_t i = 0; i < num_rotation_ids; ++i)
+    if (rotation_ids_host[i] < 0 || rotation_ids_host[i] >= h->cfg.num_images)
+      return fail(NEMIT_E_INVALID, "nemit_set_appearance_mode: rotation id outside the appearance embedding%s");
+  int32_t* ids = nullptr;
+  if (num_rotation_ids > 0) {
+    ids = static_cast<int32_t*>(malloc(sizeof(int32_t) * num_rotation_ids));
+    if (!ids) return fail(NEMIT_E_INVALID, "nemit_set_appearance_mode: out of host memory%s");
+    memcpy(ids, rotation_ids_host, sizeof(int32_t) * num_rotation_ids);
+  }
+  free(h->rotation_ids);
+  h->rotation_ids = ids;
+  h->num_rotation_ids = num_rotation_ids;
+  h->always_use_camera_indices = always_use_camera_indices != 0;
+  h->use_average_embedding = use_average_appearance_embedding != 0;
   return NEMIT_OK;
 }
 
@@ -268,12 +297,32 @@ extern "C" size_t nemit_workspace_bytes(const NemitHandle* h, int64_t n) {
   return ws_layout(n).total;
 }
 
+// Which appearance vector a call sees (NS/fields/nerfacto_field.py:272-285, NS/models/sdf_nerfacto.py:71-72,
+// NS/field_components/rotater.py:94-100): a row of the embedding in training mode or when the model was built with a
+// Rotater (always_use_camera_indices, NS/models/nerfacto.py:186-206), after camera -> rotation id mapping; else
+// the mean of the rows (use_average_appearance_embedding) or zeros.  Returns false when the row is out of range.
+static bool appearance_row(const NemitHandle* h, int training, int camera_idx, bool map_ids, int* row) {
+  if (!(training || h->always_use_camera_indices)) {
+    *row = h->use_average_embedding ? kAppMean : kAppZero;
+    return true;
+  }
+  int idx = camera_idx;
+  if (map_ids && h->rotation_ids) {
+    if (idx < 0) return false;
+    if (idx > h->num_rotation_ids - 1) idx = h->num_rotation_ids - 1;      // camera_indices.clamp(max = len - 1)
+    idx = h->rotation_ids[idx];
+  }
+  *row = idx;
+  return idx >= 0 && idx < h->cfg.num_images;
+}
+
 static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who) {
   if (!h || !r) return fail(NEMIT_E_INVALID, "%s: null argument", who);
   if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "%s: parameters not bound (nemit_bind_params)", who);
   if (r->n < 0) return fail(NEMIT_E_INVALID, "%s: negative ray count", who);
   if (r->n > 0 && (!r->o || !r->v)) return fail(NEMIT_E_INVALID, "%s: null ray pointers", who);
-  if (r->training && (r->camera_idx < 0 || r->camera_idx >= h->cfg.num_images))
+  int row;
+  if (!appearance_row(h, r->training, r->camera_idx, true, &row))
     return fail(NEMIT_E_INVALID, "%s: camera_idx outside the appearance embedding", who);
   if (!(r->anneal > 0.f)) return fail(NEMIT_E_INVALID, "%s: anneal must be > 0", who);
   if (r->layout != NEMIT_RAYS_MITSUBA_3N && r->layout != NEMIT_RAYS_NERF_N3)
@@ -281,15 +330,16 @@ static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who)
   return NEMIT_OK;
 }
 
-static void fill_ray_args(RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
+static void fill_ray_args(const NemitHandle* h, RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
   A.o = r->o; A.v = r->v; A.near_per_ray = r->near_per_ray; A.near_scalar = r->near_scalar;
-  A.n_total = r->n; A.ray_offset = off; A.n = n; A.training = r->training; A.camera_idx = r->camera_idx;
+  A.n_total = r->n; A.ray_offset = off; A.n = n; A.training = r->training;
+  appearance_row(h, r->training, r->camera_idx, true, &A.app_row);
   A.jitter = r->jitter; A.anneal = r->anneal; A.nerf_layout = r->layout == NEMIT_RAYS_NERF_N3;
 }
 
 static void fill_sample_args(const NemitHandle* h, SampleArgs& S, const NemitRays* r, int64_t off, int64_t n) {
   memset(&S, 0, sizeof(S));
-  fill_ray_args(S, r, off, n);
+  fill_ray_args(h, S, r, off, n);
   for (int i = 0; i < 2; ++i) {
     S.prop_table[i] = reinterpret_cast<const float2*>(h->P.prop_table[i]);
     S.prop_w0[i] = h->P.prop_w0[i]; S.prop_b0[i] = h->P.prop_b0[i];
@@ -361,7 +411,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     }
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n);
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges;
     F.rgb = rgb + off * 3;
@@ -441,7 +491,7 @@ extern "C" int nemit_density_fn(NemitHandle* h, int32_t which, const float* posi
   if (which == 0) {
     FieldParams P;
     fill_field_params(h->P, P);
-    e = launch_field_samples(h->M, P, positions, nullptr, n, 0, 0, density, geo_or_null, nullptr, (cudaStream_t)stream);
+    e = launch_field_samples(h->M, P, positions, nullptr, n, kAppMean, density, geo_or_null, nullptr, (cudaStream_t)stream);
   } else {
     const int i = which - 1;
     e = launch_prop_density(h->M, h->M.prop_grid[i], reinterpret_cast<const float2*>(h->P.prop_table[i]), h->P.prop_w0[i],
@@ -457,12 +507,13 @@ extern "C" int nemit_field_samples(NemitHandle* h, const float* positions, const
   if (!h || n < 0 || (n > 0 && (!positions || !directions || !density || !rgb)))
     return fail(NEMIT_E_INVALID, "nemit_field_samples: null argument%s");
   if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_field_samples: parameters not bound%s");
-  if (training && (camera_idx < 0 || camera_idx >= h->cfg.num_images))
+  int app_row;      // the model has already mapped camera -> rotation ids on ray_samples (sdf_nerfacto.py:71-72)
+  if (!appearance_row(h, training, camera_idx, false, &app_row))
     return fail(NEMIT_E_INVALID, "nemit_field_samples: camera_idx outside the appearance embedding%s");
   cudaSetDevice(h->device);
   FieldParams P;
   fill_field_params(h->P, P);
-  cudaError_t e = launch_field_samples(h->M, P, positions, directions, n, training, camera_idx, density, nullptr, rgb,
+  cudaError_t e = launch_field_samples(h->M, P, positions, directions, n, app_row, density, nullptr, rgb,
                                        (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "k_field_samples");
   h->launches++;
@@ -526,7 +577,7 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n);
     fill_field_params(h->P, F.P);
     F.t_edges2 = S.t_edges2;
     F.d_o = d_o; F.d_v = d_v;
@@ -569,7 +620,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     // pass 1: forward of the 48-sample stage + composite adjoint
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n);
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
     F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
@@ -591,7 +642,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
     FieldBwdArgs B;
     memset(&B, 0, sizeof(B));
-    fill_ray_args(B, rays, off, n);
+    fill_ray_args(h, B, rays, off, n);
     fill_field_params(h->P, B.P);
     B.G.main_table = reinterpret_cast<float2*>(h->G.main_table);
     B.G.base_w0 = h->G.base_w0; B.G.base_b0 = h->G.base_b0; B.G.base_w1 = h->G.base_w1; B.G.base_b1 = h->G.base_b1;
@@ -624,7 +675,7 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     }
     FinalizeArgs Z;
     memset(&Z, 0, sizeof(Z));
-    fill_ray_args(Z, rays, off, n);
+    fill_ray_args(h, Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = grad_o; Z.grad_v = grad_v;
     if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(h->M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
@@ -666,7 +717,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(M, S, st, h->sampler == NEMIT_SAMPLER_FAST); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n);
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.reg_chunk = rays->n;
     F.point_lights = 1;
@@ -687,7 +738,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
     FieldBwdArgs B;
     memset(&B, 0, sizeof(B));       // B.G stays null: ray gradients only
-    fill_ray_args(B, rays, off, n);
+    fill_ray_args(h, B, rays, off, n);
     fill_field_params(h->P, B.P);
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = 1.f;
     if (tc) {
@@ -703,7 +754,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     if (e != cudaSuccess) return cuda_fail(e, "k_field_backward");
     FinalizeArgs Z;
     memset(&Z, 0, sizeof(Z));
-    fill_ray_args(Z, rays, off, n);
+    fill_ray_args(h, Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = brightness_grad; Z.grad_v = nullptr;
     if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }

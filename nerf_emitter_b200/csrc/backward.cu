@@ -136,7 +136,7 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
   extern __shared__ __align__(16) unsigned char smem_raw[];
   BwdSmem* sm = reinterpret_cast<BwdSmem*>(smem_raw);
   const int tid = threadIdx.x;
-  load_field_weights(&sm->W, A.P, M.num_images, A.training, A.camera_idx, sm->app_tmp, tid, 128);
+  load_field_weights(&sm->W, A.P, M.num_images, A.app_row, sm->app_tmp, tid, 128);
   {
     float* z = reinterpret_cast<float*>(&sm->dW);
     for (int i = tid; i < (int)(sizeof(FieldWeightsSmem) / sizeof(float)); i += 128) z[i] = 0.f;
@@ -305,17 +305,12 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
   }
   for (int i = tid; i < 16; i += 128) atomicAdd(A.G.base_b1 + i, ls * D.base_b1[i]);
   for (int i = tid; i < 3; i += 128) atomicAdd(A.G.head_b2 + i, ls * D.head_b2[i]);
-  // appearance embedding (NS/fields/nerfacto_field.py:272-285): the camera's row in training mode, the mean
-  // of all rows in eval mode
+  // appearance embedding (NS/fields/nerfacto_field.py:272-285): row / mean / zeros as resolved by the host (appearance_component)
   for (int k = tid; k < kApp; k += 128) {
     float g = 0.f;
     for (int n = 0; n < kHidden; ++n) g = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], D.head_b0_eff[n], g);
     g *= ls;
-    if (A.training) {
-      atomicAdd(A.G.appearance + (int64_t)A.camera_idx * kApp + k, g);
-    } else {
-      for (int r = 0; r < M.num_images; ++r) atomicAdd(A.G.appearance + (int64_t)r * kApp + k, g / (float)M.num_images);
-    }
+    appearance_component_grad(A.G.appearance, M.num_images, A.app_row, k, g);
   }
 }
 

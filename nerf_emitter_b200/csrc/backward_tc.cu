@@ -147,15 +147,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, 256);
   for (int i = tid; i < 8 * 128; i += 256) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
   for (int i = tid; i < kApp; i += 256) {
-    float e;
-    if (A.training) {
-      e = A.P.appearance[(int64_t)A.camera_idx * kApp + i];
-    } else {
-      float s = 0.f;
-      for (int r = 0; r < M.num_images; ++r) s += A.P.appearance[(int64_t)r * kApp + i];
-      e = s / (float)M.num_images;
-    }
-    C->app[i] = e;
+    C->app[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
   if (t == 0) {
     tc::mbar_init(&H->mbar, 1);
@@ -432,16 +424,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
         for (int n = 0; n < 3; ++n) atomicAdd(A.G.head_b2 + n, fs * u[n]);
     }
     half_sync(half);
-    // appearance embedding (NS/fields/nerfacto_field.py:272-285): the camera's row in training mode, the mean of
-    // all rows in eval mode
+    // appearance embedding (NS/fields/nerfacto_field.py:272-285): row / mean / zeros as resolved by the host (appearance_component)
     if (t < kApp) {
       float g = 0.f;
       for (int n = 0; n < kHidden; ++n) g = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + t], H->dvec[n], g);
-      if (A.training) {
-        atomicAdd(A.G.appearance + (int64_t)A.camera_idx * kApp + t, g);
-      } else {
-        for (int q = 0; q < M.num_images; ++q) atomicAdd(A.G.appearance + (int64_t)q * kApp + t, g / (float)M.num_images);
-      }
+      appearance_component_grad(A.G.appearance, M.num_images, A.app_row, t, g);
     }
   }
   tc::tc_fence_before();

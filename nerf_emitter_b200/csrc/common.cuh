@@ -26,6 +26,8 @@ constexpr int kMainEnc = 32;
 constexpr int kHidden = 64;
 constexpr int kGeo = 15;
 constexpr int kApp = 32;
+constexpr int kAppMean = -1;   // RayArgs::app_row: mean of the embedding rows
+constexpr int kAppZero = -2;   // RayArgs::app_row: zero appearance vector
 constexpr int kHeadIn = 63;      // 16 SH + 15 geo + 32 appearance
 
 struct GridDev {

@@ -26,12 +26,12 @@ struct SamplesSmem {
 // GEMM chain as k_field_forward, without the per-ray composite.
 __global__ void __launch_bounds__(128)
 k_field_samples(const __grid_constant__ ModelDev M, const __grid_constant__ FieldParams P, const float* __restrict__ pos,
-                const float* __restrict__ dir, int64_t n, int training, int camera_idx, float* __restrict__ density,
+                const float* __restrict__ dir, int64_t n, int app_row, float* __restrict__ density,
                 float* __restrict__ geo, float* __restrict__ rgb) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   SamplesSmem* sm = reinterpret_cast<SamplesSmem*>(smem_raw);
   const int tid = threadIdx.x;
-  load_field_weights(&sm->W, P, M.num_images, training, camera_idx, sm->app_tmp, tid, 128);
+  load_field_weights(&sm->W, P, M.num_images, app_row, sm->app_tmp, tid, 128);
   const int64_t tiles = (n + kTileM - 1) / kTileM;
   for (int64_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
     const int64_t s = tile * kTileM + tid;
@@ -86,7 +86,7 @@ k_field_samples(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
 }
 
 cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const float* pos, const float* dir, int64_t n,
-                                 int training, int camera_idx, float* density, float* geo, float* rgb,
+                                 int app_row, float* density, float* geo, float* rgb,
                                  cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
@@ -97,7 +97,7 @@ cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const 
   }
   const int64_t tiles = (n + kTileM - 1) / kTileM;
   const int64_t ctas = tiles < 148 * 2 ? tiles : 148 * 2;
-  k_field_samples<<<(unsigned)ctas, 128, smem, stream>>>(M, P, pos, dir, n, training, camera_idx, density, geo, rgb);
+  k_field_samples<<<(unsigned)ctas, 128, smem, stream>>>(M, P, pos, dir, n, app_row, density, geo, rgb);
   return cudaGetLastError();
 }
 

@@ -29,7 +29,7 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FieldSmem* sm = reinterpret_cast<FieldSmem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  load_field_weights(&sm->W, A.P, M.num_images, A.training, A.camera_idx, sm->app_tmp, tid, 128);
+  load_field_weights(&sm->W, A.P, M.num_images, A.app_row, sm->app_tmp, tid, 128);
 
   const int64_t n_groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {

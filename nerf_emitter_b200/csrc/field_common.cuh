@@ -120,8 +120,26 @@ struct FieldWeightsSmem {
 
 // effective head bias = b0 + W0[:,31:63] . e, with e = embedding row (training) or the mean row (eval)
 // (NS/fields/nerfacto_field.py:272-285). Computed per CTA: 64 x 32 FMAs.
+// Component i of the appearance vector every sample of the call sees (NS/fields/nerfacto_field.py:272-285):
+// app_row >= 0: that embedding row (training mode, or always_use_camera_indices with a Rotater, NS/models/nerfacto.py:206);
+// kAppMean: the mean over rows (eval, use_average_appearance_embedding); kAppZero: zeros.  The host resolves the row
+// (RayArgs::app_row, api.cu appearance_row).
+__device__ __forceinline__ float appearance_component(const float* __restrict__ emb, int num_images, int app_row, int i) {
+  if (app_row >= 0) return emb[(int64_t)app_row * kApp + i];
+  if (app_row == kAppZero) return 0.f;
+  float s = 0.f;
+  for (int r = 0; r < num_images; ++r) s += emb[(int64_t)r * kApp + i];
+  return s / (float)num_images;
+}
+// its adjoint: g = d loss / d component i
+__device__ __forceinline__ void appearance_component_grad(float* __restrict__ gemb, int num_images, int app_row, int i, float g) {
+  if (app_row >= 0) { atomicAdd(gemb + (int64_t)app_row * kApp + i, g); return; }
+  if (app_row == kAppZero) return;
+  for (int r = 0; r < num_images; ++r) atomicAdd(gemb + (int64_t)r * kApp + i, g / (float)num_images);
+}
+
 __device__ __forceinline__ void load_field_weights(FieldWeightsSmem* S, const FieldParams& P, int num_images,
-                                                   int training, int camera_idx, float* app_tmp /*32 floats smem*/,
+                                                   int app_row, float* app_tmp /*32 floats smem*/,
                                                    int tid, int nthreads) {
   for (int i = tid; i < kHidden * kMainEnc; i += nthreads) { int n = i / kMainEnc, k = i % kMainEnc; S->base_w0[k * kHidden + n] = P.base_w0[i]; }
   for (int i = tid; i < 16 * kHidden; i += nthreads) { int n = i / kHidden, k = i % kHidden; S->base_w1[k * 16 + n] = P.base_w1[i]; }
@@ -136,15 +154,7 @@ __device__ __forceinline__ void load_field_weights(FieldWeightsSmem* S, const Fi
   for (int i = tid; i < 16; i += nthreads) S->base_b1[i] = P.base_b1[i];
   for (int i = tid; i < 4; i += nthreads) S->head_b2[i] = i < 3 ? P.head_b2[i] : 0.f;
   for (int i = tid; i < kApp; i += nthreads) {
-    float e;
-    if (training) {
-      e = P.appearance[(int64_t)camera_idx * kApp + i];
-    } else {
-      float s = 0.f;
-      for (int r = 0; r < num_images; ++r) s += P.appearance[(int64_t)r * kApp + i];
-      e = s / (float)num_images;
-    }
-    app_tmp[i] = e;
+    app_tmp[i] = appearance_component(P.appearance, num_images, app_row, i);
   }
   __syncthreads();
   for (int n = tid; n < kHidden; n += nthreads) {

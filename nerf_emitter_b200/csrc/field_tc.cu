@@ -107,15 +107,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   for (int i = tid; i < 16; i += 128) sm->bias_b1[i] = A.P.base_b1[i];
   for (int i = tid; i < 4; i += 128) sm->bias_h2[i] = i < 3 ? A.P.head_b2[i] : 0.f;
   for (int i = tid; i < kApp; i += 128) {
-    float e;
-    if (A.training) {
-      e = A.P.appearance[(int64_t)A.camera_idx * kApp + i];
-    } else {
-      float s = 0.f;
-      for (int r = 0; r < M.num_images; ++r) s += A.P.appearance[(int64_t)r * kApp + i];
-      e = s / (float)M.num_images;
-    }
-    sm->app_tmp[i] = e;
+    sm->app_tmp[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
   if (tid == 0) {
     tc::mbar_init(&sm->mbar, 1);

@@ -27,7 +27,7 @@ struct RayArgs {
   int64_t ray_offset;
   int64_t n;
   int training;
-  int camera_idx;
+  int app_row;           // appearance row resolved by the host: >= 0 a row, kAppMean, kAppZero (field_common.cuh)
   const float* jitter;   // (n_total,3) or null
   float anneal;
   int nerf_layout;       // NemitRays.layout: 0 = (3,N) Mitsuba unit cube, 1 = (N,3) NeRF coordinates (also for tangents / ray grads)
@@ -219,7 +219,7 @@ cudaError_t launch_film_accumulate(const FilmArgs& A, cudaStream_t stream);
 cudaError_t launch_film_develop(int64_t n, const float* accum, float* rgba, cudaStream_t stream);
 
 cudaError_t launch_field_samples(const ModelDev& M, const FieldParams& P, const float* pos, const float* dir, int64_t n,
-                                 int training, int camera_idx, float* density, float* geo, float* rgb,
+                                 int app_row, float* density, float* geo, float* rgb,
                                  cudaStream_t stream);
 cudaError_t launch_prop_density(const ModelDev& M, const GridDev& G, const float2* table, const float* w0,
                                 const float* b0, const float* w1, const float* b1, const float* pos, int64_t n,

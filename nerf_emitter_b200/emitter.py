@@ -169,6 +169,23 @@ class NerfEmitter:
         self.sampler = sampler
         return self
 
+    def set_appearance_mode(self, always_use_camera_indices: bool = False,
+                            use_average_appearance_embedding: bool = True, rotation_ids=None):
+        """The model built with a ``Rotater`` (turntable captures, NS/models/nerfacto.py:186-206): the appearance
+        embedding has one row per rotation, the row is used in eval mode too (``always_use_camera_indices``) and
+        ``rotation_ids`` (``Rotater.rotation_ids``) maps camera index -> rotation id on every ray-level call exactly
+        as ``Rotater.map_rotation_ids`` does (NS/field_components/rotater.py:94-100)."""
+        ids = None if rotation_ids is None else [int(x) for x in rotation_ids]
+        n = 0 if ids is None else len(ids)
+        arr = (C.c_int32 * n)(*ids) if n else None
+        L.check(self.lib.nemit_set_appearance_mode(self._h, int(bool(always_use_camera_indices)),
+                                                   int(bool(use_average_appearance_embedding)), arr, n),
+                "nemit_set_appearance_mode")
+        self.always_use_camera_indices = bool(always_use_camera_indices)
+        self.use_average_appearance_embedding = bool(use_average_appearance_embedding)
+        self.rotation_ids = ids
+        return self
+
     def train(self, mode: bool = True):
         self.training = bool(mode)
         return self

@@ -21,7 +21,7 @@ from __future__ import annotations
 
 import ctypes as C
 from dataclasses import dataclass
-from typing import Callable, Dict, List, Optional, Tuple
+from typing import Callable, Dict, List, Optional, Sequence, Tuple
 
 import torch
 from torch import nn
@@ -369,9 +369,17 @@ class SdfNerfactoModel(nn.Module):
     def __init__(self, num_train_data: int = 4, scene_scale: float = 1.0, spec: Optional[EmitterModelSpec] = None,
                  disable_inside_aabb: bool = True, precision: str = "fp32", sampler: str = "exact",
                  interlevel_loss_mult: float = 1.0, distortion_loss_mult: float = 7e-3,
-                 backward_num_rays_per_chunk: int = 16384) -> None:
+                 backward_num_rays_per_chunk: int = 16384, rotation_ids: Optional[Sequence[int]] = None,
+                 use_average_appearance_embedding: bool = True) -> None:
         super().__init__()
         import weakref
+        # With a Rotater (turntable captures) the reference sizes the appearance embedding by the number of rotations
+        # and sets always_use_camera_indices (nerfacto.py:186-206); ``rotation_ids`` is ``Rotater.rotation_ids``
+        # (camera -> rotation id, rotater.py:36-37), applied to the final samples by sdf_nerfacto.py:71-72.
+        self.rotation_ids = None if rotation_ids is None else [int(x) for x in rotation_ids]
+        self.use_average_appearance_embedding = use_average_appearance_embedding
+        if self.rotation_ids is not None:
+            num_train_data = len(set(self.rotation_ids))
         spec = spec or EmitterModelSpec(num_images=num_train_data)
         self.spec, self.scene_scale = spec, float(scene_scale)
         self.precision, self.sampler_mode = precision, sampler
@@ -417,6 +425,8 @@ class SdfNerfactoModel(nn.Module):
                                   disable_inside_aabb=self.disable_inside_aabb,
                                   interlevel_mult=self.interlevel_loss_mult, distortion_mult=self.distortion_loss_mult)
             self._E.set_precision(self.precision).set_sampler(self.sampler_mode)
+            self._E.set_appearance_mode(self.rotation_ids is not None, self.use_average_appearance_embedding,
+                                        self.rotation_ids)
             self._bound_ptrs = ptrs
         elif ptrs != self._bound_ptrs:
             self._E.bind_params({k: p.data for k, p in P.items()})

@@ -293,7 +293,8 @@ def sh16(v):
 # A10 + A12 + A13 + A7 + A14  main field on the 48 final samples and compositing
 # --------------------------------------------------------------------------------------------
 def main_stage(P, spec: EmitterModelSpec, o, d, t_edges, aabb, *, training: bool, camera_idx: int,
-               disable_inside_aabb=True, sh_carries_reverse_grad=False, grad_scaling=True):
+               disable_inside_aabb=True, sh_carries_reverse_grad=False, grad_scaling=True,
+               always_use_camera_indices=False):
     """nerfstudio/fields/nerfacto_field.py:228-334 (get_density, get_outputs), Field.forward
     (base_field.py:124-143), scale_gradients_by_distance_squared (losses.py:558-577),
     get_weights (cameras/rays.py:128-150), RGBRenderer (model_components/renderers.py:71-121,203-234).
@@ -315,7 +316,7 @@ def main_stage(P, spec: EmitterModelSpec, o, d, t_edges, aabb, *, training: bool
     # directions through SH, while forward-mode tangents do flow (no_grad does not stop them).
     sh = sh16(dn if sh_carries_reverse_grad else _no_reverse(dn)).reshape(-1, 16)
     emb = P["field.embedding_appearance.embedding.weight"]
-    if training:
+    if training or always_use_camera_indices:      # nerfacto_field.py:275
         app = emb[camera_idx][None, :].expand(N * S, -1)
     else:
         app = torch.ones(N * S, spec.appearance_dim) * emb.mean(dim=0)
@@ -393,7 +394,12 @@ class OracleEmitter:
 
     def __init__(self, params: Dict[str, torch.Tensor], spec: Optional[EmitterModelSpec] = None,
                  scene_scale: float = 1.0, disable_inside_aabb: bool = True,
-                 interlevel_mult: float = 1.0, distortion_mult: float = 7e-3):
+                 interlevel_mult: float = 1.0, distortion_mult: float = 7e-3,
+                 always_use_camera_indices: bool = False, rotation_ids=None):
+        # a model built with a Rotater has always_use_camera_indices=True and one embedding row per rotation
+        # (nerfstudio/models/nerfacto.py:186-206); rotation_ids = Rotater.rotation_ids
+        self.always_use_camera_indices = always_use_camera_indices
+        self.rotation_ids = None if rotation_ids is None else [int(x) for x in rotation_ids]
         self.P = {k: v.detach().clone().float().cpu() for k, v in params.items()}
         self.spec = spec or EmitterModelSpec()
         self.scene_scale = scene_scale
@@ -406,6 +412,13 @@ class OracleEmitter:
 
     def train(self, mode: bool = True):
         self.training = mode
+
+    def _cam(self, camera_idx):
+        """Rotater.map_rotation_ids (nerfstudio/field_components/rotater.py:94-100) as applied to the final samples'
+        camera_indices by sdf_nerfacto.py:71-72,92-93,127-128,198-199."""
+        if self.rotation_ids is None:
+            return camera_idx
+        return self.rotation_ids[min(camera_idx, len(self.rotation_ids) - 1)]
 
     def _near_plane(self):
         # NearFarCollider (scene_colliders.py:217-222): 0 in eval mode
@@ -425,7 +438,8 @@ class OracleEmitter:
         o, d = rays_mi_to_nerf(o + near * v, v, self.scene_scale)
         lv = self._levels(o, d, jitter)
         rgb, w, sigma, rgb_s = main_stage(self.P, self.spec, o, d, lv["t_edges"][2], self.aabb,
-                                          training=self.training, camera_idx=camera_idx,
+                                          training=self.training, camera_idx=self._cam(camera_idx),
+                                          always_use_camera_indices=self.always_use_camera_indices,
                                           disable_inside_aabb=self.disable_inside_aabb)
         if not return_aux:
             return rgb
@@ -451,7 +465,8 @@ class OracleEmitter:
         with forward_ad.dual_level():
             od, dd = rays_mi_to_nerf(forward_ad.make_dual(o, go), forward_ad.make_dual(v, gv), self.scene_scale)
             rgb, _, _, _ = main_stage(self.P, self.spec, od, dd, lv["t_edges"][2], self.aabb,
-                                      training=self.training, camera_idx=camera_idx,
+                                      training=self.training, camera_idx=self._cam(camera_idx),
+                                      always_use_camera_indices=self.always_use_camera_indices,
                                       disable_inside_aabb=self.disable_inside_aabb, grad_scaling=False)
             t = forward_ad.unpack_dual(rgb).tangent
         t = t.clone()
@@ -470,7 +485,8 @@ class OracleEmitter:
             o, d = rays_mi_to_nerf(oo, vv, self.scene_scale)
             lv = self._levels(o.detach(), d.detach(), jitter, proposal_requires_grad=proposal_requires_grad)
             rgb, w, _, _ = main_stage(P, self.spec, o, d, lv["t_edges"][2], self.aabb, training=self.training,
-                                      camera_idx=camera_idx, disable_inside_aabb=self.disable_inside_aabb)
+                                      camera_idx=self._cam(camera_idx), disable_inside_aabb=self.disable_inside_aabb,
+                                      always_use_camera_indices=self.always_use_camera_indices)
             ws = lv["weights"] + [w]
             loss = torch.sum(rgb * grad_out)
             loss = loss + self.interlevel_mult * interlevel_loss(ws, lv["s_edges"])
@@ -498,7 +514,8 @@ class OracleEmitter:
         lv = self._levels(o.detach(), d, jitter)
         t_edges = lv["t_edges"][2]
         rgb, w, _, rgb_s = main_stage(self.P, self.spec, o, d, t_edges, self.aabb, training=self.training,
-                                      camera_idx=camera_idx, disable_inside_aabb=self.disable_inside_aabb)
+                                      camera_idx=self._cam(camera_idx), disable_inside_aabb=self.disable_inside_aabb,
+                                      always_use_camera_indices=self.always_use_camera_indices)
         brightness = torch.sum(rgb * wts, dim=-1, keepdim=True)
         (grad,) = torch.autograd.grad(brightness, o, grad_outputs=torch.ones_like(brightness))
         lum = torch.sum(rgb_s.detach() * wts, dim=-1, keepdim=True)

@@ -29,7 +29,12 @@ MI2GL_LEFT = torch.tensor([[0., 0., 1., 0.], [1., 0., 0., 0.], [0., 1., 0., 0.],
 class ReferenceEmitter:
     def __init__(self, params: Dict[str, torch.Tensor], spec: Optional[EmitterModelSpec] = None,
                  scene_scale: float = 1.0, disable_inside_aabb: bool = True,
-                 interlevel_mult: float = 1.0, distortion_mult: float = 7e-3):
+                 interlevel_mult: float = 1.0, distortion_mult: float = 7e-3,
+                 always_use_camera_indices: bool = False, rotation_ids=None):
+        # always_use_camera_indices / rotation_ids: the model as NerfactoModel.populate_modules builds it when the
+        # datamanager carries a Rotater (nerfacto.py:186-206).  The Rotater class itself imports mitsuba at module
+        # scope (rotater.py:7), so its three-line map_rotation_ids (:94-100) is repeated in _map_rotation_ids below.
+        self.rotation_ids = None if rotation_ids is None else torch.tensor([int(x) for x in rotation_ids])
         self.ns = ns = import_reference()
         self.spec = spec = spec or EmitterModelSpec()
         self.scene_scale = scene_scale
@@ -45,7 +50,7 @@ class ReferenceEmitter:
             spatial_distortion=contraction, num_images=spec.num_images, use_pred_normals=False,
             use_average_appearance_embedding=True, color_output_activation="RawNeRF",
             rgb_bias=spec.rgb_bias, appearance_embedding_dim=spec.appearance_dim,
-            implementation="torch", always_use_camera_indices=False)
+            implementation="torch", always_use_camera_indices=always_use_camera_indices)
         self.props = torch.nn.ModuleList()
         for g in spec.prop_grids:
             self.props.append(ns.density_fields.HashMLPDensityField(
@@ -105,8 +110,13 @@ class ReferenceEmitter:
     def _density_fns(self):
         return [p.density_fn for p in self.props]
 
+    def _map_rotation_ids(self, camera_indices):
+        return self.rotation_ids[camera_indices.clamp(max=len(self.rotation_ids) - 1)]
+
     def _field_and_render(self, ray_samples, grad_scaling=True):
         F = self.ns.FieldHeadNames
+        if self.rotation_ids is not None:                        # sdf_nerfacto.py:71-72
+            ray_samples.camera_indices = self._map_rotation_ids(ray_samples.camera_indices)
         out = self.field.forward(ray_samples, compute_normals=False)
         if grad_scaling:
             # losses.py:558-577. Identity in the primal; `_GradientScaler` defines no jvp, and on

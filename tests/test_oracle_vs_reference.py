@@ -58,3 +58,29 @@ def test_point_lights_oracle_equals_reference_live(spec, params_factory):
     b = O.point_lights(o, v)
     assert torch.equal(a["rgb"], b["rgb"]) and torch.equal(a["depth"], b["depth"])
     assert rel_err(b["brightness_grad"], a["brightness_grad"]) < 1e-5
+
+
+@pytest.mark.parametrize("camera_idx", [4, 9])
+def test_turntable_appearance_mode_equals_reference_live(camera_idx, spec, params_factory):
+    """Model built with a Rotater (nerfacto.py:186-206): always_use_camera_indices, camera -> rotation id mapping
+    (rotater.py:94-100, sdf_nerfacto.py:71-72); the embedding row is used in eval mode too."""
+    from oracle.nerfacto_oracle import OracleEmitter
+    from oracle.ref_harness import ReferenceEmitter
+    P = params_factory(0, 1e3)
+    ids = [0, 1, 1, 3, 2, 0]
+    R = ReferenceEmitter(P, spec, always_use_camera_indices=True, rotation_ids=ids)
+    O = OracleEmitter(P, spec, always_use_camera_indices=True, rotation_ids=ids)
+    N = 200
+    o, v, g = make_rays(N, seed=13)
+    a = R.render(o, v, camera_idx=camera_idx)
+    b = O.render(o, v, camera_idx=camera_idx)
+    assert torch.equal(a, b)
+    assert not torch.equal(b, OracleEmitter(P, spec).render(o, v, camera_idx=camera_idx))     # differs from the mean embedding
+    gout = torch.randn(N, 3, generator=g)
+    go_r, gv_r, gr, _ = R.vjp(o, v, gout, camera_idx=camera_idx, proposal_requires_grad=False)
+    go_o, gv_o, gq, _ = O.vjp(o, v, gout, camera_idx=camera_idx, proposal_requires_grad=False)
+    assert rel_err(go_o, go_r) < 1e-5 and rel_err(gv_o, gv_r) < 1e-5
+    k = "field.embedding_appearance.embedding.weight"
+    row = ids[min(camera_idx, len(ids) - 1)]
+    assert rel_err(gq[k], gr[k], floor=1e-30) < 1e-4
+    assert gq[k][row].abs().max() > 0 and gq[k].abs().sum() == gq[k][row].abs().sum()          # only that row gets a gradient

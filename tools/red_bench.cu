@@ -20,6 +20,18 @@ __global__ void k_red(float* table, uint32_t mask_entries, int ops_per_thread, i
   }
 }
 
+// do random L1-missing gathers and random reductions share one path?  Each thread issues `nl` float2 gathers and `nr`
+// float2 reductions per iteration on two different 64 MiB tables.
+__global__ void k_mix(const float2* __restrict__ src, float* dst, uint32_t mask_entries, int iters, int nl, int nr, float* sink) {
+  uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+  float acc = 0.f;
+  for (int i = 0; i < iters; ++i) {
+    for (int j = 0; j < nl; ++j) { float2 v = __ldg(src + (rng(s) & mask_entries)); acc += v.x + v.y; }
+    for (int j = 0; j < nr; ++j) atomicAdd(reinterpret_cast<float2*>(dst) + (rng(s) & mask_entries), make_float2(1.f, 2.f));
+  }
+  if (acc == 123.456f) *sink = acc;
+}
+
 int main() {
   const size_t entries = 1u << 23;                      // 8 Mi entries x 8 B = 64 MiB
   float* t; CK(cudaMalloc(&t, entries * 8)); CK(cudaMemset(t, 0, entries * 8));
@@ -49,6 +61,22 @@ int main() {
     float ms; cudaEventElapsedTime(&ms, a, b);
     double lane_ops = (double)blocks * threads * ops;
     printf("random  W=%d 8 warps/SM: %.3f ms, %.1f G lane-ops/s, %.2f SM-cycles per lane-op\n", W, ms, lane_ops / ms * 1e-6, ms * 1e-3 * 1.9e9 * 148 / lane_ops);
+  }
+  {
+    float2* src; CK(cudaMalloc(&src, entries * 8)); CK(cudaMemset(src, 0, entries * 8));
+    float* sink; CK(cudaMalloc(&sink, 4));
+    const int blocks = 148 * 8, threads = 256, iters = 128;
+    const int cfg[5][2] = {{4, 0}, {0, 4}, {4, 4}, {4, 2}, {2, 4}};
+    for (uint32_t mask : {(uint32_t)entries - 1, (uint32_t)entries / 4 - 1})      // 2 x 64 MiB (exceeds the 126 MB L2) and 2 x 16 MiB
+    for (auto& c : cfg) {
+      auto launch = [&] { k_mix<<<blocks, threads>>>(src, t, mask, iters, c[0], c[1], sink); };
+      launch(); CK(cudaDeviceSynchronize());
+      cudaEventRecord(a); launch(); cudaEventRecord(b); CK(cudaDeviceSynchronize());
+      float ms; cudaEventElapsedTime(&ms, a, b);
+      const double cyc = ms * 1e-3 * 1.9e9 * 148 / ((double)blocks * threads * iters);
+      printf("mixed (%u MiB per table): %d gathers + %d reds per iteration: %.3f ms, %.2f SM-cycles per iteration (sum of the separate costs: %.2f)\n",
+             (mask + 1) >> 17, c[0], c[1], ms, cyc, c[0] * 1.0 + c[1] * 1.5);
+    }
   }
   return 0;
 }
