@@ -304,10 +304,42 @@ class NerfEmitter:
                  chunk_rays: Optional[int] = None, loss_scale: float = 1.0, proposal_requires_grad: bool = True,
                  nerf_layout: bool = False):
         """NeRFEmitterOp.ns_backward_ray (nerf_emitter_op.py:92-117): returns (grad_o, grad_v) as (3,N);
-        parameter gradients are accumulated into the bound ``grads``."""
+        parameter gradients are accumulated into the bound ``grads``.  ``proposal_requires_grad`` is the sampler's
+        ``updated`` flag (ray_samplers.py:598): one bool for the whole call, or one bool per chunk of ``chunk_rays``
+        rays (the reference evaluates it per sampler call, i.e. per chunk; runs of equal flags go to the library
+        together, the regulariser means being per chunk either way)."""
         if not self.grads:
             self.bind_grads()
         n = o3n.shape[0] if nerf_layout else o3n.shape[1]
+        if not isinstance(proposal_requires_grad, (bool, int)):
+            flags = [bool(f) for f in proposal_requires_grad]
+            chunk = int(chunk_rays or n)
+            if len(flags) != (n + chunk - 1) // max(chunk, 1):
+                raise ValueError("proposal_requires_grad: one flag per chunk of chunk_rays rays expected")
+            if len(set(flags)) <= 1:
+                proposal_requires_grad = bool(flags[0]) if flags else True
+            else:
+                if isinstance(jitter, (list, tuple)):
+                    jitter = torch.cat([j.reshape(n, 1) for j in jitter], dim=1)
+                go, gv = torch.empty_like(o3n), torch.empty_like(o3n)
+                rows = (lambda t, a, b: t[a:b]) if nerf_layout else (lambda t, a, b: t[:, a:b].contiguous())
+                c0 = 0
+                while c0 < len(flags):
+                    c1 = c0 + 1
+                    while c1 < len(flags) and flags[c1] == flags[c0]:
+                        c1 += 1
+                    a, b = c0 * chunk, min(c1 * chunk, n)
+                    nr = near[a:b] if isinstance(near, torch.Tensor) and near.numel() > 1 else near
+                    g_o, g_v = self.backward(rows(o3n, a, b), rows(v3n, a, b), grad_rgb[a:b], near=nr,
+                                             camera_idx=camera_idx, jitter=None if jitter is None else jitter[a:b],
+                                             chunk_rays=chunk, loss_scale=loss_scale,
+                                             proposal_requires_grad=flags[c0], nerf_layout=nerf_layout)
+                    if nerf_layout:
+                        go[a:b], gv[a:b] = g_o, g_v
+                    else:
+                        go[:, a:b], gv[:, a:b] = g_o, g_v
+                    c0 = c1
+                return go, gv
         R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
         _check(grad_rgb, (n, 3), "grad_rgb")
         go = torch.empty_like(o3n)

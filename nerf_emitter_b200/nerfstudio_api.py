@@ -300,7 +300,21 @@ class ProposalNetworkSampler:
         self.num_nerf_samples_per_ray = num_nerf_samples_per_ray
         self.num_proposal_samples_per_ray = tuple(num_proposal_samples_per_ray)
         self.num_proposal_network_iterations = num_proposal_network_iterations
+        self.update_sched = update_sched if update_sched is not None else (lambda step: 1)
         self._anneal, self._steps_since_update, self._step = 1.0, 0, 0
+
+    def _consume_update(self, num_calls: int = 1) -> List[bool]:
+        """The ``updated`` state machine of ray_samplers.py:598,622-623 for ``num_calls`` consecutive sampler calls
+        (one per chunk of the caller's chunk loop): a call is "updated" (proposal densities carry autograd) when
+        ``_steps_since_update > update_sched(_step)`` or ``_step < 10``, and every updated call - the no-grad primal
+        ones included - resets the counter."""
+        flags = []
+        for _ in range(int(num_calls)):
+            updated = self._steps_since_update > self.update_sched(self._step) or self._step < 10
+            if updated:
+                self._steps_since_update = 0
+            flags.append(bool(updated))
+        return flags
 
     def set_anneal(self, anneal: float) -> None:
         self._anneal = anneal
@@ -318,6 +332,7 @@ class ProposalNetworkSampler:
         model = self._owner()
         E = model._emitter()
         E.anneal = float(self._anneal)
+        self._consume_update()
         o, d = _cuda_f32(ray_bundle.origins, "origins"), _cuda_f32(ray_bundle.directions, "directions")
         aux = E.sample_levels(o, d, camera_idx=ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
         near = E.spec.near_plane if E.training else 0.0
@@ -361,6 +376,10 @@ def _spacing_inv(x):     # ray_samplers.py:251
 # -------------------------------------------------------------------------------------------------------------
 # the model
 # -------------------------------------------------------------------------------------------------------------
+def _num_chunks(num_rays: int, chunk: int) -> int:
+    return (int(num_rays) + int(chunk) - 1) // int(chunk)
+
+
 class SdfNerfactoModel(nn.Module):
     """NerfactoModel.populate_modules (NS/models/nerfacto.py:169-299) with the sdf-nerfacto overrides
     (NS/configs/method_configs.py:314-326) + the three emitter entry points of SdfNerfactoModel / Model /
@@ -369,7 +388,9 @@ class SdfNerfactoModel(nn.Module):
     def __init__(self, num_train_data: int = 4, scene_scale: float = 1.0, spec: Optional[EmitterModelSpec] = None,
                  disable_inside_aabb: bool = True, precision: str = "fp32", sampler: str = "exact",
                  interlevel_loss_mult: float = 1.0, distortion_loss_mult: float = 7e-3,
-                 backward_num_rays_per_chunk: int = 16384, rotation_ids: Optional[Sequence[int]] = None,
+                 backward_num_rays_per_chunk: int = 16384, eval_num_rays_per_chunk: int = 16384,
+                 forward_ad_num_rays_per_chunk: int = 4096, proposal_update_every: int = 1,
+                 proposal_warmup: int = 5000, rotation_ids: Optional[Sequence[int]] = None,
                  use_average_appearance_embedding: bool = True) -> None:
         super().__init__()
         import weakref
@@ -385,7 +406,12 @@ class SdfNerfactoModel(nn.Module):
         self.precision, self.sampler_mode = precision, sampler
         self.disable_inside_aabb = disable_inside_aabb
         self.interlevel_loss_mult, self.distortion_loss_mult = interlevel_loss_mult, distortion_loss_mult
+        # chunk sizes of the three chunk loops (base_model.py:53-58 as overridden by sdf-nerfacto,
+        # method_configs.py:315-316): they only matter for the sampler's per-call state machine and, in the backward,
+        # for the per-chunk regulariser means
         self.backward_num_rays_per_chunk = backward_num_rays_per_chunk
+        self.eval_num_rays_per_chunk = eval_num_rays_per_chunk
+        self.forward_ad_num_rays_per_chunk = forward_ad_num_rays_per_chunk
         aabb = torch.tensor([[-scene_scale] * 3, [scene_scale] * 3], dtype=torch.float32)
         mg = spec.main_grid
         self.field = NerfactoField(aabb, num_images=spec.num_images, hidden_dim=spec.hidden_dim,
@@ -403,7 +429,14 @@ class SdfNerfactoModel(nn.Module):
         for net in self.proposal_networks:
             net._owner = ref
         self.density_fns = [net.density_fn for net in self.proposal_networks]      # nerfacto.py:229
-        self.proposal_sampler = ProposalNetworkSampler(ref, spec.num_nerf_samples, spec.num_proposal_samples)
+
+        def update_schedule(step):                      # nerfacto.py:237-242
+            x = min(max(step / proposal_warmup, 0.0), 1.0) * proposal_update_every if proposal_warmup > 0 \
+                else float(proposal_update_every)
+            return min(max(x, 1.0), float(proposal_update_every))
+
+        self.proposal_sampler = ProposalNetworkSampler(ref, spec.num_nerf_samples, spec.num_proposal_samples,
+                                                       update_sched=update_schedule)
         self._E: Optional[NerfEmitter] = None
         self._bound_ptrs: Tuple[int, ...] = ()
 
@@ -444,6 +477,7 @@ class SdfNerfactoModel(nn.Module):
     def get_rgb_for_camera_ray_bundle(self, camera_ray_bundle: RayBundle, jitter=None) -> torch.Tensor:
         """base_model.py:290-313 -> SdfNerfactoModel.get_rgb (sdf_nerfacto.py:64-83): (N,3) radiance."""
         E = self._emitter()
+        self.proposal_sampler._consume_update(_num_chunks(len(camera_ray_bundle), self.eval_num_rays_per_chunk))
         return E.render(_cuda_f32(camera_ray_bundle.origins, "origins"), _cuda_f32(camera_ray_bundle.directions, "directions"),
                         camera_idx=camera_ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
 
@@ -454,6 +488,7 @@ class SdfNerfactoModel(nn.Module):
                                            grad_v: torch.Tensor, jitter=None) -> torch.Tensor:
         """base_model.py:315-344 -> forward_grad (sdf_nerfacto.py:85-113): tangent of the radiance, (N,3)."""
         E = self._emitter()
+        self.proposal_sampler._consume_update(_num_chunks(len(camera_ray_bundle), self.forward_ad_num_rays_per_chunk))
         return E.jvp(_cuda_f32(camera_ray_bundle.origins, "origins"), _cuda_f32(camera_ray_bundle.directions, "directions"),
                      _cuda_f32(grad_o.reshape(-1, 3), "grad_o"), _cuda_f32(grad_v.reshape(-1, 3), "grad_v"),
                      camera_idx=camera_ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
@@ -465,6 +500,7 @@ class SdfNerfactoModel(nn.Module):
         """sdf_nerfacto.py:189-212: {"rgb", "depth" (contrib), "brightness_grad"} for the light point cloud
         (NS/model_components/output_light_pc.py:74-173)."""
         E = self._emitter()
+        self.proposal_sampler._consume_update()          # called per chunk by its driver (base_model.py:260-288)
         return E.point_lights(_cuda_f32(ray_bundle.origins, "origins"), _cuda_f32(ray_bundle.directions, "directions"),
                               camera_idx=ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
 
@@ -481,13 +517,15 @@ class SdfNerfactoModel(nn.Module):
         if getattr(self, "_bound_gptrs", None) != gptrs:
             E.bind_grads({k: p.grad for k, p in P.items()})
             self._bound_gptrs = gptrs
-        updated = self.proposal_sampler._steps_since_update > 5 or self.proposal_sampler._step < 10
-        go, gv = E.backward(_cuda_f32(camera_ray_bundle.origins, "origins"),
-                            _cuda_f32(camera_ray_bundle.directions, "directions"),
-                            _cuda_f32(grad_out.reshape(-1, 3), "grad_out"), camera_idx=camera_ray_bundle.camera_index(),
-                            jitter=jitter, chunk_rays=self.backward_num_rays_per_chunk, loss_scale=loss_scale,
-                            proposal_requires_grad=updated, nerf_layout=True)
-        if updated:
-            self.proposal_sampler._steps_since_update = 0
+        o = _cuda_f32(camera_ray_bundle.origins, "origins")
+        d = _cuda_f32(camera_ray_bundle.directions, "directions")
+        g = _cuda_f32(grad_out.reshape(-1, 3), "grad_out")
+        n, chunk = o.shape[0], self.backward_num_rays_per_chunk
+        if isinstance(jitter, (list, tuple)):
+            jitter = torch.cat([j.reshape(n, 1) for j in jitter], dim=1)
+        # one sampler call per chunk: the flag can differ between the first chunk and the rest (quirk 13)
+        flags = self.proposal_sampler._consume_update(_num_chunks(n, chunk))
+        go, gv = E.backward(o, d, g, camera_idx=camera_ray_bundle.camera_index(), jitter=jitter, chunk_rays=chunk,
+                            loss_scale=loss_scale, proposal_requires_grad=flags, nerf_layout=True)
         camera_ray_bundle.origins.grad = go
         camera_ray_bundle.directions.grad = gv

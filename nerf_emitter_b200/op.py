@@ -35,6 +35,25 @@ def _near_arg(near):
     return float(near)
 
 
+def consume_sampler_updates(sampler, num_calls: int):
+    """Advance the ``updated`` state machine of a ``ProposalNetworkSampler`` - the reference's own object or the mirror
+    in ``nerfstudio_api`` - by ``num_calls`` sampler calls and return the flag of each (ray_samplers.py:598,622-623,
+    SURVEY.md 8a quirk 13).  ``None`` (no sampler object kept) means "always updated"."""
+    if sampler is None:
+        return [True] * int(num_calls)
+    flags = []
+    for _ in range(int(num_calls)):
+        updated = sampler._steps_since_update > sampler.update_sched(sampler._step) or sampler._step < 10
+        if updated:
+            sampler._steps_since_update = 0
+        flags.append(bool(updated))
+    return flags
+
+
+def _chunks(n: int, chunk: Optional[int]) -> int:
+    return 1 if not chunk else (int(n) + int(chunk) - 1) // int(chunk)
+
+
 def emitter_primal(E: NerfEmitter, o3n, v3n, near=0.0, camera_idx=0, jitter=None):
     """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> (N,3)."""
     return E.render(o3n.contiguous(), v3n.contiguous(), near=_near_arg(near), camera_idx=camera_idx, jitter=jitter)
@@ -61,24 +80,32 @@ class NerfEmitterFunction(torch.autograd.Function):
     jitter, chunk_rays)``; ``rgb.backward(g)`` fills o/v gradients and accumulates parameter gradients."""
 
     @staticmethod
-    def forward(ctx, E, o3n, v3n, dummy, near, camera_idx, jitter, chunk_rays):
+    def forward(ctx, E, o3n, v3n, dummy, near, camera_idx, jitter, chunk_rays, sampler=None):
         ctx.E, ctx.near, ctx.camera_idx, ctx.jitter, ctx.chunk_rays = E, near, camera_idx, jitter, chunk_rays
+        ctx.sampler = sampler
         ctx.save_for_backward(o3n, v3n, dummy)
+        consume_sampler_updates(sampler, _chunks(o3n.shape[1], chunk_rays))      # the no-grad primal chunks count too
         return emitter_primal(E, o3n.detach(), v3n.detach(), near, camera_idx, jitter)
 
     @staticmethod
     def backward(ctx, grad_out):
         o3n, v3n, dummy = ctx.saved_tensors
+        flags = consume_sampler_updates(ctx.sampler, _chunks(o3n.shape[1], ctx.chunk_rays))
         go, gv = emitter_vjp(ctx.E, o3n.detach(), v3n.detach(), grad_out, ctx.near, ctx.camera_idx, ctx.jitter,
-                             ctx.chunk_rays)
+                             ctx.chunk_rays, proposal_requires_grad=flags)
         gd = torch.zeros_like(dummy) if dummy is not None else None       # nerf_emitter_op.py:116
-        return None, go, gv, gd, None, None, None, None
+        return None, go, gv, gd, None, None, None, None, None
 
 
-def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chunk_rays: Optional[int] = 16384):
+def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chunk_rays: Optional[int] = 16384,
+                         sampler=None, forward_ad_chunk_rays: Optional[int] = 4096):
     """The callable to hand to ``NeRFEmitter.set_op``.  ``jitter_fn(n)`` returns the (n,3) per-ray jitter drawn from
     the samplers' generators in training mode (the reference re-seeds them between primal and adjoint,
-    NS/models/base_model.py:299,327-328); ``chunk_rays`` = ``backward_num_rays_per_chunk``."""
+    NS/models/base_model.py:299,327-328); ``chunk_rays`` = ``backward_num_rays_per_chunk`` (= ``eval_num_rays_per_chunk``
+    in sdf-nerfacto, method_configs.py:315-316).  ``sampler``: the model's ``ProposalNetworkSampler`` object (the
+    reference's own, which the trainer keeps stepping through ``step_cb``, or the mirror): its ``updated`` state
+    machine then decides per chunk whether the proposal networks get a gradient, and every primal / tangent chunk
+    advances it, as in the reference (``consume_sampler_updates``); without it every backward chunk updates them."""
     guiding = path_guiding or _NoGuiding()
     try:
         import drjit as dr          # noqa: F401
@@ -88,7 +115,7 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
 
     def torch_op(o3n, v3n, near, dummy, guiding_weight, camera_idx):
         jit = jitter_fn(o3n.shape[1]) if (jitter_fn is not None and E.training) else None
-        rgb = NerfEmitterFunction.apply(E, o3n, v3n, dummy, near, camera_idx, jit, chunk_rays)
+        rgb = NerfEmitterFunction.apply(E, o3n, v3n, dummy, near, camera_idx, jit, chunk_rays, sampler)
         guiding.train_primal(o3n.t(), v3n.t(), rgb, guiding_weight)
         return rgb.reshape(-1)
 
@@ -104,12 +131,14 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
             def eval(self, o, v, dummy):
                 self.o, self.v = o.torch(), v.torch()
                 state["jit"] = jitter_fn(self.o.shape[1]) if (jitter_fn is not None and E.training) else None
+                consume_sampler_updates(sampler, _chunks(self.o.shape[1], chunk_rays))
                 rgb = emitter_primal(E, self.o, self.v, near, camera_idx, state["jit"])
                 guiding.train_primal(self.o.t(), self.v.t(), rgb, gw)
                 return type(o)(rgb.reshape(-1))
 
             def forward(self):
                 go, gv, _ = self.grad_in("args")
+                consume_sampler_updates(sampler, _chunks(self.o.shape[1], forward_ad_chunk_rays))
                 t = emitter_jvp(E, self.o, self.v, go.torch().reshape(3, -1), gv.torch().reshape(3, -1), near,
                                 camera_idx, state["jit"])
                 guiding.train_forward(self.o.t(), self.v.t(), t, gw)
@@ -117,7 +146,9 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
 
             def backward(self):
                 g = self.grad_out().torch().reshape(-1, 3)
-                go, gv = emitter_vjp(E, self.o, self.v, g, near, camera_idx, state["jit"], chunk_rays)
+                flags = consume_sampler_updates(sampler, _chunks(self.o.shape[1], chunk_rays))
+                go, gv = emitter_vjp(E, self.o, self.v, g, near, camera_idx, state["jit"], chunk_rays,
+                                     proposal_requires_grad=flags)
                 guiding.train_backward(self.o.t(), self.v.t(), go.t(), gw)
                 T = type(self.grad_out())
                 self.set_grad_in("args", (T(go), T(gv), T(torch.zeros(1, device=go.device))))

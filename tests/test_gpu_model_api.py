@@ -166,3 +166,42 @@ def test_sampler_training_mode_with_jitter(model, spec, params_factory):
     assert rel_err(t2, aux["t_edges2"]) < 1e-3
     # euclidean edges of level 0 start at the training near plane 0.05 (NearFarCollider), moved inwards by the jitter
     assert spec.near_plane - 1e-6 <= float(rsl[0].frustums.starts.min()) < spec.near_plane + 0.01
+
+
+def test_backward_chunks_follow_the_sampler_update_state_machine(model, spec, params_factory):
+    """ray_samplers.py:598,622-623: with ``_steps_since_update > update_sched`` the FIRST backward chunk gives the
+    proposal networks a gradient and resets the counter, the following chunks do not; with ``_step < 10`` every chunk
+    does.  The model's chunk loop must equal per-chunk library calls with those flags."""
+    from nerf_emitter_b200 import NerfEmitter
+    from nerf_emitter_b200.nerfstudio_api import RayBundle
+    N, C = 500, 200
+    o3n, v3n, g = make_rays(N, seed=17)
+    o, d = _nerf_rays(o3n, v3n)
+    gout = torch.randn(N, 3, generator=g).to(DEV)
+    jit = torch.rand(N, 3, generator=g).to(DEV)
+    E = NerfEmitter(params_factory(0, 1e3), spec, device=torch.device(DEV)).train(True)
+    old_chunk = model.backward_num_rays_per_chunk
+    model.backward_num_rays_per_chunk = C
+    model.train()
+    try:
+        for step, since, flags in [(100, 2, [True, False, False]), (3, 0, [True, True, True]),
+                                   (100, 1, [False, False, False])]:
+            model.zero_grad(set_to_none=True)
+            model.proposal_sampler._step, model.proposal_sampler._steps_since_update = step, since
+            rb = RayBundle(origins=o.to(DEV), directions=d.to(DEV), camera_indices=torch.full((N, 1), 1, device=DEV))
+            model.backward_for_camera_ray_bundle(rb, gout, jitter=jit)
+            assert model.proposal_sampler._steps_since_update == (0 if flags[0] else since)
+            E.bind_grads()
+            go, gv = torch.empty(N, 3, device=DEV), torch.empty(N, 3, device=DEV)
+            for c, flag in enumerate(flags):
+                a, b = c * C, min((c + 1) * C, N)
+                go[a:b], gv[a:b] = E.backward(o[a:b].to(DEV), d[a:b].to(DEV), gout[a:b], camera_idx=1, jitter=jit[a:b],
+                                              chunk_rays=C, proposal_requires_grad=flag, nerf_layout=True)
+            assert rel_err(rb.origins.grad, go) < 1e-6 and rel_err(rb.directions.grad, gv) < 1e-6
+            named = dict(model.named_parameters())
+            for k, gref in E.grads.items():
+                assert rel_err(named[k].grad, gref, floor=1e-12) < 1e-4, (step, k)
+            prop = float(named["proposal_networks.0.encoding.hash_table"].grad.abs().sum())
+            assert (prop > 0) == any(flags), (step, prop)
+    finally:
+        model.backward_num_rays_per_chunk = old_chunk

@@ -84,3 +84,29 @@ def test_turntable_appearance_mode_equals_reference_live(camera_idx, spec, param
     row = ids[min(camera_idx, len(ids) - 1)]
     assert rel_err(gq[k], gr[k], floor=1e-30) < 1e-4
     assert gq[k][row].abs().max() > 0 and gq[k].abs().sum() == gq[k][row].abs().sum()          # only that row gets a gradient
+
+
+def test_sampler_update_state_machine_equals_reference_live(spec, params_factory):
+    """ray_samplers.py:598,622-623: which sampler calls carry proposal autograd, over a few
+    training steps with several calls (chunks) per step - the mirror's bookkeeping against the reference's sampler."""
+    from nerf_emitter_b200.nerfstudio_api import ProposalNetworkSampler
+    from oracle.ref_harness import ReferenceEmitter
+    R = ReferenceEmitter(params_factory(0, 1.0), spec)
+    R.train(True)
+    R.sampler._step, R.sampler._steps_since_update = 0, 0
+    mine = ProposalNetworkSampler(None, update_sched=lambda step: 1)
+    o, v, _ = make_rays(4, seed=1)
+    rb = R.collider(R.get_ray_bundle(o.t().contiguous(), v.t().contiguous(), 0))
+    seen = []
+    for step in list(range(0, 3)) + list(range(9, 16)):
+        R.sampler.step_cb(step)
+        mine.step_cb(step)
+        calls = 1 + step % 3
+        ref_flags = []
+        for _ in range(calls):
+            _, wl, _ = R.sampler(rb, density_fns=R._density_fns())
+            ref_flags.append(bool(wl[0].requires_grad))
+        assert mine._consume_update(calls) == ref_flags, (step, ref_flags)
+        assert mine._steps_since_update == R.sampler._steps_since_update
+        seen += ref_flags
+    assert True in seen and False in seen
