@@ -288,6 +288,16 @@ int nemit_hash_encode_grid(const NemitGrid* grid, const float* table, const floa
  * NS/utils/math.py:27-90): d (n,3), out (n, levels^2), levels in 1..4. */
 int nemit_sh_encode(const float* d, int64_t n, int32_t levels, float* out, void* stream);
 
+/* NeRFEmitter.eval_nerf up to the op call (DS/emitters/nerf.py:69-82): world rays o, v (3,n) -> emitter-local rays
+ * (o' = M o as a point, v' = M v as a vector; M = world_transform().inverse() as 3x4 row-major host floats) and, when
+ * near_out != NULL, the distance to skip: the far slab intersection with [bbox_min, bbox_max] (the unit cube padded by
+ * padding_size, nerf.py:33) for rays that hit it when outside_only, else skip_distance (nerf.py:75-79).
+ * linear_only != 0 applies only the 3x3 part to both arrays (pass M^T to carry o / v gradients back to world space).
+ * In-place (o_out == o) is allowed.  Stateless: no handle. */
+int nemit_emitter_local_rays(const float* world_to_local_3x4, const float* bbox_min, const float* bbox_max,
+                             float skip_distance, int32_t outside_only, int32_t linear_only, const float* o,
+                             const float* v, int64_t n, float* o_out, float* v_out, float* near_out, void* stream);
+
 /* MLP.forward, torch path (NS/field_components/mlp.py:163-183): nn.Linear layers in torch (out,in) layout,
  * `activation` between layers and `out_activation` after the last (0 = none, 1 = ReLU); widths <= 64. */
 #define NEMIT_MLP_MAX_LAYERS 8

@@ -462,6 +462,22 @@ extern "C" int nemit_sh_encode(const float* d, int64_t n, int32_t levels, float*
   return NEMIT_OK;
 }
 
+extern "C" int nemit_emitter_local_rays(const float* world_to_local_3x4, const float* bbox_min, const float* bbox_max,
+                                        float skip_distance, int32_t outside_only, int32_t linear_only, const float* o,
+                                        const float* v, int64_t n, float* o_out, float* v_out, float* near_out,
+                                        void* stream) {
+  if (!world_to_local_3x4 || n < 0 || (n > 0 && (!o || !v || !o_out || !v_out)))
+    return fail(NEMIT_E_INVALID, "nemit_emitter_local_rays: null argument%s");
+  if (outside_only && (!bbox_min || !bbox_max))
+    return fail(NEMIT_E_INVALID, "nemit_emitter_local_rays: outside_only needs the bounding box%s");
+  const float zero[3] = {0.f, 0.f, 0.f};
+  cudaError_t e = launch_emitter_local_rays(world_to_local_3x4, bbox_min ? bbox_min : zero, bbox_max ? bbox_max : zero,
+                                            skip_distance, outside_only != 0, linear_only != 0, o, v, n, o_out, v_out,
+                                            near_out, (cudaStream_t)stream);
+  if (e != cudaSuccess) return cuda_fail(e, "k_emitter_local_rays");
+  return NEMIT_OK;
+}
+
 extern "C" int nemit_mlp(const NemitMlp* mlp, const float* x, int64_t n, float* out, void* stream) {
   if (!mlp || n < 0 || (n > 0 && (!x || !out))) return fail(NEMIT_E_INVALID, "nemit_mlp: null argument%s");
   if (mlp->num_layers < 1 || mlp->num_layers > NEMIT_MLP_MAX_LAYERS || mlp->in_dim < 1 || mlp->in_dim > NEMIT_MLP_MAX_WIDTH)

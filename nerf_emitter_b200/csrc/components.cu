@@ -169,6 +169,70 @@ k_mlp(const __grid_constant__ MlpDev L, const float* __restrict__ x, int64_t n, 
   }
 }
 
+// NeRFEmitter.eval_nerf up to the op call (DS/emitters/nerf.py:69-82): rays from world to emitter-local space
+// (o' = A o + t as a point, v' = A v as a vector, not renormalised: mi.Transform4f @ mi.Ray3f) and the distance to skip,
+// sph_t = far slab intersection with the padded unit box when the ray hits it (outside_only), else skip_distance.
+// mode 1 applies only the linear part to both arrays (the transpose pass that carries o / v gradients back to world).
+struct LocalRayArgs {
+  float m[12];             // rows of the 3x4 world -> local matrix
+  float bmin[3], bmax[3];
+  float skip_distance;
+  int outside_only;
+  int mode;
+};
+
+__global__ void __launch_bounds__(256)
+k_emitter_local_rays(const __grid_constant__ LocalRayArgs A, const float* __restrict__ o, const float* __restrict__ v,
+                     int64_t n, float* __restrict__ o_out, float* __restrict__ v_out, float* __restrict__ near_out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float ox = o[i], oy = o[n + i], oz = o[2 * n + i];
+    const float vx = v[i], vy = v[n + i], vz = v[2 * n + i];
+    float lo[3], lv[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const float tr = A.mode == 1 ? 0.f : A.m[4 * r + 3];
+      lo[r] = fmaf(A.m[4 * r], ox, fmaf(A.m[4 * r + 1], oy, fmaf(A.m[4 * r + 2], oz, tr)));
+      lv[r] = fmaf(A.m[4 * r], vx, fmaf(A.m[4 * r + 1], vy, A.m[4 * r + 2] * vz));
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r) { o_out[r * n + i] = lo[r]; v_out[r * n + i] = lv[r]; }
+    if (near_out) {
+      float t = A.skip_distance;
+      if (A.outside_only) {
+        // mi.BoundingBox3f.ray_intersect (mitsuba 3.4.1 include/mitsuba/core/bbox.h): slab test, returns the hit flag
+        // and the near / far parameters; nerf.py:76 keeps the far one
+        bool hit = true;
+        float mint = -INFINITY, maxt = INFINITY;
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+          hit = hit && (lv[r] != 0.f || lo[r] > A.bmin[r] || lo[r] < A.bmax[r]);
+          const float rcp = 1.f / lv[r];
+          const float t1 = (A.bmin[r] - lo[r]) * rcp, t2 = (A.bmax[r] - lo[r]) * rcp;
+          mint = fmaxf(mint, fminf(t1, t2));
+          maxt = fminf(maxt, fmaxf(t1, t2));
+        }
+        hit = hit && maxt >= mint;
+        if (hit) t = maxt;
+      }
+      near_out[i] = t;
+    }
+  }
+}
+
+cudaError_t launch_emitter_local_rays(const float* m34, const float* bmin, const float* bmax, float skip_distance,
+                                      int outside_only, int mode, const float* o, const float* v, int64_t n,
+                                      float* o_out, float* v_out, float* near_out, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  LocalRayArgs A;
+  for (int i = 0; i < 12; ++i) A.m[i] = m34[i];
+  for (int i = 0; i < 3; ++i) { A.bmin[i] = bmin[i]; A.bmax[i] = bmax[i]; }
+  A.skip_distance = skip_distance; A.outside_only = outside_only; A.mode = mode;
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  k_emitter_local_rays<<<(unsigned)blocks, 256, 0, stream>>>(A, o, v, n, o_out, v_out, near_out);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_mlp(const MlpDev& L, const float* x, int64_t n, float* out, cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
   int64_t blocks = (n + 127) / 128;

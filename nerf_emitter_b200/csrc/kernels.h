@@ -226,6 +226,9 @@ cudaError_t launch_prop_density(const ModelDev& M, const GridDev& G, const float
                                 float* density, cudaStream_t stream);
 cudaError_t launch_sh_encode(const float* d, int64_t n, int levels, float* out, cudaStream_t stream);
 cudaError_t launch_mlp(const MlpDev& L, const float* x, int64_t n, float* out, cudaStream_t stream);
+cudaError_t launch_emitter_local_rays(const float* m34, const float* bmin, const float* bmax, float skip_distance,
+                                      int outside_only, int mode, const float* o, const float* v, int64_t n,
+                                      float* o_out, float* v_out, float* near_out, cudaStream_t stream);
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast = false);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);

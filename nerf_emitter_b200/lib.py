@@ -84,6 +84,9 @@ SYMBOLS = {
     "nemit_version": (C.c_int, []),
     "nemit_create": (C.c_int, [C.POINTER(NemitConfig), C.c_int, C.POINTER(_H)]),
     "nemit_destroy": (C.c_int, [_H]),
+    "nemit_emitter_local_rays": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float,
+                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "nemit_set_appearance_mode": (C.c_int, [_H, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_int32]),
     "nemit_bind_params": (C.c_int, [_H, C.POINTER(NemitParams)]),
     "nemit_bind_grads": (C.c_int, [_H, C.POINTER(NemitParams)]),

@@ -439,6 +439,15 @@ class SdfNerfactoModel(nn.Module):
                                                        update_sched=update_schedule)
         self._E: Optional[NerfEmitter] = None
         self._bound_ptrs: Tuple[int, ...] = ()
+        self._num_processed_rays = 0                    # base_model.py:122 (the trainer's rays/s meter)
+
+    def clear_num_processed_rays(self) -> None:
+        """base_model.py:124-125."""
+        self._num_processed_rays = 0
+
+    def num_processed_rays(self) -> int:
+        """base_model.py:127-128."""
+        return self._num_processed_rays
 
     # -- handle management: the library borrows the module's own parameter / .grad storage -------------------------
     def _named(self) -> Dict[str, torch.Tensor]:
@@ -477,6 +486,7 @@ class SdfNerfactoModel(nn.Module):
     def get_rgb_for_camera_ray_bundle(self, camera_ray_bundle: RayBundle, jitter=None) -> torch.Tensor:
         """base_model.py:290-313 -> SdfNerfactoModel.get_rgb (sdf_nerfacto.py:64-83): (N,3) radiance."""
         E = self._emitter()
+        self._num_processed_rays += len(camera_ray_bundle)                       # base_model.py:302
         self.proposal_sampler._consume_update(_num_chunks(len(camera_ray_bundle), self.eval_num_rays_per_chunk))
         return E.render(_cuda_f32(camera_ray_bundle.origins, "origins"), _cuda_f32(camera_ray_bundle.directions, "directions"),
                         camera_idx=camera_ray_bundle.camera_index(), jitter=jitter, nerf_layout=True)
@@ -488,6 +498,7 @@ class SdfNerfactoModel(nn.Module):
                                            grad_v: torch.Tensor, jitter=None) -> torch.Tensor:
         """base_model.py:315-344 -> forward_grad (sdf_nerfacto.py:85-113): tangent of the radiance, (N,3)."""
         E = self._emitter()
+        self._num_processed_rays += len(camera_ray_bundle)                       # base_model.py:331
         self.proposal_sampler._consume_update(_num_chunks(len(camera_ray_bundle), self.forward_ad_num_rays_per_chunk))
         return E.jvp(_cuda_f32(camera_ray_bundle.origins, "origins"), _cuda_f32(camera_ray_bundle.directions, "directions"),
                      _cuda_f32(grad_o.reshape(-1, 3), "grad_o"), _cuda_f32(grad_v.reshape(-1, 3), "grad_v"),
@@ -521,6 +532,7 @@ class SdfNerfactoModel(nn.Module):
         d = _cuda_f32(camera_ray_bundle.directions, "directions")
         g = _cuda_f32(grad_out.reshape(-1, 3), "grad_out")
         n, chunk = o.shape[0], self.backward_num_rays_per_chunk
+        self._num_processed_rays += n                                           # mitsuba_sdf.py:1157
         if isinstance(jitter, (list, tuple)):
             jitter = torch.cat([j.reshape(n, 1) for j in jitter], dim=1)
         # one sampler call per chunk: the flag can differ between the first chunk and the rest (quirk 13)
