@@ -20,6 +20,16 @@ __global__ void k_red(float* table, uint32_t mask_entries, int ops_per_thread, i
   }
 }
 
+// partially filled warps: only lanes < active issue the reduction (cost per lane-op or per instruction?)
+__global__ void k_red_partial(float* table, uint32_t mask_entries, int ops_per_thread, int active) {
+  uint32_t s = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+  const bool on = (threadIdx.x & 31) < active;
+  for (int i = 0; i < ops_per_thread; ++i) {
+    uint32_t e = rng(s) & mask_entries;
+    if (on) atomicAdd(reinterpret_cast<float2*>(table) + e, make_float2(1.f, 2.f));
+  }
+}
+
 // do random L1-missing gathers and random reductions share one path?  Each thread issues `nl` float2 gathers and `nr`
 // float2 reductions per iteration on two different 64 MiB tables.
 __global__ void k_mix(const float2* __restrict__ src, float* dst, uint32_t mask_entries, int iters, int nl, int nr, float* sink) {
@@ -61,6 +71,16 @@ int main() {
     float ms; cudaEventElapsedTime(&ms, a, b);
     double lane_ops = (double)blocks * threads * ops;
     printf("random  W=%d 8 warps/SM: %.3f ms, %.1f G lane-ops/s, %.2f SM-cycles per lane-op\n", W, ms, lane_ops / ms * 1e-6, ms * 1e-3 * 1.9e9 * 148 / lane_ops);
+  }
+  for (int active : {32, 16, 8, 4, 1}) {
+    const int blocks = 148 * 8, threads = 256, ops = 512;
+    auto launch = [&] { k_red_partial<<<blocks, threads>>>(t, entries - 1, ops, active); };
+    launch(); CK(cudaDeviceSynchronize());
+    cudaEventRecord(a); launch(); cudaEventRecord(b); CK(cudaDeviceSynchronize());
+    float ms; cudaEventElapsedTime(&ms, a, b);
+    const double instr = (double)blocks * threads / 32 * ops;
+    printf("partial warps: %2d active lanes per red.v2 instruction: %.3f ms, %.1f SM-cycles per warp instruction, %.2f per active lane\n",
+           active, ms, ms * 1e-3 * 1.9e9 * 148 / instr, ms * 1e-3 * 1.9e9 * 148 / instr / active);
   }
   {
     float2* src; CK(cudaMalloc(&src, entries * 8)); CK(cudaMemset(src, 0, entries * 8));
