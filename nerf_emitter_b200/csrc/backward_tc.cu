@@ -73,6 +73,8 @@ struct BwdTcHalf {
   alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
   alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
   float dvec[64];
+  float denc[32 * 128];                   // d encoding of the PREVIOUS tile, [column][thread] (deferred scatter)
+  float pbuf[3 * 128];                    // its normalised sample positions, [axis][thread]
   alignas(8) uint64_t mbar;               // MMA commit groups
   alignas(8) uint64_t ld_bar;             // bulk copies of one tile (65536 bytes per phase)
 };
@@ -87,8 +89,9 @@ __device__ __forceinline__ void half_sync(int half) {
 }
 
 // make the half's operand writes visible to the tensor core, let its thread 0 issue one commit group, wait for it
-template <class F>
-__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue) {
+// - `between` runs on all threads while the commit group is in flight (a slice of the previous tile's table scatter)
+template <class F, class G>
+__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue, G&& between) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
   half_sync(half);
@@ -97,9 +100,44 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
     issue();
     tc::mma_commit(&H->mbar);
   }
+  between();
   tc::mbar_wait(&H->mbar, phase);
   phase ^= 1u;
   tc::tc_fence_after();
+}
+
+// Table scatter of levels [LB, LE) for the sample this thread owned in the half's PREVIOUS tile (d encoding and position
+// parked in shared memory, one private column per thread).  An all-zero gradient pair (also: invalid rows, first tile)
+// is skipped.  Corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices
+// differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
+template <int LB, int LE>
+__device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const ModelDev& M, float2* table, float gscale) {
+  if (!table) return;                     // ray-gradient-only pass (nemit_point_lights): no parameter gradients
+  const float p[3] = {H->pbuf[t], H->pbuf[128 + t], H->pbuf[256 + t]};
+#pragma unroll
+  for (int l = LB; l < LE; ++l) {
+    const float gx = H->denc[(2 * l) * 128 + t], gy = H->denc[(2 * l + 1) * 128 + t];
+    if (gx == 0.f && gy == 0.f) continue;
+    LevelCell cell;
+    const float sc = M.main_grid.scal[l];
+    level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)l * M.main_grid.table_size, cell);
+    float cw[8];
+    corner_weights(cell, cw);
+    const float gxs = gx * gscale, gys = gy * gscale;
+    const float xs = mul_rn(p[0], sc);
+    const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
+    if (pair) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t ia = cell.idx[2 * q], ib = cell.idx[2 * q + 1];
+        const float wa = (ia & 1u) ? cw[2 * q + 1] : cw[2 * q], wb = (ia & 1u) ? cw[2 * q] : cw[2 * q + 1];
+        atomicAdd(reinterpret_cast<float4*>(table + (ia < ib ? ia : ib)), make_float4(wa * gxs, wa * gys, wb * gxs, wb * gys));
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) atomic_add_f2(table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+    }
+  }
 }
 
 // hidden layer: accumulator row x (activation row > 0) -> fp16 gradient row written over the activation row
@@ -184,6 +222,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   const int64_t tile_stride = (int64_t)gridDim.x * 2;
   bool first = true;
   uint32_t ld_phase = 0;
+  const float gscale = invS * A.loss_scale;
+  // deferred scatter: nothing parked yet
+#pragma unroll
+  for (int c = 0; c < 32; ++c) H->denc[c * 128 + t] = 0.f;
   // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
   const uint64_t pol = tc::l2_evict_first_policy();
   auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar, pol); };
@@ -232,13 +274,13 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    });
+    }, [&] { scatter_levels<0, 4>(H, t, M, A.G.main_table, gscale); });
     epi_bwd_hidden(taddr + kColD0, H->h3, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
-    });
+    }, [&] { scatter_levels<4, 7>(H, t, M, A.G.main_table, gscale); });
     if (t == 0 && has_next) {       // H3 / G3 has no reader left: the next tile's copies start here
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
       load_h3(next_tile);
@@ -248,7 +290,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
-    });
+    }, [&] { scatter_levels<7, 10>(H, t, M, A.G.main_table, gscale); });
     if (t == 0 && has_next) { load_h2(next_tile); load_in(next_tile); }
     {
       float v[16];
@@ -272,7 +314,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    });
+    }, [&] { scatter_levels<10, 13>(H, t, M, A.G.main_table, gscale); });
     epi_bwd_hidden(taddr + kColD0, H->h1, t);
     // this tile's Jacobian rows: the loads fly under the last commit group
     uint4 jn[12];
@@ -285,57 +327,34 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
-    });
+    }, [&] { scatter_levels<13, 16>(H, t, M, A.G.main_table, gscale); });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 
-    // ---- hash grid backward: table scatter-add and d/d(position) ----------------------------------------
+    // ---- hash grid backward: d/d(position) now; the table scatter of this tile is parked in shared memory and runs in
+    // slices under the NEXT tile's five commit groups (scatter_levels), so that reductions are issued all the time instead
+    // of in one burst per tile ----------------------------------------------------------------------------------
     {
       float gp[3] = {0.f, 0.f, 0.f};
-      const float gscale = invS * A.loss_scale;
+      H->pbuf[t] = p[0]; H->pbuf[128 + t] = p[1]; H->pbuf[256 + t] = p[2];
 #pragma unroll
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
         float g[8];
         tc::tmem_ld8(taddr + kColD0 + 2 * l0, g);
         tc::tmem_ld_wait();
+#pragma unroll
+        for (int k = 0; k < 8; ++k) H->denc[(2 * l0 + k) * 128 + t] = valid ? g[k] : 0.f;
         const uint4 ja = jn[(l0 >> 2) * 3], jb = jn[(l0 >> 2) * 3 + 1], jc = jn[(l0 >> 2) * 3 + 2];
         const uint32_t wj[12] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w, jc.x, jc.y, jc.z, jc.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float gx = g[2 * j], gy = g[2 * j + 1];
-          if (!valid || (gx == 0.f && gy == 0.f)) continue;
-          LevelCell cell;
-          const float sc = M.main_grid.scal[l0 + j];
-          level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell);
-          float cw[8];
-          corner_weights(cell, cw);
-          const float gxs = gx * gscale, gys = gy * gscale;
-          // corners (2q, 2q+1) differ in x only (ceil, floor).  For an even floor coordinate the two hashed indices
-          // differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
-          const float xs = mul_rn(p[0], sc);
-          const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
-          if (!A.G.main_table) {
-            // ray-gradient-only pass (nemit_point_lights): no parameter gradients
-          } else if (pair) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const uint32_t ia = cell.idx[2 * q], ib = cell.idx[2 * q + 1];
-              const float wa = (ia & 1u) ? cw[2 * q + 1] : cw[2 * q], wb = (ia & 1u) ? cw[2 * q] : cw[2 * q + 1];
-              atomicAdd(reinterpret_cast<float4*>(A.G.main_table + (ia < ib ? ia : ib)),
-                        make_float4(wa * gxs, wa * gys, wb * gxs, wb * gys));
-            }
-          } else {
-#pragma unroll
-            for (int c = 0; c < 8; ++c) atomic_add_f2(A.G.main_table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
-          }
-          if (sel) {
-            const float2 dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
-            const float2 dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
-            const float2 dz = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 2]));
-            const float scs = sc * invS;
-            gp[0] = fmaf(scs, gx * dx.x + gy * dx.y, gp[0]);
-            gp[1] = fmaf(scs, gx * dy.x + gy * dy.y, gp[1]);
-            gp[2] = fmaf(scs, gx * dz.x + gy * dz.y, gp[2]);
-          }
+          const float2 dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
+          const float2 dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
+          const float2 dz = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 2]));
+          const float scs = M.main_grid.scal[l0 + j] * invS;
+          gp[0] = fmaf(scs, gx * dx.x + gy * dx.y, gp[0]);
+          gp[1] = fmaf(scs, gx * dy.x + gy * dy.y, gp[1]);
+          gp[2] = fmaf(scs, gx * dz.x + gy * dz.y, gp[2]);
         }
       }
       if (valid && sel) {
@@ -352,6 +371,9 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     }
     first = false;
   }
+
+  // ---- the last tile's parked scatter ---------------------------------------------------------------
+  scatter_levels<0, 16>(H, t, M, A.G.main_table, gscale);
 
   // ---- flush this half's weight-gradient accumulators (torch layouts, loss scale applied) ---------------
   if (!first && A.G.main_table) {
