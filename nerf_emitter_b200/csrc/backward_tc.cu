@@ -54,6 +54,10 @@ constexpr uint32_t kColBB0 = 224;   // d base_b0   [n][*]   64 x 8
 constexpr uint32_t kColBB1 = 232;   // d base_b1   [*][n]   64 x 16 (64 identical rows: A = ones)
 constexpr uint32_t kColBH2 = 248;   // d head_b2   [*][n]   64 x 8
 constexpr uint32_t kHalfCols = 256;
+#ifndef NEMIT_SCATTER_UNROLL
+#define NEMIT_SCATTER_UNROLL 1
+#endif
+constexpr int kScatterUnroll = NEMIT_SCATTER_UNROLL;
 
 struct BwdTcCommon {
   alignas(128) uint8_t b1[64 * 32 * 2];   // base layer 0   (64 x 32)   forward K-major layout, rows = outputs
@@ -114,7 +118,7 @@ template <int LB, int LE>
 __device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const ModelDev& M, float2* table, float gscale) {
   if (!table) return;                     // ray-gradient-only pass (nemit_point_lights): no parameter gradients
   const float p[3] = {H->pbuf[t], H->pbuf[128 + t], H->pbuf[256 + t]};
-#pragma unroll
+#pragma unroll kScatterUnroll
   for (int l = LB; l < LE; ++l) {
     const float gx = H->denc[(2 * l) * 128 + t], gy = H->denc[(2 * l + 1) * 128 + t];
     if (gx == 0.f && gy == 0.f) continue;
