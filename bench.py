@@ -382,7 +382,7 @@ def kernel_roofline(prof, n, steps, mode="fwd+bwd"):
 # and backward: per launch of 65536 rays = the bench's own backward sub-chunk: 2.25 GB of kept tiles written / 2.38 GB read
 # back, profiles/r1_ncu_fwd_bwd_tc_summary.txt)
 NCU_TRAFFIC = {"k_sample_levels": 7.9e6, "k_field_forward": 63.9e6, "k_field_forward_tc": 63.8e6,
-               "k_field_forward<adjoint_seed>": 3.13e9, "k_field_backward_tc": 2.50e9}
+               "k_field_forward<adjoint_seed>": 3.13e9, "k_field_backward_tc": 2.43e9}
 
 
 if __name__ == "__main__":
