@@ -11,6 +11,8 @@ weights (weak scaling); no data-path collective in the forward, one gradient all
 from __future__ import annotations
 
 import argparse
+import contextlib
+import io
 import json
 import os
 import subprocess
@@ -386,4 +388,14 @@ NCU_TRAFFIC = {"k_sample_levels": 7.9e6, "k_field_forward": 63.9e6, "k_field_for
 
 
 if __name__ == "__main__":
-    main()
+    # stdout carries exactly one JSON line: anything a library writes to fd 1 meanwhile (NCCL's version banner
+    # under NCCL_DEBUG) goes to stderr instead
+    sys.stdout.flush()
+    _json_fd = os.dup(1)
+    os.dup2(2, 1)
+    _buf = io.StringIO()
+    try:
+        with contextlib.redirect_stdout(_buf):
+            main()
+    finally:
+        os.write(_json_fd, _buf.getvalue().encode())
