@@ -68,6 +68,13 @@ typedef struct NemitConfig {
   const float* lin0_host;       /* num_prop_samples[0]+1 values of linspace(0,1,S0+1) */
   const float* u1_host;         /* num_prop_samples[1]+1 values of linspace(0,1-1/nb,nb)       */
   const float* u2_host;         /* num_nerf_samples+1 values                                   */
+  /* Model variants this build does not implement: nemit_create fails with NEMIT_E_INVALID (and says which) when one is
+   * set, instead of silently evaluating the default model.  use_fake_contraction: FakeContraction + AABBBoxCollider
+   * (NS/field_components/spatial_distortions.py:94-103, NS/models/nerfacto.py:144-154,176,263-270); far_intersect:
+   * AABBBoxFarIntersectCollider in get_point_lights (NS/model_components/scene_colliders.py:96-143,
+   * NS/models/sdf_nerfacto.py:193-194).  Both default to False in sdf-nerfacto. */
+  int32_t use_fake_contraction;
+  int32_t far_intersect;
 } NemitConfig;
 
 /* Parameter pointers, named as in the reference state_dict (SURVEY.md 8b "Parameter ownership").
@@ -105,6 +112,16 @@ typedef struct NemitRays {
                             get_rgb_for_camera_ray_bundle / forward_grad_for_camera_ray_bundle /
                             backward_for_camera_ray_bundle (NS/models/base_model.py:290-344,
                             NS/pipelines/mitsuba_sdf.py:1144-1219); tangents and ray gradients then use (N,3) too */
+  /* Optional: sample edges kept from an earlier nemit_forward / nemit_sample_levels call (NemitLevelsOut.s_edges1,
+   * .s_edges2, .t_edges2) over the SAME rays, mode (training flag, near), anneal, jitter and parameters.  The reference
+   * re-derives identical samples in the adjoint of one CustomOp instance because it restores the samplers' generator
+   * state between the primal and the adjoint (NS/models/base_model.py:299,327-328, NS/pipelines/mitsuba_sdf.py:1152-1154);
+   * with these set nemit_backward / nemit_jvp / nemit_point_lights skip the proposal sampling pass instead.
+   * kept_t_edges2 and kept_s_edges2 (N,49) must come together; kept_s_edges1 (N,97) is needed in addition by
+   * nemit_backward when proposal_requires_grad != 0.  All NULL (default) = sample again. */
+  const float* kept_s_edges1;
+  const float* kept_s_edges2;
+  const float* kept_t_edges2;
 } NemitRays;
 #define NEMIT_RAYS_MITSUBA_3N 0
 #define NEMIT_RAYS_NERF_N3 1
@@ -345,13 +362,58 @@ int nemit_vmf_pdf(const NemitVmfLobes* lobes, const float* p, const float* d, in
 int nemit_forward_host(NemitHandle* h, const NemitRays* rays_host, float* rgb_host,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* Reverse-mode twin of nemit_forward_host (measurement honesty, SURVEY.md 8d: the metric's fwd+bwd mode through one
+ * plugin call with HOST buffers): rays_host (o, v (3,N), optional near / jitter) and grad_rgb_host (N,3) are pinned
+ * host arrays; H2D copies, nemit_forward (eval-mode primal when primal_training == 0, as a validation render, or the
+ * training-mode primal of the same CustomOp instance when != 0 - its sample edges are then kept for the adjoint
+ * unless proposal_requires_grad needs the proposal loop again), nemit_backward and the D2H copies of rgb (N,3),
+ * grad_o, grad_v (3,N) are queued on `stream`; parameter gradients accumulate into the bound buffers. */
+int nemit_backward_host(NemitHandle* h, const NemitRays* rays_host, const float* grad_rgb_host, int32_t primal_training,
+                        int64_t chunk_rays, float loss_scale, int32_t proposal_requires_grad, float* rgb_host,
+                        float* grad_o_host, float* grad_v_host, void* workspace, size_t workspace_bytes, void* stream);
+size_t nemit_backward_host_workspace_bytes(const NemitHandle* h, int64_t n);
+
+/* The one collective of the path behind the C ABI (reference: DDP's gradient all-reduce,
+ * NS/pipelines/base_pipeline.py:355-357 with the no_sync accumulation of NS/pipelines/mitsuba_sdf.py:1179-1193).
+ * nemit_comm_unique_id fills 128 bytes (ncclUniqueId) on one rank; the host broadcasts them (torch.distributed, MPI,
+ * a file - the library does not care) and every rank calls nemit_comm_init with its rank.  nemit_allreduce_grads sums
+ * `count` floats in place over the ranks with NCCL (NVLink / NVSwitch) and multiplies by `scale` IN THE SAME PASS
+ * (ncclRedOpCreatePreMulSum: GradScaler unscale or 1/world folded into the collective, no second sweep over the 77.6 MB).
+ * flat_grads: the contiguous gradient blob (NerfEmitter.bind_grads lays every .grad tensor out as a view of one buffer).
+ * NCCL is loaded at run time (dlopen of the libnccl.so.2 already in the process or on the loader path); without it
+ * nemit_comm_init fails with NEMIT_E_INVALID and says so. */
+#define NEMIT_UNIQUE_ID_BYTES 128
+int nemit_comm_unique_id(void* id_out_128);
+int nemit_comm_init(NemitHandle* h, const void* id_128, int32_t rank, int32_t world_size);
+int nemit_comm_destroy(NemitHandle* h);
+int nemit_allreduce_grads(NemitHandle* h, float* flat_grads, int64_t count, float scale, void* stream);
+
+/* Ceilings the gather / scatter kernels are measured against, re-measured on the device the handle lives on (bench.py
+ * reports every kernel's rate next to the matching one).  kind: NEMIT_MB_GATHER_L1MISS = random 8-byte lane-loads from a
+ * 64 MiB L2-resident table (one corner of a hashed level); NEMIT_MB_GATHER_L1HIT = the same from a 64 KiB table;
+ * NEMIT_MB_GATHER_COHERENT = the 32 lanes of a warp read 32 consecutive entries (coarse level, ray-coherent samples);
+ * NEMIT_MB_RED = random red.global.add.v2.f32 into a 64 MiB table (the hash-table scatter); NEMIT_MB_L2_READ = streaming
+ * 128-bit reads of a 32 MiB L2-resident buffer.  result_out[0] = operations (lane-loads / lane-ops; bytes for L2_READ)
+ * per second, result_out[1] = kernel milliseconds.  Synchronises the stream.  (The TMA tile::gather4 variant lives in
+ * tools/gather_bench.cu: it needs a driver-API tensor map, which this library does not link.) */
+#define NEMIT_MB_GATHER_L1MISS 0
+#define NEMIT_MB_GATHER_L1HIT 1
+#define NEMIT_MB_GATHER_COHERENT 2
+#define NEMIT_MB_RED 3
+#define NEMIT_MB_L2_READ 4
+int nemit_microbench(NemitHandle* h, int32_t kind, double* result_out, void* stream);
+
 /* number of kernels the library has launched on this handle since creation (bench evidence) */
 int64_t nemit_launch_count(const NemitHandle* h);
 
 /* Optional per-kernel timing: CUDA events recorded around every kernel launch ON THE LAUNCHING STREAM
  * (the reference's counterpart is the @profiler.time_function wall clock, NS/utils/profiler.py:68-131).
- * nemit_profile_read synchronises the pending events and returns accumulated milliseconds and launch
- * counts per kernel kind (arrays of NEMIT_PROFILE_KINDS). */
+ * nemit_profile_read synchronises the pending events and returns, per kernel kind (arrays of NEMIT_PROFILE_KINDS),
+ * accumulated milliseconds, launch counts and the RAYS those launches processed (so that rays per launch is what
+ * was launched, not a guess); any of the three may be NULL.  No launch is ever dropped: the event ring holds 4096
+ * launches and the oldest records are folded into the sums when it fills.  red_ops_or_null (1): reduction lane-ops
+ * (red.global.add lanes) the hash-table scatter of k_field_backward_tc issued since the last reset, counted on the
+ * device while profiling is on. */
 #define NEMIT_K_SAMPLE 0      /* k_sample_levels */
 #define NEMIT_K_FIELD_FWD 1   /* k_field_forward (fp32) */
 #define NEMIT_K_FIELD_SEED 2  /* k_field_forward<adjoint seed> */
@@ -363,7 +425,8 @@ int64_t nemit_launch_count(const NemitHandle* h);
 #define NEMIT_K_FIELD_BWD_TC 8 /* k_field_backward_tc (tensor-core dgrad / wgrad) */
 #define NEMIT_PROFILE_KINDS 9
 int nemit_profile_enable(NemitHandle* h, int32_t on);
-int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int32_t reset);
+int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int64_t* rays_per_kind,
+                       int64_t* red_ops_or_null, int32_t reset);
 
 #ifdef __cplusplus
 }

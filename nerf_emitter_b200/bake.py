@@ -54,9 +54,10 @@ def film_develop(accum: torch.Tensor) -> torch.Tensor:
 
 def bake_envmap(E: NerfEmitter, width: int = 2048, height: int = 1024, spp: int = 16, origin=(0.5, 0.5, 0.5),
                 filter: str = "gaussian", stddev: float = 0.25, seed: int = 0, rows: Optional[Tuple[int, int]] = None,
-                camera_idx: int = 0, group=None, develop: bool = True) -> torch.Tensor:
+                camera_idx: int = 0, group=None, develop: bool = True, reduce: bool = True) -> torch.Tensor:
     """(height, width, 4) rgba radiance seen from ``origin``.  ``rows`` = this rank's film rows (default: the
-    ``parallel.shard_range`` split over the process group when torch.distributed is initialised, else all rows)."""
+    ``parallel.shard_range`` split over the process group when torch.distributed is initialised, else all rows).
+    With several ranks the accumulation buffers are summed through the library's collective (``reduce``)."""
     import torch.distributed as dist
     from . import parallel
     sensor = make_sensor(width, height, spp, origin, 0.0, seed)
@@ -71,6 +72,6 @@ def bake_envmap(E: NerfEmitter, width: int = 2048, height: int = 1024, spp: int 
     L.check(E.lib.nemit_bake_envmap(E._h, C.byref(sensor), FILTERS[filter], float(stddev), int(rows[0]), int(rows[1]),
                                     int(camera_idx), _ptr(accum), _ptr(E._ws), E._ws.numel(), E._stream()),
             "nemit_bake_envmap")
-    if world > 1:
-        dist.all_reduce(accum, group=group)
+    if world > 1 and reduce:
+        E.allreduce_blob(accum, group=group)
     return film_develop(accum) if develop else accum

@@ -7,56 +7,44 @@
 #include <new>
 #include <string>
 
-#include "kernels.h"
+#include "handle.h"
 #include "vmf.h"
 
 using namespace nemit;
 
 static thread_local std::string g_err;
 
-static int fail(int code, const char* fmt, const char* a = "", long long b = 0) {
+int nemit_fail(int code, const char* fmt, const char* a, long long b) {
   char buf[512];
   snprintf(buf, sizeof(buf), fmt, a, b);
   g_err = buf;
   return code;
 }
-static int cuda_fail(cudaError_t e, const char* where) {
-  return fail(NEMIT_E_CUDA, "CUDA error in %s: ", where), g_err += cudaGetErrorString(e), NEMIT_E_CUDA;
+int nemit_cuda_fail(cudaError_t e, const char* where) {
+  return nemit_fail(NEMIT_E_CUDA, "CUDA error in %s: ", where), g_err += cudaGetErrorString(e), NEMIT_E_CUDA;
+}
+void nemit_append_error(const char* more) { g_err += more; }
+static int fail(int code, const char* fmt, const char* a = "", long long b = 0) { return nemit_fail(code, fmt, a, b); }
+static int cuda_fail(cudaError_t e, const char* where) { return nemit_cuda_fail(e, where); }
+
+// fold the oldest pending launch record into the per-kind sums (blocks until that launch has finished)
+static void profile_fold_oldest(NemitHandle* h) {
+  const int i = h->ev_head;
+  cudaEventSynchronize(h->ev[2 * i + 1]);
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, h->ev[2 * i], h->ev[2 * i + 1]) == cudaSuccess) h->kind_ms[h->ev_kind[i]] += ms;
+  h->ev_head = (i + 1) % kEvRing;
+  h->ev_count--;
 }
 
-struct NemitHandle {
-  int device;
-  ModelDev M;
-  NemitConfig cfg;
-  float* tables_dev;        // lin0 | u1 | u2 copies of the host sampler tables
-  const float* lin0;
-  const float* u1;
-  const float* u2;
-  double* opt_stats;        // 4 doubles of optimizer-step scratch (tail of tables_dev)
-  bool params_bound, grads_bound;
-  // nemit_set_appearance_mode
-  int always_use_camera_indices, use_average_embedding;
-  int32_t* rotation_ids;    // host copy of Rotater.rotation_ids, or null
-  int32_t num_rotation_ids;
-  NemitParams P, G;
-  int64_t launches;
-  int precision;
-  int sampler;
-  // optional per-kernel timing (nemit_profile_*): CUDA events around every launch on the launching stream
-  bool profile;
-  int n_pending;
-  cudaEvent_t ev[2 * 512];
-  int ev_kind[512];
-  double kind_ms[NEMIT_PROFILE_KINDS];
-  int64_t kind_launches[NEMIT_PROFILE_KINDS];
-};
-
-// launch with launch counting and optional event bracketing
+// launch with launch counting and optional event bracketing; `rays` = rays this launch processes
 template <class F>
-static cudaError_t timed_launch(NemitHandle* h, int kind, cudaStream_t st, F&& f) {
-  bool rec = h->profile && h->n_pending < 512;
-  int slot = h->n_pending;
+static cudaError_t timed_launch(NemitHandle* h, int kind, cudaStream_t st, int64_t rays, F&& f) {
+  const bool rec = h->profile && h->ev;
+  int slot = 0;
   if (rec) {
+    if (h->ev_count == kEvRing) profile_fold_oldest(h);
+    slot = (h->ev_head + h->ev_count) % kEvRing;
     if (!h->ev[2 * slot]) { cudaEventCreate(&h->ev[2 * slot]); cudaEventCreate(&h->ev[2 * slot + 1]); }
     cudaEventRecord(h->ev[2 * slot], st);
   }
@@ -64,7 +52,9 @@ static cudaError_t timed_launch(NemitHandle* h, int kind, cudaStream_t st, F&& f
   if (rec) {
     cudaEventRecord(h->ev[2 * slot + 1], st);
     h->ev_kind[slot] = kind;
-    h->n_pending++;
+    h->ev_count++;
+    h->kind_launches[kind]++;
+    h->kind_rays[kind] += rays;
   }
   h->launches++;
   return e;
@@ -75,22 +65,24 @@ extern "C" int nemit_profile_enable(NemitHandle* h, int32_t on) {
   h->profile = on != 0;
   return NEMIT_OK;
 }
-extern "C" int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int32_t reset) {
+extern "C" int nemit_profile_read(NemitHandle* h, double* ms_per_kind, int64_t* launches_per_kind, int64_t* rays_per_kind,
+                                  int64_t* red_ops_or_null, int32_t reset) {
   if (!h) return NEMIT_E_INVALID;
-  cudaSetDevice(h->device);
-  for (int i = 0; i < h->n_pending; ++i) {
-    cudaEventSynchronize(h->ev[2 * i + 1]);
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, h->ev[2 * i], h->ev[2 * i + 1]) == cudaSuccess) {
-      h->kind_ms[h->ev_kind[i]] += ms;
-      h->kind_launches[h->ev_kind[i]]++;
-    }
-  }
-  h->n_pending = 0;
+  DeviceGuard guard(h->device);
+  while (h->ev_count > 0) profile_fold_oldest(h);
   for (int k = 0; k < NEMIT_PROFILE_KINDS; ++k) {
     if (ms_per_kind) ms_per_kind[k] = h->kind_ms[k];
     if (launches_per_kind) launches_per_kind[k] = h->kind_launches[k];
-    if (reset) { h->kind_ms[k] = 0.0; h->kind_launches[k] = 0; }
+    if (rays_per_kind) rays_per_kind[k] = h->kind_rays[k];
+    if (reset) { h->kind_ms[k] = 0.0; h->kind_launches[k] = 0; h->kind_rays[k] = 0; }
+  }
+  if (red_ops_or_null || reset) {
+    cudaError_t e = cudaDeviceSynchronize();
+    unsigned long long c = 0;
+    if (e == cudaSuccess) e = cudaMemcpy(&c, h->counters, sizeof(c), cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && reset) e = cudaMemset(h->counters, 0, sizeof(unsigned long long) * 8);
+    if (e != cudaSuccess) return cuda_fail(e, "nemit_profile_read");
+    if (red_ops_or_null) *red_ops_or_null = (int64_t)c;
   }
   return NEMIT_OK;
 }
@@ -122,6 +114,12 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
       cfg->prop_hidden_dim != kPropHidden)
     return fail(NEMIT_E_INVALID, "nemit_create: this build supports hidden 64 / geo 15 / appearance 32 / proposal hidden 16%s");
   if (cfg->num_images < 1) return fail(NEMIT_E_INVALID, "nemit_create: num_images must be >= 1%s");
+  if (cfg->use_fake_contraction)
+    return fail(NEMIT_E_INVALID, "nemit_create: use_fake_contraction (FakeContraction + AABBBoxCollider, NS/models/nerfacto.py:144-154,263-270) "
+                                 "is not implemented by this build; sdf-nerfacto runs with SceneContraction(order=inf)%s");
+  if (cfg->far_intersect)
+    return fail(NEMIT_E_INVALID, "nemit_create: far_intersect (AABBBoxFarIntersectCollider in get_point_lights, NS/models/sdf_nerfacto.py:193-194) "
+                                 "is not implemented by this build%s");
   if (!cfg->lin0_host || !cfg->u1_host || !cfg->u2_host)
     return fail(NEMIT_E_INVALID, "nemit_create: sampler tables missing%s");
   if (cfg->cpu_sum_width != 0 && cfg->cpu_sum_width != 8 && cfg->cpu_sum_width != 16)
@@ -130,7 +128,7 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   cudaError_t e = cudaGetDeviceCount(&ndev);
   if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
   if (device < 0 || device >= ndev) return fail(NEMIT_E_INVALID, "nemit_create: no such CUDA device%s");
-  if ((e = cudaSetDevice(device)) != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+  DeviceGuard guard(device);
   NemitHandle* h = new (std::nothrow) NemitHandle();
   if (!h) return fail(NEMIT_E_INVALID, "nemit_create: out of host memory%s");
   memset(h, 0, sizeof(*h));
@@ -152,7 +150,7 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   h->M.interlevel_mult = cfg->interlevel_mult;
   h->M.distortion_mult = cfg->distortion_mult;
   const int n0 = kS0 + 1, n1 = kS1 + 1, n2 = kS2 + 1;
-  if ((e = cudaMalloc(&h->tables_dev, sizeof(float) * (n0 + n1 + n2 + 9))) != cudaSuccess) {
+  if ((e = cudaMalloc(&h->tables_dev, sizeof(float) * (n0 + n1 + n2 + 17))) != cudaSuccess) {
     delete h;
     return cuda_fail(e, "cudaMalloc(sampler tables)");
   }
@@ -164,16 +162,29 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   h->u1 = h->tables_dev + n0;
   h->u2 = h->tables_dev + n0 + n1;
   h->opt_stats = reinterpret_cast<double*>(h->tables_dev + ((n0 + n1 + n2 + 1) & ~1));   // 8-byte aligned tail
+  h->ev = static_cast<cudaEvent_t*>(calloc(2 * kEvRing, sizeof(cudaEvent_t)));
+  h->ev_kind = static_cast<int*>(calloc(kEvRing, sizeof(int)));
+  e = cudaMalloc(&h->counters, sizeof(unsigned long long) * 8);
+  if (e == cudaSuccess) e = cudaMemset(h->counters, 0, sizeof(unsigned long long) * 8);
+  if (e != cudaSuccess || !h->ev || !h->ev_kind) {
+    cudaFree(h->tables_dev); cudaFree(h->counters); free(h->ev); free(h->ev_kind); delete h;
+    return e != cudaSuccess ? cuda_fail(e, "cudaMalloc(counters)") : fail(NEMIT_E_INVALID, "nemit_create: out of host memory%s");
+  }
   *out = h;
   return NEMIT_OK;
 }
 
 extern "C" int nemit_destroy(NemitHandle* h) {
   if (!h) return NEMIT_OK;
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
+  nemit_comm_destroy(h);
   cudaFree(h->tables_dev);
+  cudaFree(h->counters);
   free(h->rotation_ids);
-  for (int i = 0; i < 2 * 512; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  if (h->ev)
+    for (int i = 0; i < 2 * kEvRing; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  free(h->ev);
+  free(h->ev_kind);
   delete h;
   return NEMIT_OK;
 }
@@ -250,7 +261,7 @@ extern "C" int nemit_set_precision(NemitHandle* h, int32_t precision) {
 static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
-  size_t t_edges2, s_edges2, host_stage, bwd, total;
+  size_t t_edges2, s_edges2, s_edges1, host_stage, bwd, total;
   size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles, act_tiles, seeds4;   // inside the backward block
 };
 static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
@@ -286,6 +297,7 @@ static WsLayout ws_layout(int64_t n) {
   size_t off = 0;
   L.t_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
   L.s_edges2 = off; off += align_up(sizeof(float) * (size_t)c * (kS2 + 1));
+  L.s_edges1 = off; off += align_up(sizeof(float) * (size_t)(c < kBwdChunkRays ? c : kBwdChunkRays) * (kS1 + 1));   // backward sub-chunk
   L.bwd = off;      off += backward_chunk_bytes(c, &L, off);
   L.host_stage = off; off += align_up(sizeof(float) * (size_t)(n < 1 ? 1 : n) * 13);   // o,v (6) near (1) jitter (3) rgb (3)
   L.total = off;
@@ -327,8 +339,20 @@ static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who)
   if (!(r->anneal > 0.f)) return fail(NEMIT_E_INVALID, "%s: anneal must be > 0", who);
   if (r->layout != NEMIT_RAYS_MITSUBA_3N && r->layout != NEMIT_RAYS_NERF_N3)
     return fail(NEMIT_E_INVALID, "%s: unknown ray layout", who);
+  if ((r->kept_t_edges2 != nullptr) != (r->kept_s_edges2 != nullptr) || (r->kept_s_edges1 && !r->kept_t_edges2))
+    return fail(NEMIT_E_INVALID, "%s: kept_t_edges2 and kept_s_edges2 come together (kept_s_edges1 only with them)", who);
   return NEMIT_OK;
 }
+
+// The final samples of rays [off, off + n) of a reverse- / forward-mode call: the edges kept from the primal of the same
+// CustomOp instance (NemitRays.kept_*), or a proposal sampling pass into the workspace.
+struct ChunkEdges {
+  const float* t_edges2;
+  const float* s_edges2;
+  const float* s_edges1;   // only when asked for
+};
+static int chunk_edges(NemitHandle* h, const ModelDev& M, const NemitRays* rays, int64_t off, int64_t n, char* ws,
+                       const struct WsLayout& L, bool need_s1, cudaStream_t st, ChunkEdges* out);
 
 static void fill_ray_args(const NemitHandle* h, RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
   A.o = r->o; A.v = r->v; A.near_per_ray = r->near_per_ray; A.near_scalar = r->near_scalar;
@@ -366,19 +390,38 @@ static void offset_levels(SampleArgs& S, const NemitLevelsOut* L, int64_t off) {
   if (L->inds2) S.inds2 = L->inds2 + off * (kS2 + 1);
 }
 
+static int chunk_edges(NemitHandle* h, const ModelDev& M, const NemitRays* rays, int64_t off, int64_t n, char* ws,
+                       const WsLayout& L, bool need_s1, cudaStream_t st, ChunkEdges* out) {
+  if (rays->kept_t_edges2 && (!need_s1 || rays->kept_s_edges1)) {
+    out->t_edges2 = rays->kept_t_edges2 + off * (kS2 + 1);
+    out->s_edges2 = rays->kept_s_edges2 + off * (kS2 + 1);
+    out->s_edges1 = need_s1 ? rays->kept_s_edges1 + off * (kS1 + 1) : nullptr;
+    return NEMIT_OK;
+  }
+  SampleArgs S;
+  fill_sample_args(h, S, rays, off, n);
+  S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
+  S.s_edges2 = reinterpret_cast<float*>(ws + L.s_edges2);
+  S.s_edges1 = need_s1 ? reinterpret_cast<float*>(ws + L.s_edges1) : nullptr;
+  cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, n, [&] { return launch_sample_levels(M, S, st, h->sampler == NEMIT_SAMPLER_FAST); });
+  if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+  out->t_edges2 = S.t_edges2; out->s_edges2 = S.s_edges2; out->s_edges1 = S.s_edges1;
+  return NEMIT_OK;
+}
+
 extern "C" int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const NemitLevelsOut* out,
                                    void* workspace, size_t workspace_bytes, void* stream) {
   (void)workspace; (void)workspace_bytes;
   int rc = check_rays(h, rays, "nemit_sample_levels");
   if (rc) return rc;
   if (!out) return fail(NEMIT_E_INVALID, "nemit_sample_levels: null outputs%s");
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   for (int64_t off = 0; off < rays->n; off += kChunkRays) {
     int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     offset_levels(S, out, off);
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, n, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
   }
   return NEMIT_OK;
@@ -393,7 +436,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
   WsLayout L = ws_layout(rays->n);
   if (!workspace || workspace_bytes < L.total)
     return fail(NEMIT_E_WORKSPACE, "nemit_forward: workspace too small%s (need %lld bytes)", "", (long long)L.total);
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   char* ws = static_cast<char*>(workspace);
   for (int64_t off = 0; off < rays->n; off += kChunkRays) {
     int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
@@ -403,7 +446,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
     float* user_t = S.t_edges2;
     S.t_edges2 = t_edges;
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
+    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, n, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     if (user_t) {
       e = cudaMemcpyAsync(user_t, t_edges, sizeof(float) * n * (kS2 + 1), cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
@@ -418,9 +461,9 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     F.accumulation = accumulation ? accumulation + off : nullptr;
     F.weights2 = (levels && levels->weights2) ? levels->weights2 + off * kS2 : nullptr;
     if (h->precision == NEMIT_PRECISION_FP16_TC)
-      e = timed_launch(h, NEMIT_K_FIELD_TC, (cudaStream_t)stream, [&] { return launch_field_forward_tc(h->M, F, (cudaStream_t)stream); });
+      e = timed_launch(h, NEMIT_K_FIELD_TC, (cudaStream_t)stream, n, [&] { return launch_field_forward_tc(h->M, F, (cudaStream_t)stream); });
     else
-      e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
+      e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, n, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
   }
   return NEMIT_OK;
@@ -430,7 +473,7 @@ extern "C" int nemit_hash_encode(NemitHandle* h, int32_t which, const float* x, 
   if (!h || (n > 0 && (!x || !out))) return fail(NEMIT_E_INVALID, "nemit_hash_encode: null argument%s");
   if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_hash_encode: parameters not bound%s");
   if (which < 0 || which > 2) return fail(NEMIT_E_INVALID, "nemit_hash_encode: which must be 0, 1 or 2%s");
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   const GridDev& G = which == 0 ? h->M.main_grid : h->M.prop_grid[which - 1];
   const float* t = which == 0 ? h->P.main_table : h->P.prop_table[which - 1];
   cudaError_t e = launch_hash_encode(G, reinterpret_cast<const float2*>(t), x, n, out, (cudaStream_t)stream);
@@ -502,7 +545,7 @@ extern "C" int nemit_density_fn(NemitHandle* h, int32_t which, const float* posi
   if (!h || n < 0 || (n > 0 && (!positions || !density))) return fail(NEMIT_E_INVALID, "nemit_density_fn: null argument%s");
   if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "nemit_density_fn: parameters not bound%s");
   if (which < 0 || which > 2) return fail(NEMIT_E_INVALID, "nemit_density_fn: which must be 0, 1 or 2%s");
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   cudaError_t e;
   if (which == 0) {
     FieldParams P;
@@ -526,7 +569,7 @@ extern "C" int nemit_field_samples(NemitHandle* h, const float* positions, const
   int app_row;      // the model has already mapped camera -> rotation ids on ray_samples (sdf_nerfacto.py:71-72)
   if (!appearance_row(h, training, camera_idx, false, &app_row))
     return fail(NEMIT_E_INVALID, "nemit_field_samples: camera_idx outside the appearance embedding%s");
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   FieldParams P;
   fill_field_params(h->P, P);
   cudaError_t e = launch_field_samples(h->M, P, positions, directions, n, app_row, density, nullptr, rgb,
@@ -545,7 +588,7 @@ extern "C" int nemit_forward_host(NemitHandle* h, const NemitRays* rh, float* rg
   WsLayout L = ws_layout(rh->n);
   if (!workspace || workspace_bytes < L.total)
     return fail(NEMIT_E_WORKSPACE, "nemit_forward_host: workspace too small%s (need %lld bytes)", "", (long long)L.total);
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t n = rh->n;
   float* stage = reinterpret_cast<float*>(static_cast<char*>(workspace) + L.host_stage);
@@ -581,24 +624,22 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
   WsLayout L = ws_layout(rays->n);
   if (!workspace || workspace_bytes < L.total)
     return fail(NEMIT_E_WORKSPACE, "nemit_jvp: workspace too small%s (need %lld bytes)", "", (long long)L.total);
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   char* ws = static_cast<char*>(workspace);
   cudaStream_t st = (cudaStream_t)stream;
   for (int64_t off = 0; off < rays->n; off += kChunkRays) {
     int64_t n = rays->n - off < kChunkRays ? rays->n - off : kChunkRays;
-    SampleArgs S;
-    fill_sample_args(h, S, rays, off, n);
-    S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st, h->sampler == NEMIT_SAMPLER_FAST); });
-    if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    ChunkEdges E;
+    if ((rc = chunk_edges(h, h->M, rays, off, n, ws, L, false, st, &E))) return rc;
+    cudaError_t e;
     FieldArgs F;
     memset(&F, 0, sizeof(F));
     fill_ray_args(h, F, rays, off, n);
     fill_field_params(h->P, F.P);
-    F.t_edges2 = S.t_edges2;
+    F.t_edges2 = E.t_edges2;
     F.d_o = d_o; F.d_v = d_v;
     F.d_rgb = d_rgb + off * 3;
-    e = timed_launch(h, NEMIT_K_FIELD_JVP, st, [&] { return launch_field_jvp(h->M, F, st); });
+    e = timed_launch(h, NEMIT_K_FIELD_JVP, st, n, [&] { return launch_field_jvp(h->M, F, st); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_jvp");
   }
   return NEMIT_OK;
@@ -616,23 +657,21 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
   WsLayout L = ws_layout(rays->n);
   if (!workspace || workspace_bytes < L.total)
     return fail(NEMIT_E_WORKSPACE, "nemit_backward: workspace too small%s (need %lld bytes)", "", (long long)L.total);
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   char* ws = static_cast<char*>(workspace);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
   for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
     int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
-    float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
-    float* s_edges = reinterpret_cast<float*>(ws + L.s_edges2);
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
     float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
     float* weights2 = reinterpret_cast<float*>(ws + L.weights2);
     float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
-    SampleArgs S;
-    fill_sample_args(h, S, rays, off, n);
-    S.t_edges2 = t_edges;
-    S.s_edges2 = s_edges;
-    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(h->M, S, st, h->sampler == NEMIT_SAMPLER_FAST); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    const bool prop_pass = proposal_requires_grad && h->M.interlevel_mult != 0.f;
+    ChunkEdges E;
+    if ((rc = chunk_edges(h, h->M, rays, off, n, ws, L, prop_pass, st, &E))) return rc;
+    const float* t_edges = E.t_edges2;
+    const float* s_edges = E.s_edges2;
     // pass 1: forward of the 48-sample stage + composite adjoint
     FieldArgs F;
     memset(&F, 0, sizeof(F));
@@ -650,9 +689,9 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
       F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
     }
     if (h->precision == NEMIT_PRECISION_FP16_TC)
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
     else
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(h->M, F, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed(h->M, F, st); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
     // pass 2: MLP / hash-grid backward
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
@@ -671,13 +710,14 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
       B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
       B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
       B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
-      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(h->M, B, st); });
+      B.red_ops = h->profile ? h->counters : nullptr;
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(h->M, B, st); });
     } else {
-      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(h->M, B, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, n, [&] { return launch_field_backward(h->M, B, st); });
     }
     if (e != cudaSuccess) return cuda_fail(e, "k_field_backward");
     // pass 3: interlevel loss -> proposal networks (only when the sampler says they carry autograd)
-    if (proposal_requires_grad && h->M.interlevel_mult != 0.f) {
+    if (prop_pass) {
       PropBwdArgs Q;
       memset(&Q, 0, sizeof(Q));
       fill_sample_args(h, Q, rays, off, n);
@@ -686,15 +726,80 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
         Q.g_w0[i] = h->G.prop_w0[i]; Q.g_b0[i] = h->G.prop_b0[i];
         Q.g_w1[i] = h->G.prop_w1[i]; Q.g_b1[i] = h->G.prop_b1[i];
       }
-      Q.weights2 = weights2; Q.s_edges2_in = s_edges; Q.reg_chunk = chunk_rays; Q.loss_scale = loss_scale;
-      if ((e = timed_launch(h, NEMIT_K_PROP_BWD, st, [&] { return launch_prop_backward(h->M, Q, st); })) != cudaSuccess) return cuda_fail(e, "k_prop_backward");
+      Q.weights2 = weights2; Q.s_edges2_in = s_edges; Q.s_edges1_in = E.s_edges1; Q.reg_chunk = chunk_rays; Q.loss_scale = loss_scale;
+      if ((e = timed_launch(h, NEMIT_K_PROP_BWD, st, n, [&] { return launch_prop_backward(h->M, Q, st); })) != cudaSuccess) return cuda_fail(e, "k_prop_backward");
     }
     FinalizeArgs Z;
     memset(&Z, 0, sizeof(Z));
     fill_ray_args(h, Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = grad_o; Z.grad_v = grad_v;
-    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(h->M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
+    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, n, [&] { return launch_finalize_ray_grads(h->M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
+  return NEMIT_OK;
+}
+
+// stage of nemit_backward_host behind the ordinary workspace: o v (6) near (1) jitter (3) grad_rgb (3) rgb (3) grad_o (3)
+// grad_v (3) = 22 floats per ray, then the primal's kept edges (49 + 49 + 97 floats per ray)
+static size_t host_bwd_stage_bytes(int64_t n) {
+  const size_t m = (size_t)(n < 1 ? 1 : n);
+  return align_up(sizeof(float) * m * 22) + align_up(sizeof(float) * m * (kS2 + 1)) * 2 + align_up(sizeof(float) * m * (kS1 + 1));
+}
+extern "C" size_t nemit_backward_host_workspace_bytes(const NemitHandle* h, int64_t n) {
+  (void)h;
+  return ws_layout(n).total + host_bwd_stage_bytes(n);
+}
+
+extern "C" int nemit_backward_host(NemitHandle* h, const NemitRays* rh, const float* grad_rgb_host, int32_t primal_training,
+                                   int64_t chunk_rays, float loss_scale, int32_t proposal_requires_grad, float* rgb_host,
+                                   float* grad_o_host, float* grad_v_host, void* workspace, size_t workspace_bytes,
+                                   void* stream) {
+  int rc = check_rays(h, rh, "nemit_backward_host");
+  if (rc) return rc;
+  if (!h->grads_bound) return fail(NEMIT_E_UNBOUND, "nemit_backward_host: gradient buffers not bound (nemit_bind_grads)%s");
+  if (rh->n == 0) return NEMIT_OK;
+  if (!grad_rgb_host || !rgb_host || !grad_o_host || !grad_v_host) return fail(NEMIT_E_INVALID, "nemit_backward_host: null host buffer%s");
+  if (rh->kept_t_edges2) return fail(NEMIT_E_INVALID, "nemit_backward_host: kept edges are managed by the call itself%s");
+  const int64_t n = rh->n;
+  const size_t base = ws_layout(n).total;
+  if (!workspace || workspace_bytes < base + host_bwd_stage_bytes(n))
+    return fail(NEMIT_E_WORKSPACE, "nemit_backward_host: workspace too small%s (need %lld bytes)", "", (long long)(base + host_bwd_stage_bytes(n)));
+  DeviceGuard guard(h->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  char* p = static_cast<char*>(workspace) + base;
+  float* stage = reinterpret_cast<float*>(p);
+  float *d_o = stage, *d_v = stage + 3 * n, *d_near = stage + 6 * n, *d_jit = stage + 7 * n, *d_g = stage + 10 * n,
+        *d_rgb = stage + 13 * n, *d_go = stage + 16 * n, *d_gv = stage + 19 * n;
+  p += align_up(sizeof(float) * (size_t)n * 22);
+  float* k_t2 = reinterpret_cast<float*>(p); p += align_up(sizeof(float) * (size_t)n * (kS2 + 1));
+  float* k_s2 = reinterpret_cast<float*>(p); p += align_up(sizeof(float) * (size_t)n * (kS2 + 1));
+  float* k_s1 = reinterpret_cast<float*>(p);
+  cudaError_t e;
+  if ((e = cudaMemcpyAsync(d_o, rh->o, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D o");
+  if ((e = cudaMemcpyAsync(d_v, rh->v, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D v");
+  if ((e = cudaMemcpyAsync(d_g, grad_rgb_host, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D grad_rgb");
+  NemitRays rd = *rh;
+  rd.o = d_o; rd.v = d_v;
+  if (rh->near_per_ray) {
+    if ((e = cudaMemcpyAsync(d_near, rh->near_per_ray, sizeof(float) * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D near");
+    rd.near_per_ray = d_near;
+  }
+  if (rh->jitter) {
+    if ((e = cudaMemcpyAsync(d_jit, rh->jitter, sizeof(float) * 3 * n, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuda_fail(e, "H2D jitter");
+    rd.jitter = d_jit;
+  }
+  // primal (NeRFEmitterOp.eval): the same CustomOp instance's adjoint sees the same samples when the mode is the same
+  const bool keep = (primal_training != 0) == (rh->training != 0);
+  NemitRays rp = rd;
+  rp.training = primal_training != 0;
+  NemitLevelsOut LO;
+  memset(&LO, 0, sizeof(LO));
+  if (keep) { LO.t_edges2 = k_t2; LO.s_edges2 = k_s2; if (proposal_requires_grad) LO.s_edges1 = k_s1; }
+  if ((rc = nemit_forward(h, &rp, d_rgb, nullptr, keep ? &LO : nullptr, workspace, base, stream))) return rc;
+  if (keep) { rd.kept_t_edges2 = k_t2; rd.kept_s_edges2 = k_s2; rd.kept_s_edges1 = proposal_requires_grad ? k_s1 : nullptr; }
+  if ((rc = nemit_backward(h, &rd, d_g, chunk_rays, loss_scale, proposal_requires_grad, d_go, d_gv, workspace, base, stream))) return rc;
+  if ((e = cudaMemcpyAsync(rgb_host, d_rgb, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuda_fail(e, "D2H rgb");
+  if ((e = cudaMemcpyAsync(grad_o_host, d_go, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuda_fail(e, "D2H grad_o");
+  if ((e = cudaMemcpyAsync(grad_v_host, d_gv, sizeof(float) * 3 * n, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuda_fail(e, "D2H grad_v");
   return NEMIT_OK;
 }
 
@@ -711,7 +816,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
   WsLayout L = ws_layout(rays->n);
   if (!workspace || workspace_bytes < L.total)
     return fail(NEMIT_E_WORKSPACE, "nemit_point_lights: workspace too small%s (need %lld bytes)", "", (long long)L.total);
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   char* ws = static_cast<char*>(workspace);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
@@ -720,17 +825,14 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
   const bool tc = h->precision == NEMIT_PRECISION_FP16_TC;
   for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
     int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
-    float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
-    float* s_edges = reinterpret_cast<float*>(ws + L.s_edges2);
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
     float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
     float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
     float* g_absmax = reinterpret_cast<float*>(ws + L.g_absmax);
-    SampleArgs S;
-    fill_sample_args(h, S, rays, off, n);
-    S.t_edges2 = t_edges;
-    S.s_edges2 = s_edges;
-    if ((e = timed_launch(h, NEMIT_K_SAMPLE, st, [&] { return launch_sample_levels(M, S, st, h->sampler == NEMIT_SAMPLER_FAST); })) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+    ChunkEdges E;
+    if ((rc = chunk_edges(h, M, rays, off, n, ws, L, false, st, &E))) return rc;
+    const float* t_edges = E.t_edges2;
+    const float* s_edges = E.s_edges2;
     FieldArgs F;
     memset(&F, 0, sizeof(F));
     fill_ray_args(h, F, rays, off, n);
@@ -746,9 +848,9 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
       F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
       F.act_tiles = reinterpret_cast<uint8_t*>(ws + L.act_tiles);
       F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed_tc(M, F, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(M, F, st); });
     } else {
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, [&] { return launch_field_adjoint_seed(M, F, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed(M, F, st); });
     }
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
@@ -763,16 +865,16 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
       B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
       B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
       B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
-      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, [&] { return launch_field_backward_tc(M, B, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(M, B, st); });
     } else {
-      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, [&] { return launch_field_backward(M, B, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_BWD, st, n, [&] { return launch_field_backward(M, B, st); });
     }
     if (e != cudaSuccess) return cuda_fail(e, "k_field_backward");
     FinalizeArgs Z;
     memset(&Z, 0, sizeof(Z));
     fill_ray_args(h, Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = brightness_grad; Z.grad_v = nullptr;
-    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
+    if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, n, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
   return NEMIT_OK;
 }
@@ -788,7 +890,7 @@ extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const
   if (!params_complete(exp_avg) || !params_complete(exp_avg_sq)) return fail(NEMIT_E_INVALID, "nemit_adam_step: an optimizer-state pointer is null%s");
   if (step < 1) return fail(NEMIT_E_INVALID, "nemit_adam_step: step counts from 1%s");
   if (!(grad_scale > 0.f)) return fail(NEMIT_E_INVALID, "nemit_adam_step: grad_scale must be > 0%s");
-  cudaSetDevice(h->device);
+  DeviceGuard guard(h->device);
   const NemitConfig& c = h->cfg;
   const int64_t main_n = ((int64_t)c.main_grid.num_levels << c.main_grid.log2_table_size) * 2;
   const int64_t enc = c.main_grid.num_levels * 2, hd = c.hidden_dim, head_in = 16 + c.geo_feat_dim + c.appearance_dim;
@@ -896,6 +998,7 @@ extern "C" int nemit_bake_envmap(NemitHandle* h, const NemitSphericalSensor* s, 
   if (!h || !accum) return fail(NEMIT_E_INVALID, "nemit_bake_envmap: null argument%s");
   if (row_begin < 0 || row_end > s->height || row_begin > row_end) return fail(NEMIT_E_INVALID, "nemit_bake_envmap: bad row range%s");
   if (!workspace || workspace_bytes < nemit_bake_workspace_bytes(h)) return fail(NEMIT_E_WORKSPACE, "nemit_bake_envmap: workspace too small%s");
+  DeviceGuard guard(h->device);      // the ray-generation and film kernels below carry no handle: run them on its device
   char* ws = static_cast<char*>(workspace);
   const size_t fwd_bytes = ws_layout(kChunkRays).total;
   float* stage = reinterpret_cast<float*>(ws + fwd_bytes);

@@ -115,7 +115,8 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
 // is skipped.  Corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices
 // differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
 template <int LB, int LE>
-__device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const ModelDev& M, float2* table, float gscale) {
+__device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const ModelDev& M, float2* table, float gscale,
+                                               uint32_t& nred) {
   if (!table) return;                     // ray-gradient-only pass (nemit_point_lights): no parameter gradients
   const float p[3] = {H->pbuf[t], H->pbuf[128 + t], H->pbuf[256 + t]};
 #pragma unroll kScatterUnroll
@@ -130,6 +131,7 @@ __device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const 
     const float gxs = gx * gscale, gys = gy * gscale;
     const float xs = mul_rn(p[0], sc);
     const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
+    nred += pair ? 4u : 8u;
     if (pair) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
@@ -227,6 +229,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   bool first = true;
   uint32_t ld_phase = 0;
   const float gscale = invS * A.loss_scale;
+  uint32_t nred = 0;                 // reduction lane-ops this thread issued (reported when profiling)
   // deferred scatter: nothing parked yet
 #pragma unroll
   for (int c = 0; c < 32; ++c) H->denc[c * 128 + t] = 0.f;
@@ -278,13 +281,13 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    }, [&] { scatter_levels<0, 4>(H, t, M, A.G.main_table, gscale); });
+    }, [&] { scatter_levels<0, 4>(H, t, M, A.G.main_table, gscale, nred); });
     epi_bwd_hidden(taddr + kColD0, H->h3, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
-    }, [&] { scatter_levels<4, 7>(H, t, M, A.G.main_table, gscale); });
+    }, [&] { scatter_levels<4, 7>(H, t, M, A.G.main_table, gscale, nred); });
     if (t == 0 && has_next) {       // H3 / G3 has no reader left: the next tile's copies start here
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
       load_h3(next_tile);
@@ -294,7 +297,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
-    }, [&] { scatter_levels<7, 10>(H, t, M, A.G.main_table, gscale); });
+    }, [&] { scatter_levels<7, 10>(H, t, M, A.G.main_table, gscale, nred); });
     if (t == 0 && has_next) { load_h2(next_tile); load_in(next_tile); }
     {
       float v[16];
@@ -318,7 +321,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    }, [&] { scatter_levels<10, 13>(H, t, M, A.G.main_table, gscale); });
+    }, [&] { scatter_levels<10, 13>(H, t, M, A.G.main_table, gscale, nred); });
     epi_bwd_hidden(taddr + kColD0, H->h1, t);
     // this tile's Jacobian rows: the loads fly under the last commit group
     uint4 jn[12];
@@ -331,7 +334,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
-    }, [&] { scatter_levels<13, 16>(H, t, M, A.G.main_table, gscale); });
+    }, [&] { scatter_levels<13, 16>(H, t, M, A.G.main_table, gscale, nred); });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 
     // ---- hash grid backward: d/d(position) now; the table scatter of this tile is parked in shared memory and runs in
@@ -377,7 +380,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   }
 
   // ---- the last tile's parked scatter ---------------------------------------------------------------
-  scatter_levels<0, 16>(H, t, M, A.G.main_table, gscale);
+  scatter_levels<0, 16>(H, t, M, A.G.main_table, gscale, nred);
 
   // ---- flush this half's weight-gradient accumulators (torch layouts, loss scale applied) ---------------
   if (!first && A.G.main_table) {
@@ -456,6 +459,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       for (int n = 0; n < kHidden; ++n) g = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + t], H->dvec[n], g);
       appearance_component_grad(A.G.appearance, M.num_images, A.app_row, t, g);
     }
+  }
+  if (A.red_ops) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) nred += __shfl_xor_sync(0xffffffffu, nred, o);
+    if (lane == 0) atomicAdd(A.red_ops, (unsigned long long)nred);
   }
   tc::tc_fence_before();
   __syncthreads();

@@ -125,6 +125,7 @@ struct FieldBwdArgs : RayArgs {
   const uint8_t* jac_tiles;
   const uint8_t* act_tiles;
   const float4* seeds4;
+  unsigned long long* red_ops;   // or null: device counter of the reduction lane-ops the table scatter issues (profiling)
 };
 
 struct PropBwdArgs : SampleArgs {
@@ -132,6 +133,7 @@ struct PropBwdArgs : SampleArgs {
   float* g_w0[2]; float* g_b0[2]; float* g_w1[2]; float* g_b1[2];
   const float* weights2;   // (n, 48) final weights (detached in the interlevel loss)
   const float* s_edges2_in;// (n, 49)
+  const float* s_edges1_in;// (n, 97) level-1 spacing edges of the SAME sampling pass (exact or fast sampler) that made s_edges2_in
   int64_t reg_chunk;
   float loss_scale;
 };

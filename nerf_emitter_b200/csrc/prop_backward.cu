@@ -1,5 +1,5 @@
 // prop_backward.cu - k_prop_backward: gradient of the interlevel (proposal) loss w.r.t. the two proposal
-// networks, one ray per warp.  The proposal loop is recomputed (same code as k_sample_levels), then per
+// networks, one ray per warp.  The proposal densities are recomputed in fp32 at the sampling pass's own edges, then per
 // level: outer-measure bound of the final histogram by the proposal histogram, its adjoint into the
 // proposal weights, the weights -> density adjoint, the 10->16->1 MLP backward and the hash-table
 // scatter-add.  Rays are detached on this path (NS/models/sdf_nerfacto.py:121-126): no ray gradients.
@@ -247,8 +247,9 @@ k_prop_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Prop
         prop_level_backward(pw, R, S, A.prop_table[0], A.g_table[0], M.prop_grid[0], &sm->mlp[0], M, coef,
                             A.loss_scale, acc[0], lane);
         __syncwarp();
-        pdf_resample_warp(sc, kS0, kS1, A.u1, jit ? jit[1] : -1.f, A.anneal, M.cpu_sum_width, lane, nullptr);
-        for (int i = lane; i <= kS1; i += 32) sc->s_edge[i] = sc->s_new[i];
+        // level-1 edges: the ones the sampling pass of this call produced (so the proposal histogram bounded here is the
+        // one the final samples were drawn from, whichever sampler arithmetic ran), not a second PDF stage
+        for (int i = lane; i <= kS1; i += 32) sc->s_edge[i] = A.s_edges1_in[r * (kS1 + 1) + i];
         __syncwarp();
       } else {
         prop_level_backward(pw, R, S, A.prop_table[1], A.g_table[1], M.prop_grid[1], &sm->mlp[1], M, coef,

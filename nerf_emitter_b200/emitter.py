@@ -145,14 +145,41 @@ class NerfEmitter:
         for g in self.grads.values():
             g.zero_()
 
+    def init_comm(self, group=None):
+        """Create the library's own NCCL communicator over the ranks of the (initialised) torch.distributed group:
+        rank 0 draws the unique id (nemit_comm_unique_id), torch.distributed only carries its 128 bytes to the others."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        ident = torch.zeros(L.UNIQUE_ID_BYTES, dtype=torch.uint8)
+        if rank == 0:
+            L.check(self.lib.nemit_comm_unique_id(C.c_void_p(ident.data_ptr())), "nemit_comm_unique_id")
+        carrier = ident.to(self.device) if dist.get_backend(group) == "nccl" else ident
+        dist.broadcast(carrier, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        ident = carrier.cpu().contiguous()
+        L.check(self.lib.nemit_comm_init(self._h, C.c_void_p(ident.data_ptr()), rank, world), "nemit_comm_init")
+        self.comm_world = world
+        return self
+
+    def allreduce_blob(self, blob: torch.Tensor, group=None, scale=None):
+        """In-place sum over the ranks of any contiguous fp32 CUDA tensor through nemit_allreduce_grads (the bake's film
+        accumulators use the same collective as the gradients)."""
+        import torch.distributed as dist
+        if blob.dtype != torch.float32 or not blob.is_cuda or not blob.is_contiguous():
+            raise ValueError("allreduce_blob needs a contiguous fp32 CUDA tensor")
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1 \
+                and getattr(self, "comm_world", 0) != dist.get_world_size(group):
+            self.init_comm(group)
+        L.check(self.lib.nemit_allreduce_grads(self._h, _ptr(blob), blob.numel(), 1.0 if scale is None else float(scale),
+                                               self._stream()), "nemit_allreduce_grads")
+        return blob
+
     def allreduce_grads(self, group=None, scale=None):
-        """The one collective of the path: sum parameter gradients over the ray-sharded ranks."""
-        from . import parallel
-        if getattr(self, "flat_grads", None) is not None:
-            parallel.allreduce_grads(self.flat_grads, group, scale)
-        else:
-            for g in self.grads.values():
-                parallel.allreduce_grads(g, group, scale)
+        """The one collective of the path: sum parameter gradients over the ray-sharded ranks, through the library
+        (nemit_allreduce_grads: NCCL all-reduce with the unscale folded in as a pre-multiplied sum, one pass over the
+        blob).  The communicator is created on first use when torch.distributed is initialised."""
+        if getattr(self, "flat_grads", None) is None:
+            raise L.NemitError("allreduce_grads needs the flat gradient blob: call bind_grads() without arguments")
+        return self.allreduce_blob(self.flat_grads, group, scale)
 
     def set_precision(self, precision: str = "fp32"):
         """'fp32' = exact FMA path (parity mode); 'fp16' = fp16-operand tensor-core MLP (tcgen05, fp32 accumulate)."""
@@ -203,7 +230,7 @@ class NerfEmitter:
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
-    def _rays(self, o3n, v3n, near, camera_idx, jitter, nerf_layout: bool = False) -> L.NemitRays:
+    def _rays(self, o3n, v3n, near, camera_idx, jitter, nerf_layout: bool = False, kept=None) -> L.NemitRays:
         """nerf_layout: o, v are RayBundle.origins / .directions, (N,3) rows in NeRF coordinates (NEMIT_RAYS_NERF_N3)
         instead of the CustomOp's (3,N) Mitsuba unit-cube arrays."""
         n = o3n.shape[0] if nerf_layout else o3n.shape[1]
@@ -233,6 +260,16 @@ class NerfEmitter:
         else:
             R.jitter = None
         R.anneal = float(self.anneal)
+        if kept is not None:
+            # sample edges kept from the primal of the same CustomOp instance (render(..., keep_edges=True))
+            s2 = self.spec.num_nerf_samples + 1
+            _check(kept["t_edges2"], (n, s2), "kept t_edges2")
+            _check(kept["s_edges2"], (n, s2), "kept s_edges2")
+            R.kept_t_edges2, R.kept_s_edges2 = kept["t_edges2"].data_ptr(), kept["s_edges2"].data_ptr()
+            if kept.get("s_edges1") is not None:
+                _check(kept["s_edges1"], (n, self.spec.num_proposal_samples[1] + 1), "kept s_edges1")
+                R.kept_s_edges1 = kept["s_edges1"].data_ptr()
+            self._keep.append(kept)
         return R
 
     def _levels_out(self, n: int, want_weights2: bool):
@@ -253,12 +290,25 @@ class NerfEmitter:
 
     # -- the three modes -------------------------------------------------------------------
     def render(self, o3n: torch.Tensor, v3n: torch.Tensor, near=0.0, camera_idx: int = 0, jitter=None,
-               return_aux: bool = False, nerf_layout: bool = False):
-        """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> rgb (N,3)."""
+               return_aux: bool = False, nerf_layout: bool = False, keep_edges: bool = False):
+        """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> rgb (N,3).
+        keep_edges: also return {s_edges1, s_edges2, t_edges2} (780 B per ray) for the adjoint of the same CustomOp
+        instance (``backward(..., kept=...)`` then skips the proposal sampling pass; valid while mode, near, anneal,
+        jitter and parameters are unchanged - the reference re-derives the same samples from restored generator state)."""
         n = o3n.shape[0] if nerf_layout else o3n.shape[1]
         R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
         rgb = torch.empty(n, 3, device=self.device, dtype=torch.float32)
         ws = self._workspace(n)
+        if keep_edges and not return_aux:
+            s1, s2 = self.spec.num_proposal_samples[1] + 1, self.spec.num_nerf_samples + 1
+            kept = dict(s_edges1=torch.empty(n, s1, device=self.device), s_edges2=torch.empty(n, s2, device=self.device),
+                        t_edges2=torch.empty(n, s2, device=self.device), training=self.training, anneal=self.anneal)
+            LO = L.NemitLevelsOut()
+            for k in ("s_edges1", "s_edges2", "t_edges2"):
+                setattr(LO, k, kept[k].data_ptr())
+            L.check(self.lib.nemit_forward(self._h, C.byref(R), _ptr(rgb), None, C.byref(LO), _ptr(ws), ws.numel(),
+                                           self._stream()), "nemit_forward")
+            return rgb, kept
         if not return_aux:
             L.check(self.lib.nemit_forward(self._h, C.byref(R), _ptr(rgb), None, None, _ptr(ws), ws.numel(),
                                            self._stream()), "nemit_forward")
@@ -288,10 +338,18 @@ class NerfEmitter:
                 "nemit_sample_levels")
         return aux
 
-    def jvp(self, o3n, v3n, do3n, dv3n, near=0.0, camera_idx: int = 0, jitter=None, nerf_layout: bool = False):
+    def _usable_kept(self, kept):
+        if kept is None:
+            return None
+        if bool(kept.get("training")) != self.training or float(kept.get("anneal", 1.0)) != float(self.anneal):
+            return None                      # mode changed since the primal: sample again
+        return kept
+
+    def jvp(self, o3n, v3n, do3n, dv3n, near=0.0, camera_idx: int = 0, jitter=None, nerf_layout: bool = False,
+            kept=None):
         """NeRFEmitterOp.ns_forward_ray (nerf_emitter_op.py:60-90): tangents (3,N) -> d_rgb (N,3)."""
         n = o3n.shape[0] if nerf_layout else o3n.shape[1]
-        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout, self._usable_kept(kept))
         _check(do3n, tuple(o3n.shape), "d_o")
         _check(dv3n, tuple(o3n.shape), "d_v")
         out = torch.empty(n, 3, device=self.device, dtype=torch.float32)
@@ -302,7 +360,7 @@ class NerfEmitter:
 
     def backward(self, o3n, v3n, grad_rgb, near=0.0, camera_idx: int = 0, jitter=None,
                  chunk_rays: Optional[int] = None, loss_scale: float = 1.0, proposal_requires_grad: bool = True,
-                 nerf_layout: bool = False):
+                 nerf_layout: bool = False, kept=None):
         """NeRFEmitterOp.ns_backward_ray (nerf_emitter_op.py:92-117): returns (grad_o, grad_v) as (3,N);
         parameter gradients are accumulated into the bound ``grads``.  ``proposal_requires_grad`` is the sampler's
         ``updated`` flag (ray_samplers.py:598): one bool for the whole call, or one bool per chunk of ``chunk_rays``
@@ -330,17 +388,18 @@ class NerfEmitter:
                         c1 += 1
                     a, b = c0 * chunk, min(c1 * chunk, n)
                     nr = near[a:b] if isinstance(near, torch.Tensor) and near.numel() > 1 else near
+                    kp = None if kept is None else {k: (t[a:b] if isinstance(t, torch.Tensor) else t) for k, t in kept.items()}
                     g_o, g_v = self.backward(rows(o3n, a, b), rows(v3n, a, b), grad_rgb[a:b], near=nr,
                                              camera_idx=camera_idx, jitter=None if jitter is None else jitter[a:b],
                                              chunk_rays=chunk, loss_scale=loss_scale,
-                                             proposal_requires_grad=flags[c0], nerf_layout=nerf_layout)
+                                             proposal_requires_grad=flags[c0], nerf_layout=nerf_layout, kept=kp)
                     if nerf_layout:
                         go[a:b], gv[a:b] = g_o, g_v
                     else:
                         go[:, a:b], gv[:, a:b] = g_o, g_v
                     c0 = c1
                 return go, gv
-        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout)
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, nerf_layout, kept)
         _check(grad_rgb, (n, 3), "grad_rgb")
         go = torch.empty_like(o3n)
         gv = torch.empty_like(o3n)
@@ -380,6 +439,43 @@ class NerfEmitter:
         L.check(self.lib.nemit_forward_host(self._h, C.byref(R), C.c_void_p(rgb_host.data_ptr()), _ptr(ws), ws.numel(),
                                             self._stream()), "nemit_forward_host")
         return rgb_host
+
+    def backward_host(self, o_host, v_host, grad_rgb_host, rgb_host, grad_o_host, grad_v_host, near: float = 0.0,
+                      camera_idx: int = 0, primal_training: bool = False, chunk_rays: Optional[int] = None,
+                      loss_scale: float = 1.0, proposal_requires_grad: bool = False):
+        """End-to-end fwd+bwd with pinned HOST buffers in one plugin call (nemit_backward_host): H2D of rays and
+        grad_out, the primal render (eval mode, or training mode with its edges kept for the adjoint), the
+        training-mode backward, D2H of radiance and ray gradients - all queued on the current stream."""
+        if not self.grads:
+            self.bind_grads()
+        n = o_host.shape[1]
+        for t, nm in [(o_host, "o_host"), (v_host, "v_host"), (grad_rgb_host, "grad_rgb_host"), (rgb_host, "rgb_host"),
+                      (grad_o_host, "grad_o_host"), (grad_v_host, "grad_v_host")]:
+            if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                raise ValueError("%s must be a contiguous fp32 host tensor" % nm)
+        R = L.NemitRays()
+        R.o, R.v, R.n = o_host.data_ptr(), v_host.data_ptr(), n
+        R.near_per_ray, R.near_scalar, R.camera_idx, R.training = None, float(near), int(camera_idx), 1
+        R.jitter, R.anneal = None, float(self.anneal)
+        need = int(self.lib.nemit_backward_host_workspace_bytes(self._h, n))
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        ws = self._ws
+        L.check(self.lib.nemit_backward_host(self._h, C.byref(R), C.c_void_p(grad_rgb_host.data_ptr()),
+                                             int(bool(primal_training)), int(chunk_rays or n), float(loss_scale),
+                                             int(bool(proposal_requires_grad)), C.c_void_p(rgb_host.data_ptr()),
+                                             C.c_void_p(grad_o_host.data_ptr()), C.c_void_p(grad_v_host.data_ptr()),
+                                             _ptr(ws), ws.numel(), self._stream()), "nemit_backward_host")
+        return rgb_host, grad_o_host, grad_v_host
+
+    def microbench(self):
+        """{name: operations per second} of the ceilings the kernels are reported against (nemit_microbench)."""
+        out = {}
+        for i, name in enumerate(L.MICROBENCH_KINDS):
+            res = (C.c_double * 2)()
+            L.check(self.lib.nemit_microbench(self._h, i, res, self._stream()), "nemit_microbench")
+            out[name] = float(res[0])
+        return out
 
     def hash_encode(self, x: torch.Tensor, which: int = 0) -> torch.Tensor:
         """HashEncoding.forward (NS/field_components/encodings.py:341-382) on (n,3) points in [0,1]."""
@@ -422,12 +518,19 @@ class NerfEmitter:
         """Per-kernel CUDA-event timing inside the library (on the launching stream)."""
         L.check(self.lib.nemit_profile_enable(self._h, int(on)), "nemit_profile_enable")
 
-    def profile_read(self, reset: bool = True):
-        """{kernel: (total ms, launches)} accumulated since the last reset."""
+    def profile_read(self, reset: bool = True, with_rays: bool = False):
+        """{kernel: (total ms, launches)} accumulated since the last reset; with_rays: {kernel: (ms, launches, rays)}
+        plus the key "red_lane_ops" (reduction lane-ops the tensor-core backward's table scatter issued)."""
         ms = (C.c_double * len(L.PROFILE_KINDS))()
         cnt = (C.c_int64 * len(L.PROFILE_KINDS))()
-        L.check(self.lib.nemit_profile_read(self._h, ms, cnt, int(reset)), "nemit_profile_read")
-        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(L.PROFILE_KINDS) if cnt[i]}
+        rays = (C.c_int64 * len(L.PROFILE_KINDS))()
+        red = C.c_int64(0)
+        L.check(self.lib.nemit_profile_read(self._h, ms, cnt, rays, C.byref(red), int(reset)), "nemit_profile_read")
+        if not with_rays:
+            return {k: (ms[i], int(cnt[i])) for i, k in enumerate(L.PROFILE_KINDS) if cnt[i]}
+        out = {k: (ms[i], int(cnt[i]), int(rays[i])) for i, k in enumerate(L.PROFILE_KINDS) if cnt[i]}
+        out["red_lane_ops"] = int(red.value)
+        return out
 
     def launch_count(self) -> int:
         return int(self.lib.nemit_launch_count(self._h))

@@ -28,6 +28,7 @@ class NemitConfig(C.Structure):
         ("disable_inside_aabb", C.c_int32), ("cpu_sum_width", C.c_int32),
         ("interlevel_mult", C.c_float), ("distortion_mult", C.c_float),
         ("lin0_host", c_float_p), ("u1_host", c_float_p), ("u2_host", c_float_p),
+        ("use_fake_contraction", C.c_int32), ("far_intersect", C.c_int32),
     ]
 
 
@@ -46,7 +47,8 @@ class NemitParams(C.Structure):
 class NemitRays(C.Structure):
     _fields_ = [("o", C.c_void_p), ("v", C.c_void_p), ("near_per_ray", C.c_void_p), ("near_scalar", C.c_float),
                 ("n", C.c_int64), ("camera_idx", C.c_int32), ("training", C.c_int32), ("jitter", C.c_void_p),
-                ("anneal", C.c_float), ("layout", C.c_int32)]
+                ("anneal", C.c_float), ("layout", C.c_int32),
+                ("kept_s_edges1", C.c_void_p), ("kept_s_edges2", C.c_void_p), ("kept_t_edges2", C.c_void_p)]
 
 
 class NemitLevelsOut(C.Structure):
@@ -130,8 +132,20 @@ SYMBOLS = {
     "nemit_launch_count": (C.c_int64, [_H]),
     "nemit_set_sampler": (C.c_int, [_H, C.c_int32]),
     "nemit_profile_enable": (C.c_int, [_H, C.c_int32]),
-    "nemit_profile_read": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_int32]),
+    "nemit_profile_read": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                     C.POINTER(C.c_int64), C.c_int32]),
+    "nemit_backward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_int32,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_backward_host_workspace_bytes": (C.c_size_t, [_H, C.c_int64]),
+    "nemit_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "nemit_comm_init": (C.c_int, [_H, C.c_void_p, C.c_int32, C.c_int32]),
+    "nemit_comm_destroy": (C.c_int, [_H]),
+    "nemit_allreduce_grads": (C.c_int, [_H, C.c_void_p, C.c_int64, C.c_float, C.c_void_p]),
+    "nemit_microbench": (C.c_int, [_H, C.c_int32, C.POINTER(C.c_double), C.c_void_p]),
 }
+
+MICROBENCH_KINDS = ["gather_l1miss", "gather_l1hit", "gather_coherent", "red", "l2_read"]
+UNIQUE_ID_BYTES = 128
 
 PROFILE_KINDS = ["k_sample_levels", "k_field_forward", "k_field_forward<adjoint_seed>", "k_field_backward",
                  "k_prop_backward", "k_finalize_ray_grads", "k_field_jvp", "k_field_forward_tc", "k_field_backward_tc"]

@@ -54,25 +54,29 @@ def _chunks(n: int, chunk: Optional[int]) -> int:
     return 1 if not chunk else (int(n) + int(chunk) - 1) // int(chunk)
 
 
-def emitter_primal(E: NerfEmitter, o3n, v3n, near=0.0, camera_idx=0, jitter=None):
-    """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> (N,3)."""
-    return E.render(o3n.contiguous(), v3n.contiguous(), near=_near_arg(near), camera_idx=camera_idx, jitter=jitter)
+def emitter_primal(E: NerfEmitter, o3n, v3n, near=0.0, camera_idx=0, jitter=None, keep_edges=False):
+    """NeRFEmitterOp.ns_render_ray (nerf_emitter_op.py:38-58): (3,N),(3,N) -> (N,3).
+    keep_edges: -> (rgb, kept) with the sample edges the adjoint of the same op instance re-uses instead of sampling again
+    (the reference re-derives the same samples: the generator state is restored between primal and adjoint,
+    NS/models/base_model.py:299,327-328)."""
+    return E.render(o3n.contiguous(), v3n.contiguous(), near=_near_arg(near), camera_idx=camera_idx, jitter=jitter,
+                    keep_edges=keep_edges)
 
 
-def emitter_jvp(E: NerfEmitter, o3n, v3n, grad_o3n, grad_v3n, near=0.0, camera_idx=0, jitter=None):
+def emitter_jvp(E: NerfEmitter, o3n, v3n, grad_o3n, grad_v3n, near=0.0, camera_idx=0, jitter=None, kept=None):
     """NeRFEmitterOp.ns_forward_ray (nerf_emitter_op.py:60-90): tangents (3,N) -> (N,3), NaN tangents zeroed."""
     return E.jvp(o3n.contiguous(), v3n.contiguous(), grad_o3n.contiguous(), grad_v3n.contiguous(),
-                 near=_near_arg(near), camera_idx=camera_idx, jitter=jitter)
+                 near=_near_arg(near), camera_idx=camera_idx, jitter=jitter, kept=kept)
 
 
 def emitter_vjp(E: NerfEmitter, o3n, v3n, grad_out_n3, near=0.0, camera_idx=0, jitter=None, chunk_rays=None,
-                loss_scale=1.0, proposal_requires_grad=True):
+                loss_scale=1.0, proposal_requires_grad=True, kept=None):
     """NeRFEmitterOp.ns_backward_ray (nerf_emitter_op.py:92-117): returns (o.grad, v.grad) as (3,N); parameter
     gradients are accumulated into the emitter's bound gradient buffers (the reference leaves them in
     ``param.grad``)."""
     return E.backward(o3n.contiguous(), v3n.contiguous(), grad_out_n3.contiguous(), near=_near_arg(near),
                       camera_idx=camera_idx, jitter=jitter, chunk_rays=chunk_rays, loss_scale=loss_scale,
-                      proposal_requires_grad=proposal_requires_grad)
+                      proposal_requires_grad=proposal_requires_grad, kept=kept)
 
 
 class NerfEmitterFunction(torch.autograd.Function):
@@ -85,14 +89,16 @@ class NerfEmitterFunction(torch.autograd.Function):
         ctx.sampler = sampler
         ctx.save_for_backward(o3n, v3n, dummy)
         consume_sampler_updates(sampler, _chunks(o3n.shape[1], chunk_rays))      # the no-grad primal chunks count too
-        return emitter_primal(E, o3n.detach(), v3n.detach(), near, camera_idx, jitter)
+        rgb, ctx.kept = emitter_primal(E, o3n.detach(), v3n.detach(), near, camera_idx, jitter, keep_edges=True)
+        return rgb
 
     @staticmethod
     def backward(ctx, grad_out):
         o3n, v3n, dummy = ctx.saved_tensors
         flags = consume_sampler_updates(ctx.sampler, _chunks(o3n.shape[1], ctx.chunk_rays))
         go, gv = emitter_vjp(ctx.E, o3n.detach(), v3n.detach(), grad_out, ctx.near, ctx.camera_idx, ctx.jitter,
-                             ctx.chunk_rays, proposal_requires_grad=flags)
+                             ctx.chunk_rays, proposal_requires_grad=flags, kept=ctx.kept)
+        ctx.kept = None
         gd = torch.zeros_like(dummy) if dummy is not None else None       # nerf_emitter_op.py:116
         return None, go, gv, gd, None, None, None, None, None
 
@@ -132,7 +138,7 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
                 self.o, self.v = o.torch(), v.torch()
                 state["jit"] = jitter_fn(self.o.shape[1]) if (jitter_fn is not None and E.training) else None
                 consume_sampler_updates(sampler, _chunks(self.o.shape[1], chunk_rays))
-                rgb = emitter_primal(E, self.o, self.v, near, camera_idx, state["jit"])
+                rgb, state["kept"] = emitter_primal(E, self.o, self.v, near, camera_idx, state["jit"], keep_edges=True)
                 guiding.train_primal(self.o.t(), self.v.t(), rgb, gw)
                 return type(o)(rgb.reshape(-1))
 
@@ -140,7 +146,7 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
                 go, gv, _ = self.grad_in("args")
                 consume_sampler_updates(sampler, _chunks(self.o.shape[1], forward_ad_chunk_rays))
                 t = emitter_jvp(E, self.o, self.v, go.torch().reshape(3, -1), gv.torch().reshape(3, -1), near,
-                                camera_idx, state["jit"])
+                                camera_idx, state["jit"], kept=state.get("kept"))
                 guiding.train_forward(self.o.t(), self.v.t(), t, gw)
                 self.set_grad_out(type(go)(t.reshape(-1)))
 
@@ -148,7 +154,7 @@ def make_nerf_emitter_op(E: NerfEmitter, path_guiding=None, jitter_fn=None, chun
                 g = self.grad_out().torch().reshape(-1, 3)
                 flags = consume_sampler_updates(sampler, _chunks(self.o.shape[1], chunk_rays))
                 go, gv = emitter_vjp(E, self.o, self.v, g, near, camera_idx, state["jit"], chunk_rays,
-                                     proposal_requires_grad=flags)
+                                     proposal_requires_grad=flags, kept=state.get("kept"))
                 guiding.train_backward(self.o.t(), self.v.t(), go.t(), gw)
                 T = type(self.grad_out())
                 self.set_grad_in("args", (T(go), T(gv), T(torch.zeros(1, device=go.device))))

@@ -38,8 +38,9 @@ def shard_range(total: int, rank: int, world_size: int) -> Tuple[int, int]:
 
 
 def allreduce_grads(flat_grads: torch.Tensor, group=None, scale: Optional[float] = None) -> torch.Tensor:
-    """Sum the flat parameter-gradient buffer over ranks (the one collective of the path).  ``scale`` folds the
-    GradScaler unscale (or a 1/world average) into the same pass over the buffer."""
+    """Sum a gradient buffer over ranks with torch.distributed (any backend).  The GPU path does NOT use this:
+    ``NerfEmitter.allreduce_grads`` goes through the library (nemit_allreduce_grads: NCCL with the scale folded into
+    the collective).  This torch-level twin serves host-side tests on the gloo backend and CPU tensors."""
     _, w = world()
     if w > 1:
         dist.all_reduce(flat_grads, op=dist.ReduceOp.SUM, group=group)

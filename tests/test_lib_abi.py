@@ -35,6 +35,62 @@ def test_struct_sizes_match_header(built):
     assert C.sizeof(built.NemitGrid) == 8 + 4 * 16
 
 
+def test_struct_layouts_match_a_c_compiler(built, tmp_path):
+    """sizeof / offsetof of every struct of include/nemit.h as gcc sees them vs the ctypes mirrors in lib.py."""
+    import ctypes as C
+    import subprocess
+    structs = {"NemitGrid": built.NemitGrid, "NemitConfig": built.NemitConfig, "NemitParams": built.NemitParams,
+               "NemitRays": built.NemitRays, "NemitLevelsOut": built.NemitLevelsOut, "NemitMlp": built.NemitMlp,
+               "NemitAdamGroup": built.NemitAdamGroup, "NemitSphericalSensor": built.NemitSphericalSensor,
+               "NemitVmfLobes": built.NemitVmfLobes}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "nemit.h"', 'int main(void) {']
+    for name, cls in structs.items():
+        lines.append('  printf("%s sizeof %%zu\\n", sizeof(%s));' % (name, name))
+        for field, _ in cls._fields_:
+            lines.append('  printf("%s %s %%zu\\n", offsetof(%s, %s));' % (name, field, name, field))
+    lines += ['  return 0;', '}']
+    src = tmp_path / "probe.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "probe"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout
+    seen = 0
+    for ln in out.splitlines():
+        name, field, val = ln.split()
+        cls = structs[name]
+        expect = C.sizeof(cls) if field == "sizeof" else getattr(cls, field).offset
+        assert int(val) == expect, (name, field, val, expect)
+        seen += 1
+    assert seen > 60
+
+
+def test_unsupported_model_variants_are_rejected_loudly(built):
+    """nemit_create must not silently evaluate the default model when the config asks for FakeContraction /
+    far_intersect (NS/models/nerfacto.py:144-154,263-270, NS/models/sdf_nerfacto.py:193-194)."""
+    import ctypes as C
+    import torch
+    from nerf_emitter_b200 import EmitterModelSpec
+    from nerf_emitter_b200.emitter import sampler_tables
+    lib = built.load()
+    spec = EmitterModelSpec()
+    tabs = sampler_tables(spec)
+    for flag in ("use_fake_contraction", "far_intersect"):
+        cfg = built.NemitConfig()
+        for g, dst in [(spec.main_grid, cfg.main_grid), (spec.prop_grids[0], cfg.prop_grid[0]), (spec.prop_grids[1], cfg.prop_grid[1])]:
+            dst.num_levels, dst.log2_table_size = g.num_levels, g.log2_hashmap_size
+        cfg.num_prop_samples[0], cfg.num_prop_samples[1] = spec.num_proposal_samples
+        cfg.num_nerf_samples = spec.num_nerf_samples
+        cfg.hidden_dim, cfg.geo_feat_dim, cfg.appearance_dim = spec.hidden_dim, spec.geo_feat_dim, spec.appearance_dim
+        cfg.prop_hidden_dim, cfg.num_images = spec.prop_hidden, spec.num_images
+        cfg.lin0_host = C.cast(tabs[0].data_ptr(), built.c_float_p)
+        cfg.u1_host = C.cast(tabs[1].data_ptr(), built.c_float_p)
+        cfg.u2_host = C.cast(tabs[2].data_ptr(), built.c_float_p)
+        setattr(cfg, flag, 1)
+        h = C.c_void_p()
+        assert lib.nemit_create(C.byref(cfg), 0, C.byref(h)) == -1
+        assert flag.encode() in lib.nemit_last_error()
+
+
 def test_argument_errors_without_gpu(built):
     import ctypes as C
     lib = built.load()
