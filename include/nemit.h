@@ -235,18 +235,28 @@ int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const float* rgb_w
  * (NS/engine/optimizers.py:122-137, called from NS/engine/trainer.py:517-537) for the two parameter groups of
  * NS/models/nerfacto.py:313-317 with the hyper-parameters of NS/configs/method_configs.py:331-342:
  * GradScaler.unscale_ (grad / grad_scale + non-finite check) -> clip_grad_norm_(group, max_norm) ->
- * clip_grad_value_(group, max_value) -> torch.optim.Adam step (skipped when a non-finite gradient was found),
- * in place on the borrowed tensors.  exp_avg / exp_avg_sq: Adam state in the parameter layouts (caller-owned,
- * zero-initialised); step: 1-based step count of this update; lr: the scheduler's current value
- * (NS/engine/schedulers.py:156-193); max_norm / max_value <= 0 disable the clip; zero_grads != 0 clears the
- * gradients in the same pass (optimizer.zero_grad).  stats_or_null: device float[4] = {sum g^2 fields,
- * sum g^2 proposal_networks, non-finite flag, 0} for GradScaler.update / logging. */
+ * clip_grad_value_(group, max_value) -> torch.optim.Adam step, in place on the borrowed tensors, PER GROUP as the
+ * reference does it (one optimizer and one found_inf record per group):
+ *   - a group with enabled == 0 is left untouched - parameters, moments and step count - which is what the reference does
+ *     for an optimizer none of whose parameters has a .grad (optimizers.py:136: the proposal networks on every call
+ *     whose backward chunks ran without proposal_requires_grad);
+ *   - a group whose unscaled gradients contain a non-finite value skips ITS step only (GradScaler keeps found_inf per
+ *     optimizer) and its step count does not advance (torch Adam's `step` only moves when optimizer.step() runs), so the
+ *     bias corrections stay in sync after an overflow.
+ * exp_avg / exp_avg_sq: Adam state in the parameter layouts (caller-owned, zero-initialised); step_state: DEVICE
+ * int64[2] (caller-owned, zero-initialised) = applied steps of {fields, proposal_networks}, read and advanced on the
+ * device so that a skipped step needs no host synchronisation; lr: the scheduler's current value
+ * (NS/engine/schedulers.py:156-193); max_norm / max_value <= 0 disable the clip; zero_grads != 0 clears every gradient
+ * in the same pass (optimizer.zero_grad).  stats_or_null: device float[4] = {sum g^2 fields, sum g^2 proposal_networks,
+ * non-finite flag fields, non-finite flag proposal_networks} for GradScaler.update / logging. */
 typedef struct NemitAdamGroup {
   double lr, beta1, beta2, eps;   /* python floats in torch.optim.Adam: 1 - beta is formed in double, as torch does */
   float max_norm, max_value;
+  int32_t enabled;                /* 0: no parameter of the group has a gradient on this call */
+  int32_t reserved;
 } NemitAdamGroup;
 int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const NemitParams* exp_avg_sq,
-                    const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t step,
+                    const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t* step_state,
                     float grad_scale, int32_t zero_grads, float* stats_or_null, void* stream);
 
 /* Headless spherical-sensor bake of the emitter radiance (BASELINE config 5): SphericalCamera.sample_ray

@@ -883,12 +883,12 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
 // optimizer step (optim.cu)
 // ---------------------------------------------------------------------------------------------
 extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const NemitParams* exp_avg_sq,
-                               const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t step,
+                               const NemitAdamGroup* fields, const NemitAdamGroup* proposal_networks, int64_t* step_state,
                                float grad_scale, int32_t zero_grads, float* stats_or_null, void* stream) {
-  if (!h || !exp_avg || !exp_avg_sq || !fields || !proposal_networks) return fail(NEMIT_E_INVALID, "nemit_adam_step: null argument%s");
+  if (!h || !exp_avg || !exp_avg_sq || !fields || !proposal_networks || !step_state) return fail(NEMIT_E_INVALID, "nemit_adam_step: null argument%s");
   if (!h->params_bound || !h->grads_bound) return fail(NEMIT_E_UNBOUND, "nemit_adam_step: parameters and gradients must be bound%s");
   if (!params_complete(exp_avg) || !params_complete(exp_avg_sq)) return fail(NEMIT_E_INVALID, "nemit_adam_step: an optimizer-state pointer is null%s");
-  if (step < 1) return fail(NEMIT_E_INVALID, "nemit_adam_step: step counts from 1%s");
+  if ((uintptr_t)step_state & 7) return fail(NEMIT_E_INVALID, "nemit_adam_step: step_state must be an 8-byte aligned device int64[2]%s");
   if (!(grad_scale > 0.f)) return fail(NEMIT_E_INVALID, "nemit_adam_step: grad_scale must be > 0%s");
   DeviceGuard guard(h->device);
   const NemitConfig& c = h->cfg;
@@ -928,17 +928,17 @@ extern "C" int nemit_adam_step(NemitHandle* h, const NemitParams* exp_avg, const
     OptimGroup& d = A.grp[g];
     d.beta1 = (float)s.beta1; d.beta2 = (float)s.beta2; d.eps = (float)s.eps; d.max_norm = s.max_norm; d.max_value = s.max_value;
     d.omb1 = (float)(1.0 - s.beta1); d.omb2 = (float)(1.0 - s.beta2);
-    const double bc1 = 1.0 - pow(s.beta1, (double)step), bc2 = 1.0 - pow(s.beta2, (double)step);
-    d.step_size = (float)(s.lr / bc1);
-    d.bc2_sqrt = (float)sqrt(bc2);
+    d.lr = s.lr; d.beta1_d = s.beta1; d.beta2_d = s.beta2;
+    d.enabled = s.enabled != 0;
   }
+  A.step_state = reinterpret_cast<long long*>(step_state);
   A.inv_scale = 1.f / grad_scale;
   A.zero_grads = zero_grads;
   A.stats = h->opt_stats;
   A.stats_out = stats_or_null;
   cudaError_t e = launch_adam_step(A, (cudaStream_t)stream);
   if (e != cudaSuccess) return cuda_fail(e, "k_adam_step");
-  h->launches += 2;
+  h->launches += 3;
   return NEMIT_OK;
 }
 

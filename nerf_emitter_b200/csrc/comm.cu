@@ -126,8 +126,10 @@ extern "C" int nemit_allreduce_grads(NemitHandle* h, float* flat_grads, int64_t 
   if (count == 0) return NEMIT_OK;
   DeviceGuard guard(h->device);
   cudaStream_t st = (cudaStream_t)stream;
-  if (!h->nccl_comm) {
-    // single rank: the sum is the identity, only the scale remains
+  if (!h->nccl_comm || h->comm_world == 1) {
+    // single rank: the sum is the identity, only the scale remains.  (A one-rank NCCL communicator is not used for it:
+    // NCCL 2.28.9's in-place PreMulSum all-reduce on ONE rank leaves a tail of count % 4 elements unscaled - seen on
+    // B200, tools/diag_round2.py; with two or more ranks the collective kernels run and the tail is handled.)
     if (scale != 1.f) {
       if ((uintptr_t)flat_grads & 15) return nemit_fail(NEMIT_E_INVALID, "nemit_allreduce_grads: the gradient blob must be 16-byte aligned%s");
       k_scale_inplace<<<148 * 8, 256, 0, st>>>(flat_grads, count, scale);

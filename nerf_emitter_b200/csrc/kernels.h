@@ -158,8 +158,8 @@ constexpr int kOptMaxTensors = 24;
 struct OptimGroup {
   float beta1, beta2, eps, max_norm, max_value;
   float omb1, omb2;     // (float)(1 - beta) with the subtraction in double, like torch's python-float arithmetic
-  float step_size;      // lr / (1 - beta1^step)
-  float bc2_sqrt;       // sqrt(1 - beta2^step)
+  double lr, beta1_d, beta2_d;   // bias corrections are formed on the device from the group's own applied-step count
+  int enabled;          // 0: the group has no gradients on this call (left untouched)
 };
 struct OptimArgs {
   int num_tensors;
@@ -173,8 +173,9 @@ struct OptimArgs {
   OptimGroup grp[2];
   float inv_scale;                     // 1 / GradScaler scale
   int zero_grads;
-  double* stats;                       // device scratch (4): sum g^2 per group, non-finite flag, pad
+  double* stats;                       // device scratch (4): sum g^2 per group, non-finite flag per group
   float* stats_out;                    // optional user copy as float[4]
+  long long* step_state;               // device int64[2]: applied steps per group (advanced by k_adam_finish)
 };
 cudaError_t launch_adam_step(OptimArgs& A, cudaStream_t stream);
 

@@ -366,6 +366,7 @@ class NerfEmitter:
         ``updated`` flag (ray_samplers.py:598): one bool for the whole call, or one bool per chunk of ``chunk_rays``
         rays (the reference evaluates it per sampler call, i.e. per chunk; runs of equal flags go to the library
         together, the regulariser means being per chunk either way)."""
+        kept = self._usable_kept(kept)       # the edges render(..., keep_edges=True) returned, if the mode is unchanged
         if not self.grads:
             self.bind_grads()
         n = o3n.shape[0] if nerf_layout else o3n.shape[1]

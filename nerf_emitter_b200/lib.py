@@ -67,7 +67,8 @@ class NemitMlp(C.Structure):
 
 
 class NemitAdamGroup(C.Structure):
-    _fields_ = [(n, C.c_double) for n in ["lr", "beta1", "beta2", "eps"]] + [("max_norm", C.c_float), ("max_value", C.c_float)]
+    _fields_ = [(n, C.c_double) for n in ["lr", "beta1", "beta2", "eps"]] + [("max_norm", C.c_float), ("max_value", C.c_float),
+                                                                              ("enabled", C.c_int32), ("reserved", C.c_int32)]
 
 
 class NemitSphericalSensor(C.Structure):
@@ -106,7 +107,7 @@ SYMBOLS = {
     "nemit_point_lights": (C.c_int, [_H, C.POINTER(NemitRays), C.POINTER(C.c_float), C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_adam_step": (C.c_int, [_H, C.POINTER(NemitParams), C.POINTER(NemitParams), C.POINTER(NemitAdamGroup),
-                                  C.POINTER(NemitAdamGroup), C.c_int64, C.c_float, C.c_int32, C.c_void_p, C.c_void_p]),
+                                  C.POINTER(NemitAdamGroup), C.c_void_p, C.c_float, C.c_int32, C.c_void_p, C.c_void_p]),
     "nemit_spherical_rays": (C.c_int, [C.POINTER(NemitSphericalSensor), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "nemit_film_accumulate": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_int64,

@@ -27,16 +27,27 @@ class OracleOptimizers:
         for pg in self.opt[group].param_groups:
             pg["lr"] = lr
 
-    def step(self, grads: Dict[str, torch.Tensor], grad_scale: float = 1.0) -> bool:
-        """Returns True when the step was taken (no non-finite gradient)."""
-        for k, p in self.params.items():
-            p.grad = grads[k].detach().clone().float() / grad_scale          # unscale_
-        finite = all(bool(torch.isfinite(p.grad).all()) for p in self.params.values())
+    def step(self, grads: Dict[str, torch.Tensor], grad_scale: float = 1.0, has_grads=None) -> Dict[str, bool]:
+        """One optimizer_scaler_step_all.  ``has_grads`` = {group: bool}: a group none of whose parameters has a .grad is
+        not stepped at all (optimizers.py:136).  Returns {group: stepped}: GradScaler keeps found_inf PER OPTIMIZER
+        (torch/amp/grad_scaler.py, _per_optimizer_states), so a non-finite gradient skips only the step of its own group."""
+        has_grads = has_grads or {}
+        stepped = {}
         for g, ps in self.groups.items():
+            if not has_grads.get(g, True):
+                for p in ps:
+                    p.grad = None
+                stepped[g] = False
+                continue
+            for k, p in self.params.items():
+                if group_of(k) == g:
+                    p.grad = grads[k].detach().clone().float() / grad_scale          # unscale_
+            finite = all(bool(torch.isfinite(p.grad).all()) for p in ps)
             if self.max_norm is not None:
                 torch.nn.utils.clip_grad_norm_(ps, self.max_norm)
             if self.max_value is not None:
                 torch.nn.utils.clip_grad_value_(ps, self.max_value)
             if finite:                                                       # GradScaler.step
                 self.opt[g].step()
-        return finite
+            stepped[g] = finite
+        return stepped

@@ -43,7 +43,7 @@ def test_adam_step_matches_torch(grad_mag, grad_scale, spec, params_factory):
         for grp in ("fields", "proposal_networks"):
             ref.set_lr(grp, opt.lr(grp))
         opt.optimizer_scaler_step_all(grad_scale, zero_grads=True)
-        assert ref.step(G, grad_scale)
+        assert all(ref.step(G, grad_scale).values())
         opt.scheduler_step_all()
         assert not opt.found_inf()
         assert float(E.flat_grads.abs().sum()) == 0.0                       # zero_grad fused into the step
@@ -55,6 +55,54 @@ def test_adam_step_matches_torch(grad_mag, grad_scale, spec, params_factory):
     # the parameters really moved, by about lr per touched entry
     d = (E.params["field.mlp_head.layers.1.weight"].cpu() - P["field.mlp_head.layers.1.weight"]).abs().max()
     assert 1e-3 < float(d) < 0.1
+    assert opt.step_count == (3, 3)
+
+
+def _compare(E, opt, ref, tag):
+    for k, p in ref.params.items():
+        assert rel_err(E.params[k].cpu(), p.detach(), floor=1e-2) < 1e-5, (tag, k)
+        st = ref.opt["proposal_networks" if k.startswith("proposal_networks.") else "fields"].state.get(p)
+        if not st:
+            assert float(opt.state["exp_avg"][k].abs().max()) == 0.0, (tag, k, "moments of a never-stepped group")
+            continue
+        assert rel_err(opt.state["exp_avg"][k].cpu(), st["exp_avg"], floor=1e-30) < 1e-4, (tag, k)
+        assert rel_err(opt.state["exp_avg_sq"][k].cpu(), st["exp_avg_sq"], floor=1e-30) < 1e-4, (tag, k)
+
+
+@gpu
+def test_group_without_gradients_and_skipped_steps_match_torch(spec, params_factory):
+    """(a) with proposal_update_every = 1 the proposal networks have no gradient on every other iteration and
+    the reference does not step their optimizer then (optimizers.py:136): parameters, moments and step count stay;
+    (b) found_inf is per optimizer: an inf in the fields' gradients skips the fields' step only; (c) a skipped step does
+    not advance Adam's step count, so the bias corrections of the following steps agree with torch."""
+    from nerf_emitter_b200 import NerfEmitter
+    from nerf_emitter_b200.optim import EmitterOptimizers
+    from oracle.optim_oracle import OracleOptimizers
+    P = params_factory(0, 1e3)
+    E = NerfEmitter({k: v.clone() for k, v in P.items()}, spec, device=torch.device(DEV))
+    E.bind_grads()
+    opt = EmitterOptimizers(E)
+    ref = OracleOptimizers(P)
+    #        proposal grads?  inf in fields?
+    plan = [(True, False), (False, False), (True, True), (False, False), (True, False)]
+    want_steps = [0, 0]
+    for it, (prop, poison) in enumerate(plan):
+        G = _grads(P, 200 + it, 1e-3 * 128.0)
+        if poison:
+            G["field.mlp_head.layers.0.bias"][3] = float("inf")
+        for k, g in G.items():
+            E.grads[k].copy_(g if (prop or not k.startswith("proposal_networks.")) else torch.zeros_like(g))
+        for grp in ("fields", "proposal_networks"):
+            ref.set_lr(grp, opt.lr(grp))
+        opt.optimizer_scaler_step_all(128.0, zero_grads=True, proposal_has_grads=prop)
+        stepped = ref.step(G, 128.0, has_grads={"proposal_networks": prop})
+        assert stepped == {"fields": not poison, "proposal_networks": prop}
+        assert opt.found_inf("fields") == poison and not opt.found_inf("proposal_networks")
+        want_steps[0] += int(not poison)
+        want_steps[1] += int(prop)
+        assert opt.step_count == tuple(want_steps), (it, opt.step_count, want_steps)
+        opt.scheduler_step_all()
+        _compare(E, opt, ref, "iteration %d" % it)
 
 
 @gpu
@@ -67,11 +115,13 @@ def test_non_finite_gradient_skips_the_step(spec, params_factory):
     opt = EmitterOptimizers(E)
     E.flat_grads.fill_(1e-3)
     E.grads["field.mlp_head.layers.0.bias"][3] = float("inf")
+    E.grads["proposal_networks.0.mlp_base.1.layers.0.bias"][1] = float("nan")
     opt.optimizer_scaler_step_all(65536.0, zero_grads=False)
-    assert opt.found_inf()
+    assert opt.found_inf() and opt.found_inf("fields") and opt.found_inf("proposal_networks")
     for k, p in P.items():
         assert torch.equal(E.params[k].cpu(), p), k                          # GradScaler.step skipped optimizer.step
     assert float(opt.state["exp_avg_flat"].abs().sum()) == 0.0
+    assert opt.step_count == (0, 0)
     E.zero_grads()
     E.flat_grads.fill_(1e-3)
     opt.optimizer_scaler_step_all(1.0)
@@ -82,6 +132,30 @@ def test_non_finite_gradient_skips_the_step(spec, params_factory):
 # multipliers printed by the reference's own ExponentialDecayStepScheduler (NS/engine/schedulers.py:156-193) in the build
 # container with the sdf-nerfacto settings (lr 1e-2 -> 1e-4 over 20000 steps, step_pretrain 5000, lr_lambda 0.01)
 SCHEDULE_GOLDEN = {0: 1.0000000000000004, 1: 0.9997697679981569, 4998: 0.31637342782213834, 4999: 0.0031630058853452077, 5000: 0.0031622776601683824, 10000: 0.0010000000000000002, 19999: 0.00010002302850208257, 20000: 0.00010000000000000009, 30000: 0.00010000000000000009}
+
+
+def test_default_config_is_the_reference_sdf_nerfacto_schedule():
+    """EmitterOptimizers() must train at the reference's learning rate - 1e-2 decayed, cut 100x once Mitsuba
+    takes over after PRETRAIN_ITER = 2000 steps (NS/configs/method_configs.py:288,331-342)."""
+    from nerf_emitter_b200.optim import PRETRAIN_ITER, sdf_nerfacto_optimizers
+    from oracle.ref_import import reference_available
+    cfg = sdf_nerfacto_optimizers()
+    assert PRETRAIN_ITER == 2000
+    for g in ("fields", "proposal_networks"):
+        o, s = cfg[g]["optimizer"], cfg[g]["scheduler"]
+        assert (o.lr, o.eps, o.max_norm, o.max_value) == (1e-2, 1e-15, 0.1, 0.1)
+        assert (s.lr_final, s.max_steps, s.step_pretrain, s.lr_lambda) == (1e-4, 20000, 2000, 0.01)
+        assert s.multiplier(1997, 1e-2) > 0.6 and s.multiplier(1999, 1e-2) < 0.0065      # the cut arrives at step + 1 >= 2000
+    if reference_available():
+        from oracle.ref_import import import_reference
+        import_reference()
+        import nerfstudio.engine.schedulers as S
+        rc = S.ExponentialDecayStepSchedulerConfig(lr_final=1e-4, max_steps=20000, step_pretrain=2000, lr_lambda=.01)
+        opt = torch.optim.Adam([torch.nn.Parameter(torch.zeros(1))], lr=1e-2)
+        f = S.ExponentialDecayStepScheduler(rc).get_scheduler(opt, 1e-2).lr_lambdas[0]
+        s = cfg["fields"]["scheduler"]
+        for step in [0, 1, 1998, 1999, 2000, 2319, 5000, 19999, 20000]:
+            assert s.multiplier(step, 1e-2) == pytest.approx(f(step), rel=1e-12), step
 
 
 def test_schedule_matches_reference():

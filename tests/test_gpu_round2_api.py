@@ -110,8 +110,9 @@ def test_allreduce_single_rank_applies_the_scale(E):
     E.zero_grads()
 
 
-def test_nccl_comm_of_one_rank_premul_sum(E):
-    """The library's own communicator (ncclCommInitRank through dlopen) with world size 1: the PreMulSum path."""
+def test_nccl_comm_of_one_rank(E):
+    """The library's own communicator (ncclGetUniqueId / ncclCommInitRank through dlopen) with world size 1; the scaled
+    sum of one rank is served by the library's own pass (see comm.cu), odd element count included."""
     from nerf_emitter_b200 import lib as L
     ident = (C.c_ubyte * L.UNIQUE_ID_BYTES)()
     L.check(E.lib.nemit_comm_unique_id(ident), "nemit_comm_unique_id")

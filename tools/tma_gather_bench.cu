@@ -57,7 +57,10 @@ k_gather(const __grid_constant__ CUtensorMap tmap, const float4* __restrict__ ta
     }
     if (MODE & 2) {
 #pragma unroll
-      for (int j = 4; j < 8; ++j) { const float4 v = __ldg(table + r[j]); acc += v.x + v.w; }
+      for (int j = 4; j < 8; ++j) {      // all four components used: one LDG.128 per row (two of them would turn into two LDG.32)
+        const float4 v = __ldg(table + r[j]);
+        acc += (v.x + v.y) + (v.z + v.w);
+      }
     }
     if (MODE & 1) {
       uint32_t spins = 0;
