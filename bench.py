@@ -389,6 +389,16 @@ def sharded_backward_check(E, rank, world, dist, dev):
                "max_rel_err": worst, "worst_tensor": worst_name, "tolerance": 1e-5, "ok": bool(worst <= 1e-5),
                "what": "rank-sharded nemit_backward + nemit_allreduce_grads vs rank 0 recomputing all shards alone, "
                        "max-norm relative error over every gradient tensor"}
+    # the folded scale of the collective (ncclRedOpCreatePreMulSum) on an odd-length blob vs torch.distributed + multiply
+    x = (torch.arange(100003, device=dev, dtype=torch.float32) % 977) + rank
+    y = x.clone()
+    E.allreduce_blob(x, scale=0.5)
+    dist.all_reduce(y)
+    y *= 0.5
+    torch.cuda.synchronize()
+    if out is not None:
+        out["premul_allreduce_max_rel_err"] = float((x - y).abs().max() / y.abs().max())
+        out["ok"] = bool(out["ok"] and out["premul_allreduce_max_rel_err"] <= 1e-6)
     E.zero_grads()
     E.set_precision(prec).set_sampler(samp)
     return out
