@@ -26,6 +26,21 @@
 //   scatter  : d enc (TMEM) -> red.add on the gradient table (x-neighbour corners that share an aligned 16-byte pair
 //              go out as one red.v4.f32), d enc . Jacobian -> d/d(position) -> per-ray sums.  This phase is bound by
 //              the SM's reduction issue rate (1.5 cycles per lane, tools/red_bench.cu).
+// Warp specialisation (round 2): the table scatter does not run on the compute halves any more.  A half parks the tile's
+// d-encoding rows and sample positions in shared memory (one column per sample) and signals an mbarrier; a separate
+// warpgroup of four scatter warps (one thread per parked sample, 96 registers each after setmaxnreg.dec) drains them into
+// red.global.add while the MMA chains run, serving the two halves alternately so that a full slot is always waiting, and
+// hands the slot back through a second mbarrier.  The compute halves (setmaxnreg.inc) only ever wait for their own
+// commit groups and for a free slot.
+// What bounds the scatter (measured, tools/red_bench.cu SM sweep, profiles/r2_red_bench.txt): red.global.add is limited
+// CHIP-WIDE - 184 G lane-ops/s whether 18 or 148 SMs issue them, whatever the width up to 16 bytes - i.e. by the L2
+// atomic units, not by the SM's issue rate as round 1 assumed.  So the only lever is the NUMBER of lane-ops:
+//   * x-neighbour corners of an aligned pair go out as one red.v4.f32 (round 1),
+//   * consecutive samples of a ray that fall into the same grid cell (coarse levels everywhere, all levels where the
+//     sampler has concentrated the samples) are summed across the lanes of a scatter warp with a segmented shuffle scan
+//     and issued once by the last lane of the run,
+//   * the six per-ray sums d/d(origin, direction) are reduced over the samples of a ray inside the warp before the
+//     atomics (32 x 6 lane-ops per warp -> 6 or 12).
 // Gradient operands are fp16 as in the reference's autocast path (torch.cuda.amp, NS/pipelines/mitsuba_sdf.py:
 // 1177,1193): the seed pass records max |seed| of the launch, the seeds are multiplied by the power of two that
 // brings that maximum to 16, and every result is divided by it again (exact), so the fp16 range is used without
@@ -55,9 +70,23 @@ constexpr uint32_t kColBB1 = 232;   // d base_b1   [*][n]   64 x 16 (64 identica
 constexpr uint32_t kColBH2 = 248;   // d head_b2   [*][n]   64 x 8
 constexpr uint32_t kHalfCols = 256;
 #ifndef NEMIT_SCATTER_UNROLL
-#define NEMIT_SCATTER_UNROLL 1
+#define NEMIT_SCATTER_UNROLL 2
 #endif
 constexpr int kScatterUnroll = NEMIT_SCATTER_UNROLL;
+// scatter warps: 128 threads = one sample of the parked tile each; they serve the two compute halves alternately
+constexpr int kScatterThreads = 128;
+constexpr int kComputeThreads = 256;
+constexpr int kBwdThreads = kComputeThreads + kScatterThreads;
+// register split: the CTA is launched with 168 registers per thread (65536 / 384 rounded down to a multiple of 8), i.e. a
+// pool of 64512; the scatter warpgroup shrinks and the two compute warpgroups grow out of what it released (setmaxnreg).
+// The split must fit the POOL, not the register file: a setmaxnreg.inc that cannot be served blocks for ever.
+constexpr int kLaunchRegs = 168;
+constexpr int kComputeRegs = 200;
+constexpr int kScatterRegs = 104;
+static_assert(kComputeThreads * kComputeRegs + kScatterThreads * kScatterRegs <= kBwdThreads * kLaunchRegs, "register pool of the CTA");
+#ifndef NEMIT_BWD_AGGREGATE
+#define NEMIT_BWD_AGGREGATE 1          // sum the contributions of runs of lanes that fall into the same grid cell before the red
+#endif
 
 struct BwdTcCommon {
   alignas(128) uint8_t b1[64 * 32 * 2];   // base layer 0   (64 x 32)   forward K-major layout, rows = outputs
@@ -77,10 +106,12 @@ struct BwdTcHalf {
   alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
   alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
   float dvec[64];
-  float denc[32 * 128];                   // d encoding of the PREVIOUS tile, [column][thread] (deferred scatter)
-  float pbuf[3 * 128];                    // its normalised sample positions, [axis][thread]
+  float denc[32 * 128];                   // d encoding of the tile handed to the scatter warps, [column][sample]
+  float pbuf[3 * 128];                    // its normalised sample positions, [axis][sample]
   alignas(8) uint64_t mbar;               // MMA commit groups
   alignas(8) uint64_t ld_bar;             // bulk copies of one tile (65536 bytes per phase)
+  alignas(8) uint64_t full_bar;           // 128 compute threads arrive: denc / pbuf of a tile are parked
+  alignas(8) uint64_t empty_bar;          // the half's scatter threads arrive: the slot may be overwritten
 };
 struct BwdTcSmem {
   BwdTcCommon c;
@@ -92,10 +123,13 @@ __device__ __forceinline__ void half_sync(int half) {
   asm volatile("bar.sync %0, 128;" ::"r"(half + 1) : "memory");
 }
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
+}
+
 // make the half's operand writes visible to the tensor core, let its thread 0 issue one commit group, wait for it
-// - `between` runs on all threads while the commit group is in flight (a slice of the previous tile's table scatter)
-template <class F, class G>
-__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue, G&& between) {
+template <class F>
+__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
   half_sync(half);
@@ -104,44 +138,81 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
     issue();
     tc::mma_commit(&H->mbar);
   }
-  between();
   tc::mbar_wait(&H->mbar, phase);
   phase ^= 1u;
   tc::tc_fence_after();
 }
 
-// Table scatter of levels [LB, LE) for the sample this thread owned in the half's PREVIOUS tile (d encoding and position
-// parked in shared memory, one private column per thread).  An all-zero gradient pair (also: invalid rows, first tile)
-// is skipped.  Corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices
-// differ in bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
-template <int LB, int LE>
-__device__ __forceinline__ void scatter_levels(const BwdTcHalf* H, int t, const ModelDev& M, float2* table, float gscale,
-                                               uint32_t& nred) {
-  if (!table) return;                     // ray-gradient-only pass (nemit_point_lights): no parameter gradients
-  const float p[3] = {H->pbuf[t], H->pbuf[128 + t], H->pbuf[256 + t]};
-#pragma unroll kScatterUnroll
-  for (int l = LB; l < LE; ++l) {
-    const float gx = H->denc[(2 * l) * 128 + t], gy = H->denc[(2 * l + 1) * 128 + t];
-    if (gx == 0.f && gy == 0.f) continue;
+// Table scatter of one parked tile, all 16 levels: run by the four scatter warps, thread = sample `smp` of the tile
+// (so a warp holds 32 consecutive samples, i.e. runs of consecutive samples of a ray).  Per level:
+//   * an all-zero gradient pair (also: invalid rows) contributes nothing;
+//   * lanes whose samples fall into the SAME grid cell (equal integer cell coordinates => equal 8 table indices) form a
+//     run; the 16 corner contributions are summed over the run with a segmented shuffle scan and the last lane issues them;
+//   * corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices differ in
+//     bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
+__device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int lane, const ModelDev& M, float2* table,
+                                             float gscale, uint32_t& nred) {
+  const float p[3] = {H->pbuf[smp], H->pbuf[128 + smp], H->pbuf[256 + smp]};
+#ifndef NEMIT_BWD_SCATTER_FROM
+#define NEMIT_BWD_SCATTER_FROM 0       // experiments only: first level that is scattered
+#endif
+#ifndef NEMIT_BWD_SCATTER_TO
+#define NEMIT_BWD_SCATTER_TO 16        // experiments only: one past the last level that is scattered
+#endif
+#pragma unroll 1
+  for (int l = NEMIT_BWD_SCATTER_FROM; l < NEMIT_BWD_SCATTER_TO; ++l) {
+    const float gx = H->denc[(2 * l) * 128 + smp], gy = H->denc[(2 * l + 1) * 128 + smp];
+    const bool act = gx != 0.f || gy != 0.f;
+    if (!__any_sync(0xffffffffu, act)) continue;
     LevelCell cell;
     const float sc = M.main_grid.scal[l];
     level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)l * M.main_grid.table_size, cell);
     float cw[8];
     corner_weights(cell, cw);
     const float gxs = gx * gscale, gys = gy * gscale;
-    const float xs = mul_rn(p[0], sc);
-    const bool pair = ((((int)floorf(xs)) & 1) == 0) && (cell.idx[0] != cell.idx[1]);
+    const int x0 = (int)floorf(mul_rn(p[0], sc));
+    const bool pair = ((x0 & 1) == 0) && (cell.idx[0] != cell.idx[1]);
+    float w[16];                         // (corner c, feature f) -> w[2c + f]
+#pragma unroll
+    for (int c = 0; c < 8; ++c) { w[2 * c] = cw[c] * gxs; w[2 * c + 1] = cw[c] * gys; }
+    bool issue = act;
+#if NEMIT_BWD_AGGREGATE
+    {
+      // cell key: the integer cell coordinates (resolutions <= 2048: 11 bits each); inactive lanes get a key of their own
+      const int y0 = (int)floorf(mul_rn(p[1], sc)), z0 = (int)floorf(mul_rn(p[2], sc));
+      const uint32_t key = act ? ((uint32_t)x0 | ((uint32_t)y0 << 11) | ((uint32_t)z0 << 22)) : (0xffffffe0u | (uint32_t)lane);
+      const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+      const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || key != prev);
+      if (heads != 0xffffffffu) {        // at least one run of two or more lanes in this warp
+        const int start = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));      // first lane of my run
+        const bool tail = lane == 31 || ((heads >> (lane + 1)) & 1u);
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const bool take = lane - d >= start;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const float up = __shfl_up_sync(0xffffffffu, w[i], d);
+            if (take) w[i] += up;
+          }
+        }
+        issue = act && tail;             // every lane of a multi-lane run is active; the last one holds the run's sums
+      }
+    }
+#endif
+    if (!issue) continue;
     nred += pair ? 4u : 8u;
     if (pair) {
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const uint32_t ia = cell.idx[2 * q], ib = cell.idx[2 * q + 1];
-        const float wa = (ia & 1u) ? cw[2 * q + 1] : cw[2 * q], wb = (ia & 1u) ? cw[2 * q] : cw[2 * q + 1];
-        atomicAdd(reinterpret_cast<float4*>(table + (ia < ib ? ia : ib)), make_float4(wa * gxs, wa * gys, wb * gxs, wb * gys));
+        const bool odd = ia & 1u;        // the ceil-x corner sits at the odd entry of the pair
+        const float ax = odd ? w[4 * q + 2] : w[4 * q], ay = odd ? w[4 * q + 3] : w[4 * q + 1];
+        const float bx = odd ? w[4 * q] : w[4 * q + 2], by = odd ? w[4 * q + 1] : w[4 * q + 3];
+        atomicAdd(reinterpret_cast<float4*>(table + (ia < ib ? ia : ib)), make_float4(ax, ay, bx, by));
       }
     } else {
 #pragma unroll
-      for (int c = 0; c < 8; ++c) atomic_add_f2(table + cell.idx[c], make_float2(cw[c] * gxs, cw[c] * gys));
+      for (int c = 0; c < 8; ++c) atomic_add_f2(table + cell.idx[c], make_float2(w[2 * c], w[2 * c + 1]));
     }
   }
 }
@@ -175,27 +246,34 @@ __device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int
 
 }  // namespace
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(kBwdThreads, 1)
 k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldBwdArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   BwdTcSmem* sm = reinterpret_cast<BwdTcSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
-  const int tid = threadIdx.x, half = tid >> 7, t = tid & 127, lane = tid & 31, wq = (tid >> 5) & 3;
+  const int tid = threadIdx.x, lane = tid & 31, wq = (tid >> 5) & 3;
+  // roles: threads [0, 256) = two compute halves of 128 (thread t = sample row t of the half's tile);
+  //        threads [256, 384) = four scatter warps (thread t = sample t of whichever half's parked tile is being drained)
+  const bool is_scatter = tid >= kComputeThreads;
+  const int half = is_scatter ? 0 : tid >> 7;
+  const int t = tid & 127;
   BwdTcCommon* C = &sm->c;
   BwdTcHalf* H = &sm->h[half];
 
   // ---- one-time setup ------------------------------------------------------------------------------
-  tc::stage_weight<64, 32>(C->b1, A.P.base_w0, 64, 32, 32, tid, 256);
-  tc::stage_weight<16, 64>(C->b2, A.P.base_w1, 16, 64, 64, tid, 256);
-  tc::stage_weight<64, 32>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, 256);
-  tc::stage_weight<64, 64>(C->b4, A.P.head_w1, 64, 64, 64, tid, 256);
-  tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, 256);
-  for (int i = tid; i < 8 * 128; i += 256) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
-  for (int i = tid; i < kApp; i += 256) {
+  tc::stage_weight<64, 32>(C->b1, A.P.base_w0, 64, 32, 32, tid, kBwdThreads);
+  tc::stage_weight<16, 64>(C->b2, A.P.base_w1, 16, 64, 64, tid, kBwdThreads);
+  tc::stage_weight<64, 32>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, kBwdThreads);
+  tc::stage_weight<64, 64>(C->b4, A.P.head_w1, 64, 64, 64, tid, kBwdThreads);
+  tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, kBwdThreads);
+  for (int i = tid; i < 8 * 128; i += kBwdThreads) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
+  for (int i = tid; i < kApp; i += kBwdThreads) {
     C->app[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
-  if (t == 0) {
+  if (!is_scatter && t == 0) {
     tc::mbar_init(&H->mbar, 1);
     tc::mbar_init(&H->ld_bar, 1);
+    tc::mbar_init(&H->full_bar, 128);
+    tc::mbar_init(&H->empty_bar, kScatterThreads);
     tc::fence_mbar_init();
   }
   if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
@@ -226,13 +304,37 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   const int64_t n_samples = A.n * kS2;
   const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
   const int64_t tile_stride = (int64_t)gridDim.x * 2;
+  const float gscale = invS * A.loss_scale;
+
+  if (is_scatter) {
+    // ---- scatter warps: drain the half's parked tiles into the gradient table ------------------------------------
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kScatterRegs));
+    uint32_t nred = 0;               // reduction lane-ops this thread issued (reported when profiling)
+    uint32_t j = 0;
+    // half 0 owns tiles 2b, 2b + stride, ...; half 1 owns 2b + 1, ...: drained alternately, so that while one half's tile
+    // is being scattered the other half parks its next one
+    for (int64_t tile = (int64_t)blockIdx.x * 2; tile < n_tiles; tile += tile_stride, ++j) {
+#pragma unroll 1
+      for (int hh = 0; hh < 2; ++hh) {
+        if (tile + hh >= n_tiles) break;
+        BwdTcHalf* Hh = &sm->h[hh];
+        tc::mbar_wait(&Hh->full_bar, j & 1u);
+        if (A.G.main_table)            // null: ray-gradient-only pass (nemit_point_lights), nothing to scatter
+          scatter_tile(Hh, t, lane, M, A.G.main_table, gscale, nred);
+        mbar_arrive(&Hh->empty_bar);   // release: the reads of denc / pbuf above are done
+      }
+    }
+    if (A.red_ops) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) nred += __shfl_xor_sync(0xffffffffu, nred, o);
+      if (lane == 0) atomicAdd(A.red_ops, (unsigned long long)nred);
+    }
+  } else {
+  // ---- compute halves -----------------------------------------------------------------------------------------------
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kComputeRegs));
   bool first = true;
   uint32_t ld_phase = 0;
-  const float gscale = invS * A.loss_scale;
-  uint32_t nred = 0;                 // reduction lane-ops this thread issued (reported when profiling)
-  // deferred scatter: nothing parked yet
-#pragma unroll
-  for (int c = 0; c < 32; ++c) H->denc[c * 128 + t] = 0.f;
+  uint32_t slot_phase = 1;           // empty_bar parity to wait for: a fresh barrier passes parity 1 (slot free)
   // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
   const uint64_t pol = tc::l2_evict_first_policy();
   auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar, pol); };
@@ -281,13 +383,13 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    }, [&] { scatter_levels<0, 4>(H, t, M, A.G.main_table, gscale, nred); });
+    });
     epi_bwd_hidden(taddr + kColD0, H->h3, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
-    }, [&] { scatter_levels<4, 7>(H, t, M, A.G.main_table, gscale, nred); });
+    });
     if (t == 0 && has_next) {       // H3 / G3 has no reader left: the next tile's copies start here
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
       load_h3(next_tile);
@@ -297,7 +399,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
-    }, [&] { scatter_levels<7, 10>(H, t, M, A.G.main_table, gscale, nred); });
+    });
     if (t == 0 && has_next) { load_h2(next_tile); load_in(next_tile); }
     {
       float v[16];
@@ -321,7 +423,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
-    }, [&] { scatter_levels<10, 13>(H, t, M, A.G.main_table, gscale, nred); });
+    });
     epi_bwd_hidden(taddr + kColD0, H->h1, t);
     // this tile's Jacobian rows: the loads fly under the last commit group
     uint4 jn[12];
@@ -334,14 +436,15 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
-    }, [&] { scatter_levels<13, 16>(H, t, M, A.G.main_table, gscale, nred); });
+    });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 
-    // ---- hash grid backward: d/d(position) now; the table scatter of this tile is parked in shared memory and runs in
-    // slices under the NEXT tile's five commit groups (scatter_levels), so that reductions are issued all the time instead
-    // of in one burst per tile ----------------------------------------------------------------------------------
+    // ---- hash grid backward: d/d(position) here; the table scatter of this tile is handed to the scatter warps: the rows
+    // are parked in shared memory once they have given the slot back (previous tile drained) --------------------------
     {
       float gp[3] = {0.f, 0.f, 0.f};
+      tc::mbar_wait(&H->empty_bar, slot_phase);
+      slot_phase ^= 1u;
       H->pbuf[t] = p[0]; H->pbuf[128 + t] = p[1]; H->pbuf[256 + t] = p[2];
 #pragma unroll
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
@@ -364,23 +467,44 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
           gp[2] = fmaf(scs, gx * dz.x + gy * dz.y, gp[2]);
         }
       }
+      // per-ray sums d/d(origin), d/d(direction): reduced over the samples of a ray inside the warp first (a warp's 32
+      // consecutive samples belong to at most two rays), then one lane per ray issues the six atomics
+      float v6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (valid && sel) {
         float gx[3];
         contract_vjp(x, sel, gp, gx);
         const float tmid = tsum * 0.5f;
-        float* rg = A.ray_grad + rr * 6;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          atomicAdd(rg + k, gx[k]);
-          atomicAdd(rg + 3 + k, gx[k] * tmid);
+        for (int k = 0; k < 3; ++k) { v6[k] = gx[k]; v6[3 + k] = gx[k] * tmid; }
+      }
+      {
+        const long long r_any = s / kS2;                  // also defined for rows past the end (their values are zero)
+        const long long r_first = __shfl_sync(0xffffffffu, r_any, 0), r_last = __shfl_sync(0xffffffffu, r_any, 31);
+        const bool lo = r_any == r_first;
+        float a6[6], b6[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { a6[k] = lo ? v6[k] : 0.f; b6[k] = lo ? 0.f : v6[k]; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) {
+            a6[k] += __shfl_xor_sync(0xffffffffu, a6[k], o);
+            b6[k] += __shfl_xor_sync(0xffffffffu, b6[k], o);
+          }
+        }
+        if (lane == 0 && r_first < A.n) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) atomicAdd(A.ray_grad + r_first * 6 + k, a6[k]);
+        }
+        if (lane == 31 && r_last != r_first && r_last < A.n) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) atomicAdd(A.ray_grad + r_last * 6 + k, b6[k]);
         }
       }
+      mbar_arrive(&H->full_bar);     // release: this thread's column of denc / pbuf is written
     }
     first = false;
   }
-
-  // ---- the last tile's parked scatter ---------------------------------------------------------------
-  scatter_levels<0, 16>(H, t, M, A.G.main_table, gscale, nred);
 
   // ---- flush this half's weight-gradient accumulators (torch layouts, loss scale applied) ---------------
   if (!first && A.G.main_table) {
@@ -460,11 +584,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       appearance_component_grad(A.G.appearance, M.num_images, A.app_row, t, g);
     }
   }
-  if (A.red_ops) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) nred += __shfl_xor_sync(0xffffffffu, nred, o);
-    if (lane == 0) atomicAdd(A.red_ops, (unsigned long long)nred);
-  }
+  }  // compute halves
   tc::tc_fence_before();
   __syncthreads();
   if (tid < 32) tc::tmem_dealloc<512>(C->tmem_slot);
@@ -481,7 +601,7 @@ cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, c
   const int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
   const int64_t pairs = (tiles + 1) / 2;
   const int64_t ctas = pairs < 148 ? pairs : 148;      // persistent: one CTA (two halves, all of TMEM) per SM
-  k_field_backward_tc<<<(unsigned)ctas, 256, smem, stream>>>(M, A);
+  k_field_backward_tc<<<(unsigned)ctas, kBwdThreads, smem, stream>>>(M, A);
   return cudaGetLastError();
 }
 

@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnerfemitter.so")
+# NEMIT_LIB selects another build of the same library (A/B variants of single kernels made by tools/build_variant.sh)
+LIB_PATH = os.environ.get("NEMIT_LIB") or os.path.join(_HERE, "libnerfemitter.so")
 MAX_LEVELS = 16
 
 c_float_p = C.POINTER(C.c_float)

@@ -62,6 +62,18 @@ int main() {
         printf("%s W=%d threads/CTA=%4d (full occupancy): %.3f ms, %.1f G lane-ops/s, %.2f SM-cycles per lane-op @1.9GHz\n",
                spread ? "random " : "coalesc", W, threads, ms, lane_ops / ms * 1e-6, ms * 1e-3 * 1.9e9 * 148 / lane_ops);
       }
+  // is the 1.5 cycles per lane-op an SM-side or an L2-side (chip-wide) limit?  Same kernel on fewer SMs: an SM-side limit
+  // keeps the per-SM rate, a chip-wide one raises it
+  for (int nsm : {148, 111, 74, 37, 18}) {
+    const int blocks = nsm * 8, threads = 256, ops = 512;
+    auto launch = [&] { k_red<2><<<blocks, threads>>>(t, entries - 1, ops, 1); };
+    launch(); CK(cudaDeviceSynchronize());
+    cudaEventRecord(a); launch(); cudaEventRecord(b); CK(cudaDeviceSynchronize());
+    float ms; cudaEventElapsedTime(&ms, a, b);
+    double lane_ops = (double)blocks * threads * ops;
+    printf("SM sweep: %3d SMs (8 CTAs of 256 each): %.3f ms, %.1f G lane-ops/s chip-wide, %.2f SM-cycles per lane-op per SM @1.965GHz\n",
+           nsm, ms, lane_ops / ms * 1e-6, ms * 1e-3 * 1.965e9 * nsm / lane_ops);
+  }
   // low occupancy: 8 warps per SM
   for (int W : {2, 4}) {
     const int blocks = 148, threads = 256, ops = 4096;
