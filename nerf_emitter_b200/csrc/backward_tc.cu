@@ -28,9 +28,11 @@
 //              the SM's reduction issue rate (1.5 cycles per lane, tools/red_bench.cu).
 // Warp specialisation (round 2): the table scatter does not run on the compute halves any more.  A half parks the tile's
 // d-encoding rows and sample positions in shared memory (one column per sample) and signals an mbarrier; a separate
-// warpgroup of four scatter warps (one thread per parked sample, 96 registers each after setmaxnreg.dec) drains them into
-// red.global.add while the MMA chains run, serving the two halves alternately so that a full slot is always waiting, and
-// hands the slot back through a second mbarrier.  The compute halves (setmaxnreg.inc) only ever wait for their own
+// set of scatter warps (two warpgroups: a thread per parked sample in each, group g taking the levels l with l % 2 == g;
+// 64 registers each after setmaxnreg.dec) drains them into red.global.add while the MMA chains run, serving the two halves
+// alternately so that a full slot is always waiting, and hands the slot back through a second mbarrier.  Measured per
+// 2^16 rays: round-1 kernel 1.93 ms; one scatter warpgroup 1.86; + run aggregation 1.61; + early exit of the scan 1.54;
+// two scatter warpgroups 1.42 (the scatter warps are instruction-bound, ncu: profiles/r2_ncu_backward_ws_agg_summary.txt).  The compute halves (setmaxnreg.inc) only ever wait for their own
 // commit groups and for a free slot.
 // What bounds the scatter (measured, tools/red_bench.cu SM sweep, profiles/r2_red_bench.txt): red.global.add is limited
 // CHIP-WIDE - 184 G lane-ops/s whether 18 or 148 SMs issue them, whatever the width up to 16 bytes - i.e. by the L2
@@ -74,15 +76,19 @@ constexpr uint32_t kHalfCols = 256;
 #endif
 constexpr int kScatterUnroll = NEMIT_SCATTER_UNROLL;
 // scatter warps: 128 threads = one sample of the parked tile each; they serve the two compute halves alternately
-constexpr int kScatterThreads = 128;
+#ifndef NEMIT_SCATTER_GROUPS
+#define NEMIT_SCATTER_GROUPS 2         // scatter warpgroups: group g takes the levels l with l % groups == g
+#endif
+constexpr int kScatterGroups = NEMIT_SCATTER_GROUPS;
+constexpr int kScatterThreads = 128 * kScatterGroups;
 constexpr int kComputeThreads = 256;
 constexpr int kBwdThreads = kComputeThreads + kScatterThreads;
 // register split: the CTA is launched with 168 registers per thread (65536 / 384 rounded down to a multiple of 8), i.e. a
 // pool of 64512; the scatter warpgroup shrinks and the two compute warpgroups grow out of what it released (setmaxnreg).
 // The split must fit the POOL, not the register file: a setmaxnreg.inc that cannot be served blocks for ever.
-constexpr int kLaunchRegs = 168;
-constexpr int kComputeRegs = 200;
-constexpr int kScatterRegs = 104;
+constexpr int kLaunchRegs = kScatterGroups == 1 ? 168 : 128;
+constexpr int kComputeRegs = kScatterGroups == 1 ? 200 : 192;
+constexpr int kScatterRegs = kScatterGroups == 1 ? 104 : 64;
 static_assert(kComputeThreads * kComputeRegs + kScatterThreads * kScatterRegs <= kBwdThreads * kLaunchRegs, "register pool of the CTA");
 #ifndef NEMIT_BWD_AGGREGATE
 #define NEMIT_BWD_AGGREGATE 1          // sum the contributions of runs of lanes that fall into the same grid cell before the red
@@ -150,8 +156,8 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
 //     run; the 16 corner contributions are summed over the run with a segmented shuffle scan and the last lane issues them;
 //   * corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices differ in
 //     bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
-__device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int lane, const ModelDev& M, float2* table,
-                                             float gscale, uint32_t& nred) {
+__device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int lane, int group, const ModelDev& M,
+                                             float2* table, float gscale, uint32_t& nred) {
   const float p[3] = {H->pbuf[smp], H->pbuf[128 + smp], H->pbuf[256 + smp]};
 #ifndef NEMIT_BWD_SCATTER_FROM
 #define NEMIT_BWD_SCATTER_FROM 0       // experiments only: first level that is scattered
@@ -160,7 +166,7 @@ __device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int la
 #define NEMIT_BWD_SCATTER_TO 16        // experiments only: one past the last level that is scattered
 #endif
 #pragma unroll 1
-  for (int l = NEMIT_BWD_SCATTER_FROM; l < NEMIT_BWD_SCATTER_TO; ++l) {
+  for (int l = NEMIT_BWD_SCATTER_FROM + group; l < NEMIT_BWD_SCATTER_TO; l += kScatterGroups) {
     const float gx = H->denc[(2 * l) * 128 + smp], gy = H->denc[(2 * l + 1) * 128 + smp];
     const bool act = gx != 0.f || gy != 0.f;
     if (!__any_sync(0xffffffffu, act)) continue;
@@ -189,6 +195,7 @@ __device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int la
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
           const bool take = lane - d >= start;
+          if (!__any_sync(0xffffffffu, take)) break;       // no run of this warp is longer than d
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             const float up = __shfl_up_sync(0xffffffffu, w[i], d);
@@ -252,7 +259,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   BwdTcSmem* sm = reinterpret_cast<BwdTcSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   const int tid = threadIdx.x, lane = tid & 31, wq = (tid >> 5) & 3;
   // roles: threads [0, 256) = two compute halves of 128 (thread t = sample row t of the half's tile);
-  //        threads [256, 384) = four scatter warps (thread t = sample t of whichever half's parked tile is being drained)
+  //        threads [256, ...) = scatter warpgroups (thread t = sample t of whichever half's parked tile is being drained)
   const bool is_scatter = tid >= kComputeThreads;
   const int half = is_scatter ? 0 : tid >> 7;
   const int t = tid & 127;
@@ -320,7 +327,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
         BwdTcHalf* Hh = &sm->h[hh];
         tc::mbar_wait(&Hh->full_bar, j & 1u);
         if (A.G.main_table)            // null: ray-gradient-only pass (nemit_point_lights), nothing to scatter
-          scatter_tile(Hh, t, lane, M, A.G.main_table, gscale, nred);
+          scatter_tile(Hh, t, lane, (tid - kComputeThreads) >> 7, M, A.G.main_table, gscale, nred);
         mbar_arrive(&Hh->empty_bar);   // release: the reads of denc / pbuf above are done
       }
     }

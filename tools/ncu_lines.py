@@ -11,7 +11,7 @@ for f in sorted(os.listdir(tmp)):
     txt = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
     if kname not in txt:
         continue
-    cur_fun, outer = None, None
+    cur_fun, outer, pending = None, None, False
     for ln in txt.splitlines():
         m = re.match(r"\s*\.text\.(\S+):", ln)
         if m:
@@ -19,10 +19,13 @@ for f in sorted(os.listdir(tmp)):
             continue
         m = re.match(r'\s*//## File "([^"]+)", line (\d+)( inlined at.*)?$', ln)
         if m:
-            if not m.group(3):
+            if not m.group(3) or (os.environ.get("INNER") and not pending):
                 outer = (os.path.basename(m.group(1)), int(m.group(2)))
+            pending = True
             continue
         m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
+        if m:
+            pending = False
         if m and cur_fun and kname in cur_fun:
             line_of[int(m.group(1), 16)] = (outer, m.group(2).strip())
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
