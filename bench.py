@@ -40,7 +40,7 @@ LOADS_FIELD = 48 * 16 * 8                           # main-grid lane-loads per r
 MISS_FIELD = 48 * 11 * 4                            # of which compulsory L1 misses: 11 hashed levels x 4 (y,z) pairs: 2 112
 ALG_BYTES_SAMPLING = LOADS_SAMPLING * 8             # 112 640 B
 ALG_BYTES_FIELD = LOADS_FIELD * 8                   # 49 152 B
-SEED_KEEP_BYTES = 48 * (64 + 192 + 448 + 16)        # per ray: encoding, Jacobian, activations, seeds kept for the backward
+SEED_KEEP_BYTES = 48 * (64 + 192 + 192 + 16)        # per ray: encoding, Jacobian, activations, seeds kept for the backward
 ALG_BYTES = {"k_sample_levels": ALG_BYTES_SAMPLING, "k_field_forward": ALG_BYTES_FIELD,
              "k_field_forward_tc": ALG_BYTES_FIELD,
              "k_field_forward<adjoint_seed>": ALG_BYTES_FIELD + SEED_KEEP_BYTES,   # fp16 mode; fp32 mode keeps 16 B/sample

@@ -277,15 +277,15 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   if (L) L->g_absmax = off;
   off += align_up(sizeof(float));
   // tensor-core backward: per sample of the backward sub-chunk the encoding row (64 B), its Jacobian (192 B), the
-  // activations H1 / IN / H2 / H3 (448 B) and the pre-activation seeds (16 B), kept by the seed pass
+  // operand rows H1 / IN (192 B) and the pre-activation seeds (16 B), kept by the seed pass (H2 / H3 are recomputed)
   const size_t bc = (size_t)(c < kBwdChunkRays ? c : kBwdChunkRays);
   const size_t tiles = (bc * kS2 + 127) / 128 + 3;
   if (L) L->enc_tiles = off;
-  off += align_up(tiles * 8192);
+  off += align_up(tiles * (size_t)kEncTileBytes);
   if (L) L->jac_tiles = off;
-  off += align_up(tiles * 24576);
+  off += align_up(tiles * (size_t)kJacTileBytes);
   if (L) L->act_tiles = off;
-  off += align_up(tiles * 57344);
+  off += align_up(tiles * (size_t)kActTileBytes);
   if (L) L->seeds4 = off;
   off += align_up(tiles * 128 * 16);
   return off - base;

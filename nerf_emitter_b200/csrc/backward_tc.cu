@@ -3,13 +3,16 @@
 //
 // The seed pass (k_field_forward_tc<1>, field_tc.cu) has already run the forward of the chunk on the tensor cores and
 // kept, per 128-sample tile and in the UMMA operand layout: the hash encoding E, its Jacobian d enc / d offset, the
-// post-ReLU activations H1, IN = [SH16 | geo15 | 1], H2, H3, and per sample the seed d loss / d pre-activation
-// (rgb xyz with the SafeExp derivative, density w with the trunc_exp derivative and the selector).  So this kernel
-// neither gathers from the parameter table (its L2 working set is the gradient table alone) nor recomputes anything.
+// operand rows H1 and IN = [SH16 | geo15 | 1], and per sample the seed d loss / d pre-activation (rgb xyz with the
+// SafeExp derivative, density w with the trunc_exp derivative and the selector): 464 B per sample.  So this kernel
+// never gathers from the parameter table (its L2 working set is the gradient table alone).  The two head hidden layers
+// H2, H3 (256 B per sample in round 1) are recomputed here from IN with two forward MMAs + epilogues per tile: the
+// compute halves wait for the scatter warps anyway, and the same fp16 operands through the same instruction shapes
+// give the same bits, hence the same ReLU masks, as the seed pass had.
 //
 // One CTA = 256 threads = two independent halves of 128 threads; a half owns one tile at a time (thread t = sample
 // row t).  Per tile:
-//   load     : E, H1, IN, H2, H3 arrive by five 1-D bulk copies (cp.async.bulk -> mbarrier complete_tx) straight into
+//   load     : E, H1, IN arrive by three 1-D bulk copies (cp.async.bulk -> mbarrier complete_tx) straight into
 //              the operand buffers; the copies of the NEXT tile are issued as soon as a buffer's last reader (an MMA
 //              commit group) has completed, so they fly under the remaining layers and the scatter
 //   backward : for every layer, in ONE commit group,
@@ -102,6 +105,8 @@ struct BwdTcCommon {
   alignas(128) uint8_t b5[16 * 64 * 2];   // head layer 2   (3 rows used of 16)
   alignas(128) uint8_t ones[8 * 128 * 2]; // MN-major 8 x 128 operand of fp16 ones
   float app[kApp];
+  float bias_h0[64];                      // head layer 0 bias with the appearance columns folded in (as the forward)
+  float bias_h1[64];
   uint32_t tmem_slot;
 };
 struct BwdTcHalf {
@@ -123,7 +128,7 @@ struct BwdTcSmem {
   BwdTcCommon c;
   BwdTcHalf h[2];
 };
-constexpr uint32_t kTileLoadBytes = 8192 + 57344;
+constexpr uint32_t kTileLoadBytes = kEncTileBytes + kActTileBytes;
 
 __device__ __forceinline__ void half_sync(int half) {
   asm volatile("bar.sync %0, 128;" ::"r"(half + 1) : "memory");
@@ -224,6 +229,29 @@ __device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int la
   }
 }
 
+// forward recompute of a head hidden layer: accumulator row + bias, ReLU -> fp16 operand row (k_field_forward_tc's
+// epilogue_hidden, same arithmetic in the same order)
+__device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* buf, int row) {
+  float v[4][16];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
+  tc::tmem_ld_wait();
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+#pragma unroll
+    for (int hh = 0; hh < 2; ++hh) {
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = hh * 8 + q * 2;
+        const float x0 = fmaxf(v[c][j] + bias[c * 16 + j], 0.f), x1 = fmaxf(v[c][j + 1] + bias[c * 16 + j + 1], 0.f);
+        w[q] = tc::pack_h2(x0, x1);
+      }
+      *reinterpret_cast<uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
 // hidden layer: accumulator row x (activation row > 0) -> fp16 gradient row written over the activation row
 __device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int row) {
   float v[4][16];
@@ -284,9 +312,16 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     tc::fence_mbar_init();
   }
   if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
+  for (int i = tid; i < 64; i += kBwdThreads) C->bias_h1[i] = A.P.head_b1[i];
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
+  for (int n = tid; n < 64; n += kBwdThreads) {          // as k_field_forward_tc: b0 + W0[:, 31:63] . appearance, same order
+    float b = A.P.head_b0[n];
+    for (int k = 0; k < kApp; ++k) b = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], C->app[k], b);
+    C->bias_h0[n] = b;
+  }
+  __syncthreads();
   const uint32_t tm = C->tmem_slot + (uint32_t)half * kHalfCols;   // this half's columns, lane 0
   const uint32_t taddr = tm + ((uint32_t)(wq * 32) << 16);         // this warp's 32 TMEM lanes
   uint32_t phase = 0;
@@ -344,16 +379,14 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   uint32_t slot_phase = 1;           // empty_bar parity to wait for: a fresh barrier passes parity 1 (slot free)
   // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
   const uint64_t pol = tc::l2_evict_first_policy();
-  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * 8192, 8192, &H->ld_bar, pol); };
-  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * 57344, 16384, &H->ld_bar, pol); };
-  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * 57344 + 16384, 8192, &H->ld_bar, pol); };
-  auto load_h2 = [&](int64_t tl) { tc::bulk_g2s(H->h2, A.act_tiles + tl * 57344 + 24576, 16384, &H->ld_bar, pol); };
-  auto load_h3 = [&](int64_t tl) { tc::bulk_g2s(H->h3, A.act_tiles + tl * 57344 + 40960, 16384, &H->ld_bar, pol); };
+  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * kEncTileBytes, 8192, &H->ld_bar, pol); };
+  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * kActTileBytes, 16384, &H->ld_bar, pol); };
+  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * kActTileBytes + 16384, 8192, &H->ld_bar, pol); };
   {
     const int64_t tile0 = (int64_t)blockIdx.x * 2 + half;
     if (t == 0 && tile0 < n_tiles) {
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
-      load_h3(tile0); load_h2(tile0); load_in(tile0); load_h1(tile0); load_e(tile0);
+      load_in(tile0); load_h1(tile0); load_e(tile0);
     }
   }
   for (int64_t tile = (int64_t)blockIdx.x * 2 + half; tile < n_tiles; tile += tile_stride) {
@@ -385,6 +418,16 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     tc::mbar_wait(&H->ld_bar, ld_phase);
     ld_phase ^= 1u;
 
+    // ---- head hidden layers, forward again (H2, H3 are not kept) ------------------------------------------
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->in, 128), tc::op_kmajor(C->b3, 64), tc::idesc_f16(128, 64), 2, false);
+    });
+    epi_fwd_hidden(taddr + kColD0, C->bias_h0, H->h2, t);
+    mma_step(H, half, t, phase, [&] {
+      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_kmajor(C->b4, 64), tc::idesc_f16(128, 64), 4, false);
+    });
+    epi_fwd_hidden(taddr + kColD0, C->bias_h1, H->h3, t);
+
     // ---- head MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
@@ -397,17 +440,16 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
     });
-    if (t == 0 && has_next) {       // H3 / G3 has no reader left: the next tile's copies start here
-      tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
-      load_h3(next_tile);
-    }
     epi_bwd_hidden(taddr + kColD0, H->h2, t);
     mma_step(H, half, t, phase, [&] {
       tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
     });
-    if (t == 0 && has_next) { load_h2(next_tile); load_in(next_tile); }
+    if (t == 0 && has_next) {       // IN has no reader left: the next tile's copies start here
+      tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
+      load_in(next_tile);
+    }
     {
       float v[16];
       tc::tmem_ld16(taddr + kColD0, v);
@@ -435,7 +477,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     // this tile's Jacobian rows: the loads fly under the last commit group
     uint4 jn[12];
     {
-      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * 24576) + t;
+      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * kJacTileBytes) + t;
 #pragma unroll
       for (int c = 0; c < 12; ++c) jn[c] = __ldcs(jp + c * 128);
     }

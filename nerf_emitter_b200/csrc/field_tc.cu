@@ -187,7 +187,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
             wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
             wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
           }
-          uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * 24576) + (l0 >> 2) * 3 * 128 + tid;
+          uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * kJacTileBytes) + (l0 >> 2) * 3 * 128 + tid;
           __stcs(jp, make_uint4(wj[0], wj[1], wj[2], wj[3]));
           __stcs(jp + 128, make_uint4(wj[4], wj[5], wj[6], wj[7]));
           __stcs(jp + 256, make_uint4(wj[8], wj[9], wj[10], wj[11]));
@@ -195,9 +195,9 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       }
       // adjoint-seed mode keeps the activations (fp16 operand rows) for k_field_backward_tc
       uint8_t* act = nullptr;
-      if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * 57344;
+      if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * kActTileBytes;
       // ---- base MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32>(sm, sm->b1, tmem, phase, tid, act ? A.enc_tiles + tile_id * 8192 : nullptr, 8192, policy);
+      run_layer<64, 32>(sm, sm->b1, tmem, phase, tid, act ? A.enc_tiles + tile_id * kEncTileBytes : nullptr, 8192, policy);
       epilogue_hidden(taddr, sm->bias_b0, sm->a, tid);
       run_layer<16, 64>(sm, sm->b2, tmem, phase, tid, act, 16384, policy);
       {
@@ -230,9 +230,10 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       // ---- head MLP ------------------------------------------------------------------------------------
       run_layer<64, 32>(sm, sm->b3, tmem, phase, tid, act ? act + 16384 : nullptr, 8192, policy);
       epilogue_hidden(taddr, sm->bias_h0, sm->a, tid);
-      run_layer<64, 64>(sm, sm->b4, tmem, phase, tid, act ? act + 24576 : nullptr, 16384, policy);
+      // H2 / H3 are not kept: the backward recomputes them from IN (kernels.h)
+      run_layer<64, 64>(sm, sm->b4, tmem, phase, tid);
       epilogue_hidden(taddr, sm->bias_h1, sm->a, tid);
-      run_layer<16, 64>(sm, sm->b5, tmem, phase, tid, act ? act + 40960 : nullptr, 16384, policy);
+      run_layer<16, 64>(sm, sm->b5, tmem, phase, tid);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);

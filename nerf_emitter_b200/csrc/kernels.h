@@ -63,6 +63,11 @@ struct FieldParams {
   const float* appearance;
 };
 
+constexpr int kEncTileBytes = 8192;     // 128 samples x 32 fp16
+constexpr int kJacTileBytes = 24576;    // 128 samples x 96 fp16
+constexpr int kActTileBytes = 24576;    // H1 (16384) | IN (8192)
+constexpr int kKeptBytesPerSample = (kEncTileBytes + kJacTileBytes + kActTileBytes) / 128 + 16;   // 464 (round 1: 720)
+
 struct FieldArgs : RayArgs {
   FieldParams P;
   const float* t_edges2;   // (n, 49) chunk-local
@@ -85,8 +90,10 @@ struct FieldArgs : RayArgs {
   // Tile = 128 consecutive samples of the chunk; 16-byte chunk c of row r of tile i lives at
   //   enc_tiles + i * 8192  + (c * 128 + r) * 16   (c < 4 : fp16 encoding, 8 values per chunk, = the UMMA A operand)
   //   jac_tiles + i * 24576 + (c * 128 + r) * 16   (c < 12: fp16 d enc / d offset, per level dx.xy dy.xy dz.xy)
-  //   act_tiles + i * 57344 + {0: H1 (8 chunks), 16384: IN = [SH16 | geo15 | 1] (4), 24576: H2 (8), 40960: H3 (8)}
-  //             + (c * 128 + r) * 16                          fp16 post-ReLU activations = UMMA operands as well
+  //   act_tiles + i * kActTileBytes + {0: H1 (8 chunks), 16384: IN = [SH16 | geo15 | 1] (4)} + (c * 128 + r) * 16
+  //             fp16 operand rows of the base hidden layer and of the head input.  The two head hidden layers H2, H3 are
+  //             NOT kept (round 2): k_field_backward_tc recomputes them from IN with two forward MMAs on the idle tensor
+  //             pipe - same fp16 operands, same instruction shapes, hence the same bits and the same ReLU masks
   uint8_t* enc_tiles;
   uint8_t* jac_tiles;
   uint8_t* act_tiles;
