@@ -164,10 +164,13 @@ extern "C" int nemit_create(const NemitConfig* cfg, int device, NemitHandle** ou
   h->opt_stats = reinterpret_cast<double*>(h->tables_dev + ((n0 + n1 + n2 + 1) & ~1));   // 8-byte aligned tail
   h->ev = static_cast<cudaEvent_t*>(calloc(2 * kEvRing, sizeof(cudaEvent_t)));
   h->ev_kind = static_cast<int*>(calloc(kEvRing, sizeof(int)));
-  e = cudaMalloc(&h->counters, sizeof(unsigned long long) * 8);
+  for (int i = 0; i < 2 && e == cudaSuccess; ++i)
+    e = cudaMalloc(&h->prop_half[i], sizeof(uint32_t) * ((size_t)cfg->prop_grid[i].num_levels << cfg->prop_grid[i].log2_table_size));
+  if (e == cudaSuccess) e = cudaMalloc(&h->counters, sizeof(unsigned long long) * 8);
   if (e == cudaSuccess) e = cudaMemset(h->counters, 0, sizeof(unsigned long long) * 8);
   if (e != cudaSuccess || !h->ev || !h->ev_kind) {
-    cudaFree(h->tables_dev); cudaFree(h->counters); free(h->ev); free(h->ev_kind); delete h;
+    cudaFree(h->tables_dev); cudaFree(h->counters); cudaFree(h->prop_half[0]); cudaFree(h->prop_half[1]);
+    free(h->ev); free(h->ev_kind); delete h;
     return e != cudaSuccess ? cuda_fail(e, "cudaMalloc(counters)") : fail(NEMIT_E_INVALID, "nemit_create: out of host memory%s");
   }
   *out = h;
@@ -180,6 +183,8 @@ extern "C" int nemit_destroy(NemitHandle* h) {
   nemit_comm_destroy(h);
   cudaFree(h->tables_dev);
   cudaFree(h->counters);
+  cudaFree(h->prop_half[0]);
+  cudaFree(h->prop_half[1]);
   free(h->rotation_ids);
   if (h->ev)
     for (int i = 0; i < 2 * kEvRing; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
@@ -368,6 +373,7 @@ static void fill_sample_args(const NemitHandle* h, SampleArgs& S, const NemitRay
     S.prop_table[i] = reinterpret_cast<const float2*>(h->P.prop_table[i]);
     S.prop_w0[i] = h->P.prop_w0[i]; S.prop_b0[i] = h->P.prop_b0[i];
     S.prop_w1[i] = h->P.prop_w1[i]; S.prop_b1[i] = h->P.prop_b1[i];
+    S.prop_table_h[i] = h->prop_half[i];
   }
   S.lin0 = h->lin0; S.u1 = h->u1; S.u2 = h->u2;
 }

@@ -16,6 +16,7 @@ struct NemitHandle {
   const float* u1;
   const float* u2;
   double* opt_stats;        // optimizer-step scratch (tail of tables_dev)
+  uint32_t* prop_half[2];   // packed-half copies of the proposal tables for the fast sampler (scratch, rewritten per launch)
   unsigned long long* counters;   // device counters: [0] red lane-ops of the tensor-core backward (profiling only)
   bool params_bound, grads_bound;
   // nemit_set_appearance_mode

@@ -37,6 +37,7 @@ __host__ __device__ inline float ray_scale(const ModelDev& M, const RayArgs& A) 
 
 struct SampleArgs : RayArgs {
   const float2* prop_table[2];
+  uint32_t* prop_table_h[2];   // fast sampler: packed-half copies of the two tables (handle-owned scratch, rewritten per launch)
   const float* prop_w0[2];
   const float* prop_b0[2];
   const float* prop_w1[2];

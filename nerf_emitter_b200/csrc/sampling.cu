@@ -44,7 +44,7 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
     for (int lvl = 0; lvl < 2; ++lvl) {
       const int S = lvl == 0 ? kS0 : kS1;          // bins at this level
       const int Mn = lvl == 0 ? kS1 : kS2;         // samples of the next level
-      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane);
+      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane, nullptr, A.prop_table_h[lvl]);
       float* w_out = lvl == 0 ? A.weights0 : A.weights1;
       if (w_out) {
         for (int i = lane; i < S; i += 32) w_out[r * S + i] = sc->buf[i];
@@ -71,6 +71,18 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
   }
 }
 
+// fp32 (2 features) -> packed half2 copy of both proposal tables, one pass of 10 MB read + 5 MB written per sampler launch
+// (the parameters may have changed since the last call; the library cannot know)
+__global__ void k_prop_tables_half(const float2* __restrict__ t0, const float2* __restrict__ t1, uint32_t* __restrict__ h0,
+                                   uint32_t* __restrict__ h1, int n0, int n1) {
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n0 + n1; i += stride) {
+    const float2 v = i < n0 ? __ldg(t0 + i) : __ldg(t1 + (i - n0));
+    const __half2 hv = __float22half2_rn(v);
+    (i < n0 ? h0[i] : h1[i - n0]) = *reinterpret_cast<const uint32_t*>(&hv);
+  }
+}
+
 template <class MLP>
 static cudaError_t launch_sample_levels_t(const ModelDev& M, const SampleArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
@@ -87,6 +99,13 @@ static cudaError_t launch_sample_levels_t(const ModelDev& M, const SampleArgs& A
   return cudaGetLastError();
 }
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast) {
+  if (fast && A.n > 0) {
+    if (!A.prop_table_h[0] || !A.prop_table_h[1]) return cudaErrorInvalidValue;
+    const int n0 = M.prop_grid[0].num_levels * (int)M.prop_grid[0].table_size, n1 = M.prop_grid[1].num_levels * (int)M.prop_grid[1].table_size;
+    k_prop_tables_half<<<148 * 4, 256, 0, stream>>>(A.prop_table[0], A.prop_table[1], A.prop_table_h[0], A.prop_table_h[1], n0, n1);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+  }
   return fast ? launch_sample_levels_t<PropMlpFastSmem>(M, A, stream) : launch_sample_levels_t<PropMlpSmem>(M, A, stream);
 }
 

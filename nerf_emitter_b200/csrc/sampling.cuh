@@ -119,10 +119,7 @@ __device__ __forceinline__ void load_prop_mlp_fast(PropMlpFastSmem* dst, const f
 __device__ __forceinline__ __half2 lerp_h2(__half2 a_hi, __half2 b_lo, __half2 f) {
   return __hfma2(f, __hsub2(a_hi, b_lo), b_lo);
 }
-__device__ __forceinline__ __half2 blend_cell_h2(const float2 v[8], const LevelCell& c) {
-  __half2 h[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) h[k] = __float22half2_rn(v[k]);
+__device__ __forceinline__ __half2 blend_cell_h2(const __half2 h[8], const LevelCell& c) {
   const __half2 fx = __float2half2_rn(c.fx), fy = __float2half2_rn(c.fy), fz = __float2half2_rn(c.fz);
   const __half2 a = lerp_h2(h[0], h[1], fx), b = lerp_h2(h[2], h[3], fx);
   const __half2 cc = lerp_h2(h[4], h[5], fx), d = lerp_h2(h[6], h[7], fx);
@@ -151,17 +148,22 @@ __device__ __forceinline__ bool contract_normalise_fast(const float x[3], const 
   return sel;
 }
 
-static __device__ __noinline__ float prop_density_fast(float x0, float x1, float x2, const float2* __restrict__ table,
+// `table` is the packed-half copy of the proposal table (k_prop_tables_half, one __half2 per entry, refreshed by every
+// sampler launch): the same cvt.rn the blend applied per corner before, done once per entry instead of 40 times per sample
+static __device__ __noinline__ float prop_density_fast(float x0, float x1, float x2, const uint32_t* __restrict__ table,
                                                        const GridDev& G, const PropMlpFastSmem* W, const ModelDev& M) {
   float x[3] = {x0, x1, x2}, p[3];
   if (!contract_normalise_fast(x, M, p)) return 0.f;
   LevelCell cell[kPropLevels];
-  float2 v[kPropLevels][8];
+  __half2 v[kPropLevels][8];
 #pragma unroll
   for (int l = 0; l < kPropLevels; ++l) {
     level_cell(p, G.scal[l], G.table_mask, (uint32_t)l * G.table_size, cell[l]);
 #pragma unroll
-    for (int c = 0; c < 8; ++c) v[l][c] = ldg_f2(table, cell[l].idx[c]);
+    for (int c = 0; c < 8; ++c) {
+      const uint32_t u = __ldg(table + cell[l].idx[c]);
+      v[l][c] = *reinterpret_cast<const __half2*>(&u);
+    }
   }
   __half2 acc[8];
   {
@@ -255,7 +257,7 @@ template <class MLP = PropMlpSmem>
 __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const RayCtx& R, int S,
                                                        const float2* __restrict__ table, const GridDev& G,
                                                        const MLP* W, const ModelDev& M, int lane,
-                                                       float* ds_out = nullptr) {
+                                                       float* ds_out = nullptr, const uint32_t* __restrict__ table_h = nullptr) {
   constexpr bool kFast = !cuda::std::is_same<MLP, PropMlpSmem>::value;
 #pragma unroll 1
   for (int i = lane; i < S; i += 32) {
@@ -265,7 +267,7 @@ __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const Ra
     float sigma;
     if constexpr (kFast)
       sigma = prop_density_fast(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
-                                sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
+                                sample_pos(R.o[2], R.d[2], tsum), table_h, G, W, M);
     else
       sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
                            sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);

@@ -6,7 +6,7 @@ rep, so, kname = sys.argv[1], os.path.abspath(sys.argv[2]), sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 30
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", so], cwd=tmp, capture_output=True)
-line_of = {}
+line_of = {}          # demangled function name -> {offset: ((file, line), sass)}
 for f in sorted(os.listdir(tmp)):
     txt = subprocess.run(["nvdisasm", "-gi", "-c", os.path.join(tmp, f)], capture_output=True, text=True).stdout
     if kname not in txt:
@@ -19,7 +19,11 @@ for f in sorted(os.listdir(tmp)):
             continue
         m = re.match(r'\s*//## File "([^"]+)", line (\d+)( inlined at.*)?$', ln)
         if m:
-            if not m.group(3) or (os.environ.get("INNER") and not pending):
+            # a group of marker lines precedes an instruction: innermost first, then each inlined-at site, outermost last
+            if os.environ.get("INNER"):
+                if not pending:
+                    outer = (os.path.basename(m.group(1)), int(m.group(2)))
+            elif not m.group(3):
                 outer = (os.path.basename(m.group(1)), int(m.group(2)))
             pending = True
             continue
@@ -27,7 +31,7 @@ for f in sorted(os.listdir(tmp)):
         if m:
             pending = False
         if m and cur_fun and kname in cur_fun:
-            line_of[int(m.group(1), 16)] = (outer, m.group(2).strip())
+            line_of.setdefault(cur_fun, {})[int(m.group(1), 16)] = (outer, m.group(2).strip())
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 # several kernels may be in the report: take the blocks whose "Kernel Name" matches
@@ -40,9 +44,14 @@ for r in rows:
         cur["hdr"] = r
     elif cur is not None and cur["hdr"] and r and r[0].startswith("0x"):
         cur["rows"].append(r)
+def norm(x):
+    return re.sub(r"\(.*", "", x).replace("nemit::", "").replace("void ", "").replace(" ", "")
+demangled = {norm(subprocess.run(["c++filt", f], capture_output=True, text=True).stdout.strip()): f for f in line_of}
 for b in blocks:
-    if kname not in b["name"].replace("::", "") and kname not in b["name"]:
+    key = norm(b["name"])
+    if kname not in key or key not in demangled:
         continue
+    lo = line_of[demangled[key]]
     hdr = b["hdr"]
     col = {h: i for i, h in enumerate(hdr)}
     stalls = [h for h in hdr if h.startswith("stall_") and "Not Issued" not in h]
@@ -53,7 +62,7 @@ for b in blocks:
         off = int(r[0], 16) - base
         n = int(r[col["# Samples"]] or 0)
         tot += n
-        where = line_of.get(off, ((None, 0), ""))[0] or ("?", 0)
+        where = lo.get(off, ((None, 0), ""))[0] or ("?", 0)
         per[where]["n"] += n
         per[where]["inst"] += int(r[col["Instructions Executed"]] or 0)
         for s in stalls:
