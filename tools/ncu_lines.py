@@ -67,7 +67,8 @@ for b in blocks:
         per[where]["inst"] += int(r[col["Instructions Executed"]] or 0)
         for s in stalls:
             per[where][s] += int(r[col[s]] or 0)
-    print("==", b["name"], "total samples", tot)
+    tot_inst = sum(c["inst"] for c in per.values())
+    print("==", b["name"], "total samples", tot, "warp instructions", tot_inst)
     src = {}
     for (fn, ln), c in sorted(per.items(), key=lambda kv: -kv[1]["n"])[:top]:
         if fn not in src:
@@ -75,5 +76,5 @@ for b in blocks:
             src[fn] = open(p).read().splitlines() if os.path.isfile(p) else []
         text = src[fn][ln - 1].strip()[:90] if 0 < ln <= len(src[fn]) else ""
         why = sorted(((c[s], s[6:]) for s in stalls), reverse=True)[:3]
-        print("%6d %5.1f%%  %s:%d  %-92s %s" % (c["n"], 100.0 * c["n"] / max(tot, 1), fn, ln, text,
+        print("%6d %5.1f%% inst %5.1f%%  %s:%d  %-92s %s" % (c["n"], 100.0 * c["n"] / max(tot, 1), 100.0 * c["inst"] / max(tot_inst, 1), fn, ln, text,
                                                ", ".join("%s %d" % (s, n) for n, s in why if n)))
