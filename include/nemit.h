@@ -161,6 +161,28 @@ int nemit_set_appearance_mode(NemitHandle* h, int32_t always_use_camera_indices,
                               int32_t use_average_appearance_embedding, const int32_t* rotation_ids_host,
                               int32_t num_rotation_ids);
 
+/* Per-sample frustum rotation of turntable captures: Rotater.apply_frustums (NS/field_components/rotater.py:125-149,
+ * hooked into RayBundle.get_ray_samples, NS/cameras/rays.py:285-286, by get_ray_bundle, DS/emitters/nerf_op.py:86-87).
+ * transforms_host: num_rotations x (3 x 4) row-major [R | t] in NeRF coordinates = Rotater.get_torch_transforms(...)[:, :3, :4]
+ * (call again when a rotation optimizer has moved them); the rotation of a call is the one of rotation id =
+ * rotation_ids[min(camera_idx, len - 1)] (nemit_set_appearance_mode; identity mapping without a table).
+ * bound_type NEMIT_ROT_SPHERE: bound_host = {centre xyz, radius} (|x - c| < r); NEMIT_ROT_BOX: {min xyz, max xyz} (inclusive).
+ * A sample whose UNROTATED position lies inside the bound takes origin R o + t and direction R d.  Which stages rotate
+ * follows the reference to the letter:
+ *   proposal levels (sampling, and the proposal networks' backward)  always - every get_ray_samples call runs the hook;
+ *   final 48 samples in nemit_forward                                rotated (positions and SH directions);
+ *   final samples in nemit_jvp                                       primal rotated, tangents those of the unrotated ray
+ *                                                                    (NS/models/sdf_nerfacto.py:96-104);
+ *   final samples in nemit_backward                                  NOT rotated: get_backward_outputs puts the ray's own
+ *                                                                    origins / directions back (sdf_nerfacto.py:129-131);
+ *   final samples in nemit_point_lights                              rotated, the origin gradient goes back through R^T
+ *                                                                    (calc_brightness_grad, NS/models/nerfacto.py:547-556).
+ * num_rotations == 0 removes the rotater. */
+#define NEMIT_ROT_SPHERE 1
+#define NEMIT_ROT_BOX 2
+int nemit_set_rotater(NemitHandle* h, int32_t num_rotations, const float* transforms_host, int32_t bound_type,
+                      const float* bound_host);
+
 /* borrow parameter / gradient pointers (never copied, never freed) */
 int nemit_bind_params(NemitHandle* h, const NemitParams* p);
 int nemit_bind_grads(NemitHandle* h, const NemitParams* g);

@@ -186,6 +186,7 @@ extern "C" int nemit_destroy(NemitHandle* h) {
   cudaFree(h->prop_half[0]);
   cudaFree(h->prop_half[1]);
   free(h->rotation_ids);
+  free(h->rot_transforms);
   if (h->ev)
     for (int i = 0; i < 2 * kEvRing; ++i) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
   free(h->ev);
@@ -214,6 +215,26 @@ extern "C" int nemit_set_appearance_mode(NemitHandle* h, int32_t always_use_came
   h->num_rotation_ids = num_rotation_ids;
   h->always_use_camera_indices = always_use_camera_indices != 0;
   h->use_average_embedding = use_average_appearance_embedding != 0;
+  return NEMIT_OK;
+}
+
+extern "C" int nemit_set_rotater(NemitHandle* h, int32_t num_rotations, const float* transforms_host, int32_t bound_type,
+                                 const float* bound_host) {
+  if (!h) return fail(NEMIT_E_INVALID, "nemit_set_rotater: null handle%s");
+  if (num_rotations < 0) return fail(NEMIT_E_INVALID, "nemit_set_rotater: negative rotation count%s");
+  if (num_rotations == 0) {
+    free(h->rot_transforms);
+    h->rot_transforms = nullptr; h->num_rotations = 0; h->rot_mode = 0;
+    return NEMIT_OK;
+  }
+  if (!transforms_host || !bound_host) return fail(NEMIT_E_INVALID, "nemit_set_rotater: null argument%s");
+  if (bound_type != NEMIT_ROT_SPHERE && bound_type != NEMIT_ROT_BOX) return fail(NEMIT_E_INVALID, "nemit_set_rotater: unknown bound type%s");
+  float* t = static_cast<float*>(malloc(sizeof(float) * 12 * (size_t)num_rotations));
+  if (!t) return fail(NEMIT_E_INVALID, "nemit_set_rotater: out of host memory%s");
+  memcpy(t, transforms_host, sizeof(float) * 12 * (size_t)num_rotations);
+  free(h->rot_transforms);
+  h->rot_transforms = t; h->num_rotations = num_rotations; h->rot_mode = bound_type;
+  for (int k = 0; k < 6; ++k) h->rot_bound[k] = k < (bound_type == NEMIT_ROT_SPHERE ? 4 : 6) ? bound_host[k] : 0.f;
   return NEMIT_OK;
 }
 
@@ -333,6 +354,17 @@ static bool appearance_row(const NemitHandle* h, int training, int camera_idx, b
   return idx >= 0 && idx < h->cfg.num_images;
 }
 
+// rotation id of a call: Rotater.map_rotation_ids(camera_idx) (rotater.py:94-100), -1 when it has no transform
+static int rotation_id(const NemitHandle* h, int camera_idx) {
+  int idx = camera_idx;
+  if (h->rotation_ids) {
+    if (idx < 0) return -1;
+    if (idx > h->num_rotation_ids - 1) idx = h->num_rotation_ids - 1;
+    idx = h->rotation_ids[idx];
+  }
+  return (idx >= 0 && idx < h->num_rotations) ? idx : -1;
+}
+
 static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who) {
   if (!h || !r) return fail(NEMIT_E_INVALID, "%s: null argument", who);
   if (!h->params_bound) return fail(NEMIT_E_UNBOUND, "%s: parameters not bound (nemit_bind_params)", who);
@@ -341,6 +373,8 @@ static int check_rays(const NemitHandle* h, const NemitRays* r, const char* who)
   int row;
   if (!appearance_row(h, r->training, r->camera_idx, true, &row))
     return fail(NEMIT_E_INVALID, "%s: camera_idx outside the appearance embedding", who);
+  if (h && h->rot_mode && rotation_id(h, r->camera_idx) < 0)
+    return fail(NEMIT_E_INVALID, "%s: camera_idx has no rotation transform (nemit_set_rotater)", who);
   if (!(r->anneal > 0.f)) return fail(NEMIT_E_INVALID, "%s: anneal must be > 0", who);
   if (r->layout != NEMIT_RAYS_MITSUBA_3N && r->layout != NEMIT_RAYS_NERF_N3)
     return fail(NEMIT_E_INVALID, "%s: unknown ray layout", who);
@@ -359,7 +393,17 @@ struct ChunkEdges {
 static int chunk_edges(NemitHandle* h, const ModelDev& M, const NemitRays* rays, int64_t off, int64_t n, char* ws,
                        const struct WsLayout& L, bool need_s1, cudaStream_t st, ChunkEdges* out);
 
-static void fill_ray_args(const NemitHandle* h, RayArgs& A, const NemitRays* r, int64_t off, int64_t n) {
+// rotate: whether THIS stage's samples go through Rotater.apply_frustums (see nemit_set_rotater in nemit.h)
+static void fill_ray_args(const NemitHandle* h, RayArgs& A, const NemitRays* r, int64_t off, int64_t n, bool rotate = false) {
+  A.rot.mode = 0;
+  if (rotate && h->rot_mode) {
+    const int id = rotation_id(h, r->camera_idx);
+    if (id >= 0) {
+      A.rot.mode = h->rot_mode;
+      memcpy(A.rot.m, h->rot_transforms + 12 * (size_t)id, sizeof(float) * 12);
+      memcpy(A.rot.b, h->rot_bound, sizeof(float) * 6);
+    }
+  }
   A.o = r->o; A.v = r->v; A.near_per_ray = r->near_per_ray; A.near_scalar = r->near_scalar;
   A.n_total = r->n; A.ray_offset = off; A.n = n; A.training = r->training;
   appearance_row(h, r->training, r->camera_idx, true, &A.app_row);
@@ -368,7 +412,7 @@ static void fill_ray_args(const NemitHandle* h, RayArgs& A, const NemitRays* r, 
 
 static void fill_sample_args(const NemitHandle* h, SampleArgs& S, const NemitRays* r, int64_t off, int64_t n) {
   memset(&S, 0, sizeof(S));
-  fill_ray_args(h, S, r, off, n);
+  fill_ray_args(h, S, r, off, n, true);          // every proposal level's samples are rotated
   for (int i = 0; i < 2; ++i) {
     S.prop_table[i] = reinterpret_cast<const float2*>(h->P.prop_table[i]);
     S.prop_w0[i] = h->P.prop_w0[i]; S.prop_b0[i] = h->P.prop_b0[i];
@@ -460,7 +504,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     }
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(h, F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n, true);
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges;
     F.rgb = rgb + off * 3;
@@ -640,7 +684,7 @@ extern "C" int nemit_jvp(NemitHandle* h, const NemitRays* rays, const float* d_o
     cudaError_t e;
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(h, F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n, true);
     fill_field_params(h->P, F.P);
     F.t_edges2 = E.t_edges2;
     F.d_o = d_o; F.d_v = d_v;
@@ -841,7 +885,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     const float* s_edges = E.s_edges2;
     FieldArgs F;
     memset(&F, 0, sizeof(F));
-    fill_ray_args(h, F, rays, off, n);
+    fill_ray_args(h, F, rays, off, n, true);
     fill_field_params(h->P, F.P);
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.reg_chunk = rays->n;
     F.point_lights = 1;
@@ -862,7 +906,7 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     if ((e = cudaMemsetAsync(ray_grad, 0, sizeof(float) * 6 * (size_t)n, st)) != cudaSuccess) return cuda_fail(e, "memset ray_grad");
     FieldBwdArgs B;
     memset(&B, 0, sizeof(B));       // B.G stays null: ray gradients only
-    fill_ray_args(h, B, rays, off, n);
+    fill_ray_args(h, B, rays, off, n, true);
     fill_field_params(h->P, B.P);
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = 1.f;
     if (tc) {
@@ -880,6 +924,9 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
     memset(&Z, 0, sizeof(Z));
     fill_ray_args(h, Z, rays, off, n);
     Z.ray_grad = ray_grad; Z.grad_o = brightness_grad; Z.grad_v = nullptr;
+    // brightness_grad = d / d ray_bundle.origins (nerfacto.py:565-568): the op's near change of variables
+    // (o.grad -= near * v.grad, nerf_emitter_op.py:112) does not belong to this pass
+    Z.near_per_ray = nullptr; Z.near_scalar = 0.f;
     if ((e = timed_launch(h, NEMIT_K_FINALIZE, st, n, [&] { return launch_finalize_ray_grads(M, Z, st); })) != cudaSuccess) return cuda_fail(e, "k_finalize_ray_grads");
   }
   return NEMIT_OK;

@@ -157,9 +157,11 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
       t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
     }
     const float tsum = add_rn(t0, t1);
-    float x[3], p[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) x[k] = sample_pos(o[k], d[k], tsum);
+    float x[3], p[3], dirq[3];
+    // Rotater.apply_frustums only where the reference's reverse pass sees rotated final samples: the light-point-cloud
+    // pass (calc_brightness_grad, NS/models/nerfacto.py:547-556); get_backward_outputs puts the unrotated rays back
+    // (NS/models/sdf_nerfacto.py:129-131).  The host sets A.rot accordingly.
+    const bool rotated = rot_sample(A.rot, o, d, tsum, x, dirq);
     const bool sel = contract_normalise(x, M, p);
     // ---- forward recompute, activations kept ----------------------------------------------
     main_encode_to_tile(p, A.P.main_table, M.main_grid, sm->enc, tid);
@@ -171,7 +173,7 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
     const float raw = sm->in[15 * kTileM + tid];
     {
       float c[16];
-      sh16((d[0] + 1.f) * 0.5f, (d[1] + 1.f) * 0.5f, (d[2] + 1.f) * 0.5f, c);
+      sh16((dirq[0] + 1.f) * 0.5f, (dirq[1] + 1.f) * 0.5f, (dirq[2] + 1.f) * 0.5f, c);
 #pragma unroll
       for (int k = 0; k < 16; ++k) sm->in[k * kTileM + tid] = c[k];
       sm->in[31 * kTileM + tid] = 0.f;
@@ -271,6 +273,11 @@ k_field_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Fie
       if (sel) {
         float gx[3];
         contract_vjp(x, sel, gp, gx);
+        if (rotated) {            // x = R (o + d t) + t0: the cotangent goes back through R^T
+          float gr[3];
+          rot_transpose(A.rot, gx, gr);
+          gx[0] = gr[0]; gx[1] = gr[1]; gx[2] = gr[2];
+        }
         const float tm = tsum * 0.5f;
         float* rg = A.ray_grad + rr * 6;
 #pragma unroll

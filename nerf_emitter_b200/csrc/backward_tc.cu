@@ -405,9 +405,9 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       seed = __ldcs(A.seeds4 + s);
     }
     const float tsum = add_rn(t0, t1);
-    float x[3], p[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) x[k] = sample_pos(o[k], d[k], tsum);
+    float x[3], p[3], dirq[3];
+    // Rotater.apply_frustums where the reverse pass sees rotated final samples (the light-point-cloud pass only, see backward.cu)
+    const bool rotated = rot_sample(A.rot, o, d, tsum, x, dirq);
     const bool sel = contract_normalise(x, M, p);
 
     // d loss / d (rgb pre-activation): 3 of 16 columns
@@ -522,6 +522,11 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       if (valid && sel) {
         float gx[3];
         contract_vjp(x, sel, gp, gx);
+        if (rotated) {
+          float gr[3];
+          rot_transpose(A.rot, gx, gr);
+          gx[0] = gr[0]; gx[1] = gr[1]; gx[2] = gr[2];
+        }
         const float tmid = tsum * 0.5f;
 #pragma unroll
         for (int k = 0; k < 3; ++k) { v6[k] = gx[k]; v6[3 + k] = gx[k] * tmid; }

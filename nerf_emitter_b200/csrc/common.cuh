@@ -100,6 +100,46 @@ __device__ __forceinline__ float sample_pos(float o, float d, float tsum) {
   return add_rn(o, mul_rn(mul_rn(d, tsum), 0.5f));
 }
 
+// Rotater.apply_frustums (NS/field_components/rotater.py:125-149, hooked into RayBundle.get_ray_samples at
+// NS/cameras/rays.py:285-286): per SAMPLE, if the sample's unrotated position lies inside the rotation bound (sphere around
+// the scene centre, or an axis-aligned box), the sample takes the rotated ray's origin and direction
+// (batch_affine_left, NS/utils/mi_gl_conversion.py:69-73).  Passed by value inside the kernels' argument blocks.
+struct RotArgs {
+  int mode;        // 0 = no rotation, 1 = bounding sphere, 2 = axis-aligned box
+  float m[12];     // 3 x 4 row-major [R | t] of the call's rotation, NeRF coordinates (Rotater.torch_transforms[id, :3, :4])
+  float b[6];      // sphere: centre xyz, radius; box: min xyz, max xyz (inclusive, rotater.py:129-130)
+};
+
+// position x and direction dir of the sample at t = tsum / 2 on the ray (o, d); returns true when it was rotated
+__device__ __forceinline__ bool rot_sample(const RotArgs& Q, const float o[3], const float d[3], float tsum, float x[3],
+                                           float dir[3]) {
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { x[k] = add_rn(o[k], mul_rn(mul_rn(d[k], tsum), 0.5f)); dir[k] = d[k]; }
+  if (Q.mode == 0) return false;
+  bool inside;
+  if (Q.mode == 1) {
+    const float a = x[0] - Q.b[0], b = x[1] - Q.b[1], c = x[2] - Q.b[2];
+    inside = sqrtf(a * a + b * b + c * c) < Q.b[3];
+  } else {
+    inside = Q.b[0] <= x[0] && x[0] <= Q.b[3] && Q.b[1] <= x[1] && x[1] <= Q.b[4] && Q.b[2] <= x[2] && x[2] <= Q.b[5];
+  }
+  if (!inside) return false;
+  float o2[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    o2[i] = Q.m[4 * i] * o[0] + Q.m[4 * i + 1] * o[1] + Q.m[4 * i + 2] * o[2] + Q.m[4 * i + 3];
+    dir[i] = Q.m[4 * i] * d[0] + Q.m[4 * i + 1] * d[1] + Q.m[4 * i + 2] * d[2];
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) x[k] = add_rn(o2[k], mul_rn(mul_rn(dir[k], tsum), 0.5f));
+  return true;
+}
+// transpose of the rotation: cotangent of a rotated sample's origin / direction back to the ray's
+__device__ __forceinline__ void rot_transpose(const RotArgs& Q, const float g[3], float out[3]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) out[i] = Q.m[i] * g[0] + Q.m[4 + i] * g[1] + Q.m[8 + i] * g[2];
+}
+
 // SceneContraction(order=inf) + (x+2)/4 + selector (NS/field_components/spatial_distortions.py:67-70,
 // NS/fields/density_fields.py:96-106, NS/data/scene_box.py:36-37). Returns selector; p is zeroed when
 // the selector is false (density_fields.py:106).

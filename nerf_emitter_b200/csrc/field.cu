@@ -56,9 +56,8 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
       const int rr = s / kS2, si = s % kS2;
       const float t0 = sm->t_edge[rr * (kS2 + 1) + si], t1 = sm->t_edge[rr * (kS2 + 1) + si + 1];
       const float tsum = add_rn(t0, t1);
-      float x[3], p[3];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) x[k] = sample_pos(sm->ray_o[rr * 3 + k], sm->ray_d[rr * 3 + k], tsum);
+      float x[3], p[3], dirq[3];
+      rot_sample(A.rot, &sm->ray_o[rr * 3], &sm->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       main_encode_to_tile(p, A.P.main_table, M.main_grid, sm->bufA, tid);
       __syncthreads();
@@ -72,8 +71,7 @@ k_field_forward(const __grid_constant__ ModelDev M, const __grid_constant__ Fiel
         sm->sigma[s] = sel ? expf(raw) : 0.f;       // trunc_exp * selector
         float c[16];
         // SH at (d+1)/2 (NS/fields/base_field.py:146-152)
-        sh16((sm->ray_d[rr * 3 + 0] + 1.f) * 0.5f, (sm->ray_d[rr * 3 + 1] + 1.f) * 0.5f,
-             (sm->ray_d[rr * 3 + 2] + 1.f) * 0.5f, c);
+        sh16((dirq[0] + 1.f) * 0.5f, (dirq[1] + 1.f) * 0.5f, (dirq[2] + 1.f) * 0.5f, c);
 #pragma unroll
         for (int k = 0; k < 16; ++k) sm->bufA[k * kTileM + tid] = c[k];
         sm->bufA[31 * kTileM + tid] = 0.f;      // pad row of the K=32 head GEMM

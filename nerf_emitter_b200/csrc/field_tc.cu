@@ -154,9 +154,8 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       const int rr = s / kS2, si = s % kS2;
       const float t0 = sm->t_edge[rr * (kS2 + 1) + si], t1 = sm->t_edge[rr * (kS2 + 1) + si + 1];
       const float tsum = add_rn(t0, t1);
-      float x[3], p[3];
-#pragma unroll
-      for (int k = 0; k < 3; ++k) x[k] = sample_pos(sm->ray_o[rr * 3 + k], sm->ray_d[rr * 3 + k], tsum);
+      float x[3], p[3], dirq[3];
+      rot_sample(A.rot, &sm->ray_o[rr * 3], &sm->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
       // ---- hash encoding: 4 levels = 8 values = one 16-byte K-chunk of this thread's A row ------------
@@ -207,8 +206,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         const float raw = v[0] + sm->bias_b1[0];
         sm->sigma[s] = sel ? expf(raw) : 0.f;                         // trunc_exp * selector, fp32
         float c[16];
-        sh16((sm->ray_d[rr * 3 + 0] + 1.f) * 0.5f, (sm->ray_d[rr * 3 + 1] + 1.f) * 0.5f,
-             (sm->ray_d[rr * 3 + 2] + 1.f) * 0.5f, c);
+        sh16((dirq[0] + 1.f) * 0.5f, (dirq[1] + 1.f) * 0.5f, (dirq[2] + 1.f) * 0.5f, c);
         uint32_t w[4];
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {

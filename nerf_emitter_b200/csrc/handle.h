@@ -23,6 +23,11 @@ struct NemitHandle {
   int always_use_camera_indices, use_average_embedding;
   int32_t* rotation_ids;    // host copy of Rotater.rotation_ids, or null
   int32_t num_rotation_ids;
+  // nemit_set_rotater: Rotater.apply_frustums (bound + one 3x4 transform per rotation id), host copies
+  int rot_mode;             // 0 = none, NEMIT_ROT_SPHERE, NEMIT_ROT_BOX
+  int num_rotations;
+  float* rot_transforms;    // num_rotations x 12
+  float rot_bound[6];
   NemitParams P, G;
   int64_t launches;
   int precision;

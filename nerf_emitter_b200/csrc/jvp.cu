@@ -103,12 +103,12 @@ k_field_jvp(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArg
       const int rr = s / kS2, si = s % kS2;
       const float t0 = sm->t_edge[rr * (kS2 + 1) + si], t1 = sm->t_edge[rr * (kS2 + 1) + si + 1];
       const float tsum = add_rn(t0, t1);
-      float x[3], p[3], dx[3], dp[3];
+      float x[3], p[3], dx[3], dp[3], dirq[3];
+      // primal: Rotater.apply_frustums when set; the tangents stay those of the unrotated ray - forward_grad attaches them
+      // to the already rotated frustums (NS/models/sdf_nerfacto.py:96-104)
+      rot_sample(A.rot, &sm->ray_o[rr * 3], &sm->ray_d[rr * 3], tsum, x, dirq);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        x[k] = sample_pos(sm->ray_o[rr * 3 + k], sm->ray_d[rr * 3 + k], tsum);
-        dx[k] = sm->ray_do[rr * 3 + k] + sm->ray_dd[rr * 3 + k] * (tsum * 0.5f);
-      }
+      for (int k = 0; k < 3; ++k) dx[k] = sm->ray_do[rr * 3 + k] + sm->ray_dd[rr * 3 + k] * (tsum * 0.5f);
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       contract_jvp(x, sel, dx, dp);
       main_encode_dual_to_tile(p, dp, A.P.main_table, M.main_grid, sm->bufA, sm->dA, tid);
@@ -124,8 +124,7 @@ k_field_jvp(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArg
         sm->sigma[s] = sel ? expf(raw) : 0.f;
         sm->dsigma[s] = sel ? expf(fminf(fmaxf(raw, -15.f), 15.f)) * draw : 0.f;   // _TruncExp.jvp
         float c[16], ct[16];
-        const float qx = (sm->ray_d[rr * 3 + 0] + 1.f) * 0.5f, qy = (sm->ray_d[rr * 3 + 1] + 1.f) * 0.5f,
-                    qz = (sm->ray_d[rr * 3 + 2] + 1.f) * 0.5f;
+        const float qx = (dirq[0] + 1.f) * 0.5f, qy = (dirq[1] + 1.f) * 0.5f, qz = (dirq[2] + 1.f) * 0.5f;
         sh16(qx, qy, qz, c);
         // forward-mode tangents do flow through the no_grad SH
         sh16_tangent(qx, qy, qz, sm->ray_dd[rr * 3 + 0] * 0.5f, sm->ray_dd[rr * 3 + 1] * 0.5f,

@@ -31,6 +31,8 @@ struct RayArgs {
   const float* jitter;   // (n_total,3) or null
   float anneal;
   int nerf_layout;       // NemitRays.layout: 0 = (3,N) Mitsuba unit cube, 1 = (N,3) NeRF coordinates (also for tangents / ray grads)
+  RotArgs rot;           // Rotater.apply_frustums for the samples THIS launch evaluates (mode 0 = off); set per stage by the
+                         // host: the sampler stages always rotate, the final-sample stage only where the reference does
 };
 // the scene_scale argument of load_ray; 0 selects the (N,3) NeRF-coordinate layout
 __host__ __device__ inline float ray_scale(const ModelDev& M, const RayArgs& A) { return A.nerf_layout ? 0.f : M.scene_scale; }

@@ -65,7 +65,7 @@ __device__ __forceinline__ float prop_mlp_hidden(const float enc[kPropEnc], cons
 static __device__ __noinline__ void prop_level_backward(PbWarp* pw, const RayCtx& R, int S, const float2* __restrict__ table,
                                                  float2* __restrict__ g_table, const GridDev& G,
                                                  const PropMlpSmem* W, const ModelDev& M, float coef, float loss_scale,
-                                                 float (&acc)[kAccPerLane], int lane) {
+                                                 float (&acc)[kAccPerLane], int lane, const RotArgs& Q) {
   WarpScratch* sc = &pw->sc;
   // cumulative proposal weights cy[0..S] (losses.py:66) and a zeroed difference array
   float carry = 0.f;
@@ -134,7 +134,8 @@ static __device__ __noinline__ void prop_level_backward(PbWarp* pw, const RayCtx
     float gs = pw->gw[i];
     float t0 = s_to_t(sc->s_edge[i], R.s_near, R.s_far), t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
     float tsum = add_rn(t0, t1);
-    float x[3] = {sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum), sample_pos(R.o[2], R.d[2], tsum)};
+    float x[3], dirq[3];
+    rot_sample(Q, R.o, R.d, tsum, x, dirq);       // the proposal samples are rotated like every level's (rays.py:285-286)
     float p[3];
     bool sel = contract_normalise(x, M, p);
     bool live = sel && gs != 0.f;
@@ -242,10 +243,11 @@ k_prop_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Prop
 #pragma unroll 1
     for (int lvl = 0; lvl < 2; ++lvl) {
       const int S = lvl == 0 ? kS0 : kS1;
-      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane, pw->ds);
+      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane, pw->ds, nullptr,
+                             A.rot.mode ? &A.rot : nullptr);
       if (lvl == 0) {
         prop_level_backward(pw, R, S, A.prop_table[0], A.g_table[0], M.prop_grid[0], &sm->mlp[0], M, coef,
-                            A.loss_scale, acc[0], lane);
+                            A.loss_scale, acc[0], lane, A.rot);
         __syncwarp();
         // level-1 edges: the ones the sampling pass of this call produced (so the proposal histogram bounded here is the
         // one the final samples were drawn from, whichever sampler arithmetic ran), not a second PDF stage
@@ -253,7 +255,7 @@ k_prop_backward(const __grid_constant__ ModelDev M, const __grid_constant__ Prop
         __syncwarp();
       } else {
         prop_level_backward(pw, R, S, A.prop_table[1], A.g_table[1], M.prop_grid[1], &sm->mlp[1], M, coef,
-                            A.loss_scale, acc[1], lane);
+                            A.loss_scale, acc[1], lane, A.rot);
         __syncwarp();
       }
     }

@@ -44,7 +44,8 @@ k_sample_levels(const __grid_constant__ ModelDev M, const __grid_constant__ Samp
     for (int lvl = 0; lvl < 2; ++lvl) {
       const int S = lvl == 0 ? kS0 : kS1;          // bins at this level
       const int Mn = lvl == 0 ? kS1 : kS2;         // samples of the next level
-      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane, nullptr, A.prop_table_h[lvl]);
+      proposal_level_weights(sc, R, S, A.prop_table[lvl], M.prop_grid[lvl], &sm->mlp[lvl], M, lane, nullptr, A.prop_table_h[lvl],
+                             A.rot.mode ? &A.rot : nullptr);
       float* w_out = lvl == 0 ? A.weights0 : A.weights1;
       if (w_out) {
         for (int i = lane; i < S; i += 32) w_out[r * S + i] = sc->buf[i];

@@ -257,7 +257,8 @@ template <class MLP = PropMlpSmem>
 __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const RayCtx& R, int S,
                                                        const float2* __restrict__ table, const GridDev& G,
                                                        const MLP* W, const ModelDev& M, int lane,
-                                                       float* ds_out = nullptr, const uint32_t* __restrict__ table_h = nullptr) {
+                                                       float* ds_out = nullptr, const uint32_t* __restrict__ table_h = nullptr,
+                                                       const RotArgs* Q = nullptr) {
   constexpr bool kFast = !cuda::std::is_same<MLP, PropMlpSmem>::value;
 #pragma unroll 1
   for (int i = lane; i < S; i += 32) {
@@ -265,12 +266,16 @@ __device__ __forceinline__ void proposal_level_weights(WarpScratch* sc, const Ra
     float t1 = s_to_t(sc->s_edge[i + 1], R.s_near, R.s_far);
     float tsum = add_rn(t0, t1);
     float sigma;
+    float x[3], dir[3];
+    if (Q) rot_sample(*Q, R.o, R.d, tsum, x, dir);      // Rotater.apply_frustums: every level's samples (rays.py:285-286)
+    else {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) x[k] = sample_pos(R.o[k], R.d[k], tsum);
+    }
     if constexpr (kFast)
-      sigma = prop_density_fast(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
-                                sample_pos(R.o[2], R.d[2], tsum), table_h, G, W, M);
+      sigma = prop_density_fast(x[0], x[1], x[2], table_h, G, W, M);
     else
-      sigma = prop_density(sample_pos(R.o[0], R.d[0], tsum), sample_pos(R.o[1], R.d[1], tsum),
-                           sample_pos(R.o[2], R.d[2], tsum), table, G, W, M);
+      sigma = prop_density(x[0], x[1], x[2], table, G, W, M);
     sc->buf[i] = mul_rn(sub_rn(t1, t0), sigma);
     if (ds_out) ds_out[i] = sc->buf[i];
   }

@@ -213,6 +213,32 @@ class NerfEmitter:
         self.rotation_ids = ids
         return self
 
+    def set_rotater(self, transforms=None, center=None, radius=None, aabb=None):
+        """Per-sample frustum rotation of turntable captures, ``Rotater.apply_frustums`` (NS/field_components/rotater.py:
+        125-149).  ``transforms``: (R, 4, 4) or (R, 3, 4) = ``Rotater.get_torch_transforms(arange(R))`` in NeRF
+        coordinates; the bound is the sphere (``center`` (3,), ``radius``; the reference's default: the scene centre and
+        sqrt(3) * scene_scale, rotater.py:64-66) or the box ``aabb`` (2,3).  ``transforms=None`` removes it.  Which
+        stages rotate follows the reference (include/nemit.h, nemit_set_rotater)."""
+        if transforms is None:
+            L.check(self.lib.nemit_set_rotater(self._h, 0, None, 0, None), "nemit_set_rotater")
+            self.rotater = None
+            return self
+        T = torch.as_tensor(transforms, dtype=torch.float32).cpu()[:, :3, :4].contiguous()
+        if aabb is not None:
+            b = torch.as_tensor(aabb, dtype=torch.float32).reshape(6)
+            kind = 2
+        else:
+            if center is None or radius is None:
+                raise ValueError("set_rotater needs either (center, radius) or aabb")
+            b = torch.cat([torch.as_tensor(center, dtype=torch.float32).reshape(3), torch.tensor([float(radius)]),
+                           torch.zeros(2)])
+            kind = 1
+        b = b.contiguous()
+        L.check(self.lib.nemit_set_rotater(self._h, T.shape[0], C.cast(T.data_ptr(), L.c_float_p), kind,
+                                           C.cast(b.data_ptr(), L.c_float_p)), "nemit_set_rotater")
+        self.rotater = dict(transforms=T, bound=b, kind=kind)
+        return self
+
     def train(self, mode: bool = True):
         self.training = bool(mode)
         return self

@@ -92,6 +92,7 @@ SYMBOLS = {
                                            C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                            C.c_void_p, C.c_void_p, C.c_void_p]),
     "nemit_set_appearance_mode": (C.c_int, [_H, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.c_int32]),
+    "nemit_set_rotater": (C.c_int, [_H, C.c_int32, C.POINTER(C.c_float), C.c_int32, C.POINTER(C.c_float)]),
     "nemit_bind_params": (C.c_int, [_H, C.POINTER(NemitParams)]),
     "nemit_bind_grads": (C.c_int, [_H, C.POINTER(NemitParams)]),
     "nemit_set_precision": (C.c_int, [_H, C.c_int32]),

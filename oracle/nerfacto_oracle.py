@@ -222,12 +222,37 @@ def pdf_resample(w, s_edges, num_new: int, jitter: Optional[torch.Tensor], pad: 
 
 
 # --------------------------------------------------------------------------------------------
+# A3  Rotater.apply_frustums (turntable captures)
+# --------------------------------------------------------------------------------------------
+def apply_frustums(rot, o, d, t_edges):
+    """nerfstudio/field_components/rotater.py:125-149 (get_rotation_mask + apply_frustums) with batch_affine_left
+    (nerfstudio/utils/mi_gl_conversion.py:69-73), as hooked into RayBundle.get_ray_samples (cameras/rays.py:285-286).
+    RESTATED: rotater.py imports mitsuba at module scope and cannot be imported here; these are its 15 lines of torch.
+    rot: None or dict(T (4,4) of the call's rotation id, kind 'sphere' | 'box', center (3,), radius, aabb (2,3)).
+    o, d (N,3); t_edges (N,S+1).  Returns per-sample origins and directions (N,S,3)."""
+    t0, t1 = t_edges[..., :-1, None], t_edges[..., 1:, None]
+    S = t0.shape[1]
+    o_s, d_s = o[:, None, :].expand(-1, S, -1), d[:, None, :].expand(-1, S, -1)
+    if rot is None:
+        return o_s, d_s
+    pos = o_s + d_s * (t0 + t1) / 2                                # Frustums.get_positions, cameras/rays.py:49-58
+    if rot["kind"] == "sphere":
+        mask = torch.linalg.norm(pos - rot["center"], dim=-1, keepdim=True) < rot["radius"]
+    else:
+        mask = ((rot["aabb"][0] <= pos).all(dim=-1, keepdim=True) & (pos <= rot["aabb"][1]).all(dim=-1, keepdim=True))
+    T = rot["T"]
+    o2 = (T[:3, :3] @ o.unsqueeze(-1))[..., 0] + T[:3, 3]
+    d2 = (T[:3, :3] @ d.unsqueeze(-1))[..., 0]
+    return torch.where(mask, o2[:, None, :].expand(-1, S, -1), o_s), torch.where(mask, d2[:, None, :].expand(-1, S, -1), d_s)
+
+
+# --------------------------------------------------------------------------------------------
 # A9  the three-level proposal loop
 # --------------------------------------------------------------------------------------------
 def sample_levels(P, spec: EmitterModelSpec, o, d, near: float, far: float, aabb, *,
                   disable_inside_aabb=True, jitter: Optional[Sequence[torch.Tensor]] = None,
                   anneal: float = 1.0, proposal_requires_grad: bool = False,
-                  edges_override: Optional[Sequence[Optional[torch.Tensor]]] = None):
+                  edges_override: Optional[Sequence[Optional[torch.Tensor]]] = None, rot=None):
     """nerfstudio/model_components/ray_samplers.py:584-626.  o, d (N,3) NeRF coords (detached by
     the caller for the backward variant, sdf_nerfacto.py:121-126).  Returns per-level spacing edges,
     euclidean edges, weights and the searchsorted indices.
@@ -257,7 +282,8 @@ def sample_levels(P, spec: EmitterModelSpec, o, d, near: float, far: float, aabb
         out["t_edges"].append(t_e)
         if lvl < 2:
             t0, t1 = t_e[..., :-1, None], t_e[..., 1:, None]
-            pos = o[:, None, :] + d[:, None, :] * (t0 + t1) / 2       # cameras/rays.py:49-58
+            o_s, d_s = apply_frustums(rot, o, d, t_e)                 # every level's get_ray_samples runs the hook
+            pos = o_s + d_s * (t0 + t1) / 2                           # cameras/rays.py:49-58
             with torch.set_grad_enabled(proposal_requires_grad and torch.is_grad_enabled()):
                 sig = proposal_density(P, lvl, spec.prop_grids[lvl], pos, aabb, disable_inside_aabb)
                 wfull = weights_from_density(sig, t1 - t0)
@@ -294,15 +320,18 @@ def sh16(v):
 # --------------------------------------------------------------------------------------------
 def main_stage(P, spec: EmitterModelSpec, o, d, t_edges, aabb, *, training: bool, camera_idx: int,
                disable_inside_aabb=True, sh_carries_reverse_grad=False, grad_scaling=True,
-               always_use_camera_indices=False):
+               always_use_camera_indices=False, o_s=None, d_s=None):
     """nerfstudio/fields/nerfacto_field.py:228-334 (get_density, get_outputs), Field.forward
     (base_field.py:124-143), scale_gradients_by_distance_squared (losses.py:558-577),
     get_weights (cameras/rays.py:128-150), RGBRenderer (model_components/renderers.py:71-121,203-234).
-    o, d (N,3); t_edges (N,49).  Returns rgb (N,3), weights (N,48,1), per-sample density and rgb."""
+    o, d (N,3); t_edges (N,49).  Returns rgb (N,3), weights (N,48,1), per-sample density and rgb.
+    o_s, d_s (N,48,3): per-sample frustum origins / directions when a Rotater has rewritten them (apply_frustums)."""
     N = o.shape[0]
     t0, t1 = t_edges[..., :-1, None], t_edges[..., 1:, None]
     S = t0.shape[1]
-    pos = o[:, None, :] + d[:, None, :] * (t0 + t1) / 2
+    if o_s is None:
+        o_s, d_s = o[:, None, :].expand(N, S, 3), d[:, None, :].expand(N, S, 3)
+    pos = o_s + d_s * (t0 + t1) / 2
     p, sel = normalised_positions(pos, aabb, disable_inside_aabb)
     enc = hash_encode(p.view(-1, 3), P["field.mlp_base_grid.hash_table"], spec.main_grid)
     h = F.relu(F.linear(enc, P["field.mlp_base_mlp.layers.0.weight"], P["field.mlp_base_mlp.layers.0.bias"]))
@@ -311,7 +340,7 @@ def main_stage(P, spec: EmitterModelSpec, o, d, t_edges, aabb, *, training: bool
     raw_sigma, geo = torch.split(h, [1, spec.geo_feat_dim], dim=-1)
     sigma = trunc_exp(raw_sigma) * sel[..., None]
 
-    dn = (d[:, None, :].expand(N, S, 3) + 1.0) / 2.0
+    dn = (d_s + 1.0) / 2.0
     # encodings.py:708 decorates the torch SH with no_grad: no reverse-mode gradient reaches the
     # directions through SH, while forward-mode tangents do flow (no_grad does not stop them).
     sh = sh16(dn if sh_carries_reverse_grad else _no_reverse(dn)).reshape(-1, 16)
@@ -395,7 +424,9 @@ class OracleEmitter:
     def __init__(self, params: Dict[str, torch.Tensor], spec: Optional[EmitterModelSpec] = None,
                  scene_scale: float = 1.0, disable_inside_aabb: bool = True,
                  interlevel_mult: float = 1.0, distortion_mult: float = 7e-3,
-                 always_use_camera_indices: bool = False, rotation_ids=None):
+                 always_use_camera_indices: bool = False, rotation_ids=None, rotater=None):
+        # rotater: None or dict(transforms (R,4,4), kind 'sphere' | 'box', center, radius, aabb) = the Rotater's buffers
+        self.rotater = rotater
         # a model built with a Rotater has always_use_camera_indices=True and one embedding row per rotation
         # (nerfstudio/models/nerfacto.py:186-206); rotation_ids = Rotater.rotation_ids
         self.always_use_camera_indices = always_use_camera_indices
@@ -420,13 +451,21 @@ class OracleEmitter:
             return camera_idx
         return self.rotation_ids[min(camera_idx, len(self.rotation_ids) - 1)]
 
+    def _rot(self, camera_idx):
+        """The call's rotation (Rotater.get_torch_transforms(map_rotation_ids(camera_indices)), rotater.py:74-100)."""
+        if self.rotater is None:
+            return None
+        r = dict(self.rotater)
+        r["T"] = torch.as_tensor(self.rotater["transforms"], dtype=torch.float32)[self._cam(camera_idx)]
+        return r
+
     def _near_plane(self):
         # NearFarCollider (scene_colliders.py:217-222): 0 in eval mode
         return self.spec.near_plane if self.training else 0.0
 
-    def _levels(self, o, d, jitter, proposal_requires_grad=False):
+    def _levels(self, o, d, jitter, proposal_requires_grad=False, camera_idx=0):
         return sample_levels(self.P, self.spec, o, d, self._near_plane(), self.spec.far_plane, self.aabb,
-                             disable_inside_aabb=self.disable_inside_aabb,
+                             rot=self._rot(camera_idx), disable_inside_aabb=self.disable_inside_aabb,
                              jitter=jitter if self.training else None, anneal=self.anneal,
                              proposal_requires_grad=proposal_requires_grad,
                              edges_override=getattr(self, "edges_override", None))
@@ -436,11 +475,12 @@ class OracleEmitter:
         o = o3n.t().contiguous()
         v = v3n.t().contiguous()
         o, d = rays_mi_to_nerf(o + near * v, v, self.scene_scale)
-        lv = self._levels(o, d, jitter)
+        lv = self._levels(o, d, jitter, camera_idx=camera_idx)
+        o_s, d_s = apply_frustums(self._rot(camera_idx), o, d, lv["t_edges"][2])
         rgb, w, sigma, rgb_s = main_stage(self.P, self.spec, o, d, lv["t_edges"][2], self.aabb,
                                           training=self.training, camera_idx=self._cam(camera_idx),
                                           always_use_camera_indices=self.always_use_camera_indices,
-                                          disable_inside_aabb=self.disable_inside_aabb)
+                                          disable_inside_aabb=self.disable_inside_aabb, o_s=o_s, d_s=d_s)
         if not return_aux:
             return rgb
         N = o.shape[0]
@@ -461,13 +501,21 @@ class OracleEmitter:
         go = do3n.t().contiguous() + near * dv3n.t().contiguous()
         gv = dv3n.t().contiguous()
         on, dn = rays_mi_to_nerf(o, v, self.scene_scale)
-        lv = self._levels(on, dn, jitter)
+        lv = self._levels(on, dn, jitter, camera_idx=camera_idx)
         with forward_ad.dual_level():
             od, dd = rays_mi_to_nerf(forward_ad.make_dual(o, go), forward_ad.make_dual(v, gv), self.scene_scale)
+            o_s = d_s = None
+            if self.rotater is not None:
+                # sdf_nerfacto.py:96-104: the tangents are attached to the frustums the sampler returned, i.e. to the
+                # already rotated per-sample origins / directions; the tangents themselves stay those of the ray
+                po, pd = apply_frustums(self._rot(camera_idx), on, dn, lv["t_edges"][2])
+                to, td = forward_ad.unpack_dual(od).tangent, forward_ad.unpack_dual(dd).tangent
+                o_s = forward_ad.make_dual(po.contiguous(), to[:, None, :].expand_as(po).contiguous())
+                d_s = forward_ad.make_dual(pd.contiguous(), td[:, None, :].expand_as(pd).contiguous())
             rgb, _, _, _ = main_stage(self.P, self.spec, od, dd, lv["t_edges"][2], self.aabb,
                                       training=self.training, camera_idx=self._cam(camera_idx),
                                       always_use_camera_indices=self.always_use_camera_indices,
-                                      disable_inside_aabb=self.disable_inside_aabb, grad_scaling=False)
+                                      disable_inside_aabb=self.disable_inside_aabb, grad_scaling=False, o_s=o_s, d_s=d_s)
             t = forward_ad.unpack_dual(rgb).tangent
         t = t.clone()
         t[torch.isnan(t)] = 0.
@@ -483,7 +531,10 @@ class OracleEmitter:
             oo = (o3n.t().contiguous() + near * v3n.t().contiguous()).detach().requires_grad_(True)
             vv = v3n.t().contiguous().detach().requires_grad_(True)
             o, d = rays_mi_to_nerf(oo, vv, self.scene_scale)
-            lv = self._levels(o.detach(), d.detach(), jitter, proposal_requires_grad=proposal_requires_grad)
+            # the proposal levels are rotated (the hook runs in every get_ray_samples); the final samples are NOT: the
+            # ray's own origins / directions are put back before the field is evaluated (sdf_nerfacto.py:129-131)
+            lv = self._levels(o.detach(), d.detach(), jitter, proposal_requires_grad=proposal_requires_grad,
+                              camera_idx=camera_idx)
             rgb, w, _, _ = main_stage(P, self.spec, o, d, lv["t_edges"][2], self.aabb, training=self.training,
                                       camera_idx=self._cam(camera_idx), disable_inside_aabb=self.disable_inside_aabb,
                                       always_use_camera_indices=self.always_use_camera_indices)
@@ -511,11 +562,12 @@ class OracleEmitter:
         v = v3n.t().contiguous()
         o, d = rays_mi_to_nerf(o + near * v, v, self.scene_scale)
         o = o.detach().requires_grad_(True)
-        lv = self._levels(o.detach(), d, jitter)
+        lv = self._levels(o.detach(), d, jitter, camera_idx=camera_idx)
         t_edges = lv["t_edges"][2]
+        o_s, d_s = apply_frustums(self._rot(camera_idx), o, d, t_edges)      # calc_brightness_grad, nerfacto.py:553-554
         rgb, w, _, rgb_s = main_stage(self.P, self.spec, o, d, t_edges, self.aabb, training=self.training,
                                       camera_idx=self._cam(camera_idx), disable_inside_aabb=self.disable_inside_aabb,
-                                      always_use_camera_indices=self.always_use_camera_indices)
+                                      always_use_camera_indices=self.always_use_camera_indices, o_s=o_s, d_s=d_s)
         brightness = torch.sum(rgb * wts, dim=-1, keepdim=True)
         (grad,) = torch.autograd.grad(brightness, o, grad_outputs=torch.ones_like(brightness))
         lum = torch.sum(rgb_s.detach() * wts, dim=-1, keepdim=True)

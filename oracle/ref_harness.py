@@ -30,7 +30,13 @@ class ReferenceEmitter:
     def __init__(self, params: Dict[str, torch.Tensor], spec: Optional[EmitterModelSpec] = None,
                  scene_scale: float = 1.0, disable_inside_aabb: bool = True,
                  interlevel_mult: float = 1.0, distortion_mult: float = 7e-3,
-                 always_use_camera_indices: bool = False, rotation_ids=None):
+                 always_use_camera_indices: bool = False, rotation_ids=None, rotater=None):
+        # rotater: None or dict(transforms (R,4,4), kind 'sphere' | 'box', center, radius, aabb): the buffers of a
+        # nerfstudio.field_components.rotater.Rotater.  That module imports mitsuba at module scope and cannot be imported
+        # here, so its apply_frustums / get_rotation_mask (rotater.py:125-149) are RESTATED in _apply_frustums below and
+        # hooked into the reference's own RayBundle.get_ray_samples (cameras/rays.py:285-286) exactly as get_ray_bundle
+        # does (differentiable-sdf-rendering/python/emitters/nerf_op.py:86-87).
+        self.rotater = rotater
         # always_use_camera_indices / rotation_ids: the model as NerfactoModel.populate_modules builds it when the
         # datamanager carries a Rotater (nerfacto.py:186-206).  The Rotater class itself imports mitsuba at module
         # scope (rotater.py:7), so its three-line map_rotation_ids (:94-100) is repeated in _map_rotation_ids below.
@@ -105,7 +111,37 @@ class ReferenceEmitter:
         v = v @ MI2GL_LEFT[:3, :3].t()
         rb = self.ns.rays.RayBundle(origins=o, directions=v, pixel_area=torch.ones_like(o[..., :1]))
         rb.set_camera_indices(camera_idx)
+        if self.rotater is not None:
+            rb.rotater = self._apply_frustums
         return rb
+
+    def _apply_frustums(self, frustums, camera_indices):
+        """RESTATEMENT of Rotater.apply_frustums + get_rotation_mask (rotater.py:125-149) with batch_affine_left
+        (nerfstudio/utils/mi_gl_conversion.py:69-73)."""
+        R = self.rotater
+        positions = frustums.get_positions()
+        if R["kind"] == "sphere":
+            rotate_mask = torch.linalg.norm(positions - R["center"], dim=-1, keepdim=True) < R["radius"]
+        else:
+            rotate_mask = ((R["aabb"][0] <= positions).all(dim=-1, keepdim=True) &
+                           (positions <= R["aabb"][1]).all(dim=-1, keepdim=True))
+        ids = camera_indices[..., 0]
+        if self.rotation_ids is not None:
+            ids = self._map_rotation_ids(ids)
+        transforms = torch.as_tensor(R["transforms"], dtype=torch.float32)[ids]
+
+        def batch_affine_left(M, x, is_pos=True):
+            res = (M[..., :3, :3] @ x.unsqueeze(-1))[..., 0]
+            if is_pos:
+                res = res + M[..., :3, 3]
+            return res
+        frustums.origins = torch.where(
+            rotate_mask, batch_affine_left(transforms, frustums.origins[..., :1, :]).expand(frustums.origins.shape),
+            frustums.origins)
+        frustums.directions = torch.where(
+            rotate_mask,
+            batch_affine_left(transforms, frustums.directions[..., :1, :], is_pos=False).expand(frustums.directions.shape),
+            frustums.directions)
 
     def _density_fns(self):
         return [p.density_fn for p in self.props]
@@ -221,6 +257,8 @@ def reference_point_lights(R: "ReferenceEmitter", o3n, v3n, near=0.0, camera_idx
         rb.origins.requires_grad = True
         rs.frustums.origins = rb.origins.unsqueeze(-2).expand_as(rs.frustums.origins)
         rs.frustums.directions = rb.directions.unsqueeze(-2).expand_as(rs.frustums.directions)
+        if rb.rotater is not None:                                # nerfacto.py:553-554
+            rb.rotater(rs.frustums, rb.camera_indices[..., None])
         rgb, weights, out = R._field_and_render(rs)
         brightness = torch.sum(rgb * wts, dim=-1, keepdim=True)
         (grad,) = torch.autograd.grad(brightness, rb.origins, grad_outputs=torch.ones_like(brightness))
