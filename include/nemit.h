@@ -389,6 +389,23 @@ int nemit_vmf_sample(const NemitVmfLobes* lobes, const float* p, const float* u,
 int nemit_vmf_pdf(const NemitVmfLobes* lobes, const float* p, const float* d, int64_t n,
                   float* pdf, void* stream);
 
+/* The same two calls as the emitter makes them, in WORLD space (vMF.py:24-56, 64-81): frame holds world_transform() and its
+ * inverse as 3 x 4 row-major HOST floats (Transform4f.transform_affine: points take the translation, vectors do not) and the
+ * emitter's bounding sphere m_bsphere.  it_p (N,3) world-space reference points.  sample: p = W^-1 it.p, lobe choice and warp
+ * as above, d = normalize(W d_local), ds.pdf = pdf_direction(it, ds), dist = 2 max(r_bsphere, |it.p - c|), ds.p = it.p +
+ * d dist (ds.n = -d, ds.uv = 0, ds.delta = false and the returned weight 0 carry no arithmetic); dist_or_null (N) and
+ * ds_p_or_null (N,3) may be NULL.  pdf: d = normalize(W^-1 ds.d), p = W^-1 it.p. */
+typedef struct NemitVmfFrame {
+  float world_to_local[12];
+  float local_to_world[12];
+  float bsphere_center[3];
+  float bsphere_radius;
+} NemitVmfFrame;
+int nemit_vmf_sample_direction(const NemitVmfLobes* lobes, const NemitVmfFrame* frame, const float* it_p, const float* u,
+                               int64_t n, float* d, float* pdf, float* dist_or_null, float* ds_p_or_null, void* stream);
+int nemit_vmf_pdf_direction(const NemitVmfLobes* lobes, const NemitVmfFrame* frame, const float* it_p, const float* ds_d,
+                            int64_t n, float* pdf, void* stream);
+
 /* end-to-end entry with HOST (pinned) ray and radiance buffers: H2D copy, forward, D2H copy,
  * all queued on `stream`; the device staging lives in the workspace. */
 int nemit_forward_host(NemitHandle* h, const NemitRays* rays_host, float* rgb_host,

@@ -1121,3 +1121,37 @@ extern "C" int nemit_vmf_pdf(const NemitVmfLobes* lobes, const float* p, const f
                                  (cudaStream_t)stream);
   return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_pdf");
 }
+
+static void frame_to_dev(const NemitVmfFrame* f, VmfFrame& F) {
+  memset(&F, 0, sizeof(F));
+  F.on = 1;
+  memcpy(F.w2l, f->world_to_local, sizeof(F.w2l));
+  memcpy(F.l2w, f->local_to_world, sizeof(F.l2w));
+  memcpy(F.centre, f->bsphere_center, sizeof(F.centre));
+  F.radius = f->bsphere_radius;
+}
+extern "C" int nemit_vmf_sample_direction(const NemitVmfLobes* lobes, const NemitVmfFrame* frame, const float* it_p,
+                                          const float* u, int64_t n, float* d, float* pdf, float* dist_or_null,
+                                          float* ds_p_or_null, void* stream) {
+  int rc = check_lobes(lobes, "nemit_vmf_sample_direction");
+  if (rc) return rc;
+  if (!frame) return fail(NEMIT_E_INVALID, "nemit_vmf_sample_direction: null frame%s");
+  if (n < 0 || (n > 0 && (!it_p || !u || !d || !pdf))) return fail(NEMIT_E_INVALID, "nemit_vmf_sample_direction: bad sample arguments%s");
+  VmfFrame F;
+  frame_to_dev(frame, F);
+  cudaError_t e = launch_vmf_sample(lobes->position, lobes->weight, lobes->std, lobes->num_lobes, it_p, u, n, d, pdf,
+                                    (cudaStream_t)stream, &F, dist_or_null, ds_p_or_null);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_sample");
+}
+extern "C" int nemit_vmf_pdf_direction(const NemitVmfLobes* lobes, const NemitVmfFrame* frame, const float* it_p,
+                                       const float* ds_d, int64_t n, float* pdf, void* stream) {
+  int rc = check_lobes(lobes, "nemit_vmf_pdf_direction");
+  if (rc) return rc;
+  if (!frame) return fail(NEMIT_E_INVALID, "nemit_vmf_pdf_direction: null frame%s");
+  if (n < 0 || (n > 0 && (!it_p || !ds_d || !pdf))) return fail(NEMIT_E_INVALID, "nemit_vmf_pdf_direction: bad sample arguments%s");
+  VmfFrame F;
+  frame_to_dev(frame, F);
+  cudaError_t e = launch_vmf_pdf(lobes->position, lobes->weight, lobes->std, lobes->num_lobes, it_p, ds_d, n, pdf,
+                                 (cudaStream_t)stream, &F);
+  return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_pdf");
+}

@@ -5,8 +5,12 @@
 // al. 2017), warp::square_to_von_mises_fisher (concentric-disk warp) and its pdf.  They are restated
 // here from the published Mitsuba 3 sources; parity is pinned only by properties (tests/test_vmf*.py).
 //
-// Everything is in emitter-local coordinates: the caller applies world_transform (vMF.py:25,37,65-67).
+// Without a VmfFrame everything is in emitter-local coordinates; with one the kernels do what the emitter does: it.p and
+// ds.d are world-space, p = W^-1 it.p, d = normalize(W d_local), pdf evaluated at normalize(W^-1 d), and the rest of the
+// DirectionSample (dist = 2 max(r_bsphere, |it.p - c|), ds.p = it.p + d dist) is written too (vMF.py:25,37-50,65-67).
 // One thread per sample; the K lobes (position, 1/std^2, pmf, cdf) live in shared memory.
+#include <cstring>
+
 #include "vmf.h"
 #include "common.cuh"
 
@@ -71,28 +75,45 @@ __device__ __forceinline__ float mixture_pdf(const LobeSmem* L, int K, float px,
   return sum;
 }
 
+// Transform4f::transform_affine of a point / of a vector (3 x 4 row-major)
+__device__ __forceinline__ void xf_point(const float* m, float& x, float& y, float& z) {
+  const float a = m[0] * x + m[1] * y + m[2] * z + m[3], b = m[4] * x + m[5] * y + m[6] * z + m[7],
+              c = m[8] * x + m[9] * y + m[10] * z + m[11];
+  x = a; y = b; z = c;
+}
+__device__ __forceinline__ void xf_vector(const float* m, float& x, float& y, float& z) {
+  const float a = m[0] * x + m[1] * y + m[2] * z, b = m[4] * x + m[5] * y + m[6] * z, c = m[8] * x + m[9] * y + m[10] * z;
+  x = a; y = b; z = c;
+}
+
 __global__ void __launch_bounds__(256)
 k_vmf_pdf(const float* __restrict__ pos, const float* __restrict__ weight, const float* __restrict__ std, int K,
-          const float* __restrict__ p, const float* __restrict__ d, int64_t n, float* __restrict__ pdf) {
+          const float* __restrict__ p, const float* __restrict__ d, int64_t n, float* __restrict__ pdf,
+          const __grid_constant__ VmfFrame F) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   LobeSmem* L = reinterpret_cast<LobeSmem*>(smem_raw);
   load_lobes(L, pos, weight, std, K);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float dx = d[3 * i], dy = d[3 * i + 1], dz = d[3 * i + 2];
+    float px = p[3 * i], py = p[3 * i + 1], pz = p[3 * i + 2];
+    if (F.on) { xf_vector(F.w2l, dx, dy, dz); xf_point(F.w2l, px, py, pz); }      // vMF.py:65-67
     float inv = rsqrtf(dx * dx + dy * dy + dz * dz);          // vMF.py:66 normalize(d)
-    pdf[i] = mixture_pdf(L, K, p[3 * i], p[3 * i + 1], p[3 * i + 2], dx * inv, dy * inv, dz * inv);
+    pdf[i] = mixture_pdf(L, K, px, py, pz, dx * inv, dy * inv, dz * inv);
   }
 }
 
 __global__ void __launch_bounds__(256)
 k_vmf_sample(const float* __restrict__ pos, const float* __restrict__ weight, const float* __restrict__ std, int K,
              const float* __restrict__ p, const float* __restrict__ u, int64_t n, float* __restrict__ d_out,
-             float* __restrict__ pdf) {
+             float* __restrict__ pdf, const __grid_constant__ VmfFrame F, float* __restrict__ dist_out,
+             float* __restrict__ ds_p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   LobeSmem* L = reinterpret_cast<LobeSmem*>(smem_raw);
   load_lobes(L, pos, weight, std, K);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float px = p[3 * i], py = p[3 * i + 1], pz = p[3 * i + 2];
+    const float wpx = px, wpy = py, wpz = pz;                 // it.p (world)
+    if (F.on) xf_point(F.w2l, px, py, pz);                    // vMF.py:25
     float ux = u[2 * i], uy = u[2 * i + 1];
     // DiscreteDistribution::sample_reuse: first index in [first,last] with cdf[index] >= u*sum
     float value = ux * L->sum;
@@ -142,8 +163,25 @@ k_vmf_sample(const float* __restrict__ pos, const float* __restrict__ weight, co
     float wz = sz * vx + tz * vy + mz * vz;
     float inv = rsqrtf(wx * wx + wy * wy + wz * wz);          // vMF.py:38 normalize
     wx *= inv; wy *= inv; wz *= inv;
+    float lx2 = wx, ly2 = wy, lz2 = wz;                       // the direction pdf_direction will see in local space
+    if (F.on) {
+      xf_vector(F.l2w, wx, wy, wz);                           // vMF.py:37-38: to world, normalize
+      inv = rsqrtf(wx * wx + wy * wy + wz * wz);
+      wx *= inv; wy *= inv; wz *= inv;
+      lx2 = wx; ly2 = wy; lz2 = wz;
+      xf_vector(F.w2l, lx2, ly2, lz2);                        // vMF.py:65-66: back, normalize
+      inv = rsqrtf(lx2 * lx2 + ly2 * ly2 + lz2 * lz2);
+      lx2 *= inv; ly2 *= inv; lz2 *= inv;
+    }
     d_out[3 * i] = wx; d_out[3 * i + 1] = wy; d_out[3 * i + 2] = wz;
-    pdf[i] = mixture_pdf(L, K, px, py, pz, wx, wy, wz);       // vMF.py:54 ds.pdf = pdf_direction(...)
+    pdf[i] = mixture_pdf(L, K, px, py, pz, lx2, ly2, lz2);    // vMF.py:54 ds.pdf = pdf_direction(...)
+    if (dist_out || ds_p) {
+      // vMF.py:40-46: the reference point may lie outside the bounding sphere (a sensor): dist = 2 max(r, |it.p - c|)
+      const float ax = wpx - F.centre[0], ay = wpy - F.centre[1], az = wpz - F.centre[2];
+      const float dist = 2.f * fmaxf(F.radius, sqrtf(ax * ax + ay * ay + az * az));
+      if (dist_out) dist_out[i] = dist;
+      if (ds_p) { ds_p[3 * i] = wpx + wx * dist; ds_p[3 * i + 1] = wpy + wy * dist; ds_p[3 * i + 2] = wpz + wz * dist; }
+    }
   }
 }
 
@@ -154,26 +192,33 @@ static cudaError_t prep(const void* fn, int K, size_t* smem) {
 }
 
 cudaError_t launch_vmf_sample(const float* pos, const float* weight, const float* std, int K, const float* p,
-                              const float* u, int64_t n, float* d, float* pdf, cudaStream_t stream) {
+                              const float* u, int64_t n, float* d, float* pdf, cudaStream_t stream, const VmfFrame* frame,
+                              float* dist, float* ds_p) {
   if (n <= 0) return cudaSuccess;
+  VmfFrame F;
+  memset(&F, 0, sizeof(F));
+  if (frame) F = *frame;
   size_t smem;
   cudaError_t e = prep((const void*)k_vmf_sample, K, &smem);
   if (e != cudaSuccess) return e;
   int64_t blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  k_vmf_sample<<<(unsigned)blocks, 256, smem, stream>>>(pos, weight, std, K, p, u, n, d, pdf);
+  k_vmf_sample<<<(unsigned)blocks, 256, smem, stream>>>(pos, weight, std, K, p, u, n, d, pdf, F, dist, ds_p);
   return cudaGetLastError();
 }
 
 cudaError_t launch_vmf_pdf(const float* pos, const float* weight, const float* std, int K, const float* p,
-                           const float* d, int64_t n, float* pdf, cudaStream_t stream) {
+                           const float* d, int64_t n, float* pdf, cudaStream_t stream, const VmfFrame* frame) {
   if (n <= 0) return cudaSuccess;
+  VmfFrame F;
+  memset(&F, 0, sizeof(F));
+  if (frame) F = *frame;
   size_t smem;
   cudaError_t e = prep((const void*)k_vmf_pdf, K, &smem);
   if (e != cudaSuccess) return e;
   int64_t blocks = (n + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  k_vmf_pdf<<<(unsigned)blocks, 256, smem, stream>>>(pos, weight, std, K, p, d, n, pdf);
+  k_vmf_pdf<<<(unsigned)blocks, 256, smem, stream>>>(pos, weight, std, K, p, d, n, pdf, F);
   return cudaGetLastError();
 }
 

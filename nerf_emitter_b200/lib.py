@@ -77,6 +77,11 @@ class NemitSphericalSensor(C.Structure):
                 ("spp", C.c_int32), ("seed", C.c_uint32)]
 
 
+class NemitVmfFrame(C.Structure):
+    _fields_ = [("world_to_local", C.c_float * 12), ("local_to_world", C.c_float * 12), ("bsphere_center", C.c_float * 3),
+                ("bsphere_radius", C.c_float)]
+
+
 class NemitVmfLobes(C.Structure):
     _fields_ = [("position", C.c_void_p), ("weight", C.c_void_p), ("std", C.c_void_p), ("num_lobes", C.c_int32)]
 
@@ -131,6 +136,10 @@ SYMBOLS = {
                                    C.c_void_p, C.c_void_p]),
     "nemit_vmf_pdf": (C.c_int, [C.POINTER(NemitVmfLobes), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                                 C.c_void_p]),
+    "nemit_vmf_sample_direction": (C.c_int, [C.POINTER(NemitVmfLobes), C.POINTER(NemitVmfFrame), C.c_void_p, C.c_void_p,
+                                             C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "nemit_vmf_pdf_direction": (C.c_int, [C.POINTER(NemitVmfLobes), C.POINTER(NemitVmfFrame), C.c_void_p, C.c_void_p,
+                                          C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_forward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "nemit_launch_count": (C.c_int64, [_H]),
     "nemit_set_sampler": (C.c_int, [_H, C.c_int32]),

@@ -54,7 +54,7 @@ def cluster_light(position: torch.Tensor, weight: torch.Tensor, n_cluster: int =
                   init_means: Optional[torch.Tensor] = None, check_every: int = 5) -> Dict[str, torch.Tensor]:
     """gmm_cluster_light.py:41-85: best of ``n_trials`` weighted fits of ``n_cluster`` isotropic normals;
     returns {'position' (K,3), 'std' (K,1), 'weight' (K)} as device tensors (``equalize`` only re-splits heavy points
-    into equal copies, which leaves every weighted sum unchanged, so it is a no-op here)."""
+    into equal copies, which leaves every weighted EM sum unchanged; the initial means are drawn by weight either way)."""
     if not position.is_cuda:
         raise L.NemitError("cluster_light: CUDA tensors required; there is no CPU path")
     x = position.reshape(-1, 3).float().contiguous()
@@ -67,9 +67,29 @@ def cluster_light(position: torch.Tensor, weight: torch.Tensor, n_cluster: int =
     best = None
     for trial in range(n_trials if init_means is None else 1):
         if init_means is None:
-            # initial means: points drawn in proportion to their weight; one shared variance; equal priors
-            idx = torch.multinomial(w / w.sum(), n_cluster, replacement=False, generator=gen)
-            mean = x[idx].contiguous()
+            # initial means: points drawn in proportion to their weight; one shared variance; equal priors.  Drawn by
+            # inverting the cumulative weights (torch.multinomial stops at 2^24 categories, and compensate_pc leaves the
+            # masked points in place with weight 0); with fewer weighted points than clusters the draw repeats points,
+            # jittered like the reference's position_noisy (gmm_cluster_light.py:60), instead of raising
+            cdf = torch.cumsum(w.double(), 0)
+            n_pos = int((w > 0).sum())
+            if n_pos == 0:
+                raise ValueError("cluster_light: every point has zero weight")
+            if n_pos >= n_cluster:
+                # without replacement: stratified draw over the cumulative weight, one point per stratum, deduplicated
+                u = (torch.arange(n_cluster, device=dev, dtype=torch.float64)
+                     + torch.rand(n_cluster, device=dev, dtype=torch.float64, generator=gen)) / n_cluster * cdf[-1]
+                idx = torch.searchsorted(cdf, u, right=True).clamp(max=x.shape[0] - 1)
+                idx = torch.unique(idx)
+                if idx.numel() < n_cluster:     # heavy points caught several strata: fill up with the next heaviest unused ones
+                    rest = torch.argsort(w, descending=True)
+                    rest = rest[~torch.isin(rest, idx)][: n_cluster - idx.numel()]
+                    idx = torch.cat([idx, rest])
+                mean = x[idx].contiguous()
+            else:
+                pos_idx = torch.nonzero(w > 0).reshape(-1)
+                idx = pos_idx[torch.arange(n_cluster, device=dev) % n_pos]
+                mean = (x[idx] + 1e-6 * torch.randn(n_cluster, 3, device=dev, generator=gen)).contiguous()
         else:
             mean = init_means.to(dev).float().contiguous()
         spread = float(((x - (x * w[:, None]).sum(0) / w.sum()).square().sum(1) * w).sum() / w.sum() / 3.0)

@@ -12,8 +12,12 @@ class VmfMixture:
     """Lobe table of ``VonMisesFisherEmitter``: position (K,3), weight (K), std (K)
     (loaded by ``load_vmf_params``, NS/path_guiding/vmf_guiding.py:52-57)."""
 
-    def __init__(self, position: torch.Tensor, weight: torch.Tensor, std: torch.Tensor):
+    def __init__(self, position: torch.Tensor, weight: torch.Tensor, std: torch.Tensor, world_transform=None,
+                 bsphere_center=(0.5, 0.5, 0.5), bsphere_radius: float = 0.8660254037844386):
+        """world_transform: the emitter's to_world as a (4,4) / (3,4) matrix (None = identity: points and directions are
+        emitter-local); bsphere: the emitter's bounding sphere m_bsphere (default: the unit cube's)."""
         self.lib = L.load()
+        self.set_world_transform(world_transform, bsphere_center, bsphere_radius)
         if not position.is_cuda:
             raise L.NemitError("VmfMixture needs CUDA tensors; there is no CPU path")
         K = position.shape[0]
@@ -26,6 +30,48 @@ class VmfMixture:
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.position.device).cuda_stream)
+
+    def set_world_transform(self, world_transform=None, bsphere_center=(0.5, 0.5, 0.5), bsphere_radius: float = 0.8660254037844386):
+        """params['to_world'] of the emitter (Rotater.apply_sdf_scene moves it per rotation, rotater.py:115-123)."""
+        T = torch.eye(4, dtype=torch.float64)
+        if world_transform is not None:
+            W = torch.as_tensor(world_transform, dtype=torch.float64).cpu()
+            T[:W.shape[0], :4] = W[:, :4]
+        Ti = torch.linalg.inv(T)
+        f = L.NemitVmfFrame()
+        for i, x in enumerate(Ti[:3, :4].reshape(-1).tolist()):
+            f.world_to_local[i] = x
+        for i, x in enumerate(T[:3, :4].reshape(-1).tolist()):
+            f.local_to_world[i] = x
+        for i in range(3):
+            f.bsphere_center[i] = float(bsphere_center[i])
+        f.bsphere_radius = float(bsphere_radius)
+        self._frame = f
+        self.world_transform = T
+        return self
+
+    def sample_direction_world(self, it_p: torch.Tensor, u: torch.Tensor):
+        """VonMisesFisherEmitter.sample_direction (vMF.py:24-56) for world-space reference points it_p (N,3):
+        -> DirectionSample fields {d (N,3), pdf (N), dist (N), p (N,3), n (N,3) = -d}; the returned weight is 0."""
+        n = it_p.shape[0]
+        it_p = it_p.float().contiguous()
+        u = u.float().contiguous()
+        f = dict(device=it_p.device, dtype=torch.float32)
+        d, pdf, dist, p = torch.empty(n, 3, **f), torch.empty(n, **f), torch.empty(n, **f), torch.empty(n, 3, **f)
+        L.check(self.lib.nemit_vmf_sample_direction(C.byref(self._lobes), C.byref(self._frame), it_p.data_ptr(), u.data_ptr(), n,
+                                                    d.data_ptr(), pdf.data_ptr(), dist.data_ptr(), p.data_ptr(), self._stream()),
+                "nemit_vmf_sample_direction")
+        return {"d": d, "pdf": pdf, "dist": dist, "p": p, "n": -d}
+
+    def pdf_direction_world(self, it_p: torch.Tensor, ds_d: torch.Tensor):
+        """VonMisesFisherEmitter.pdf_direction (vMF.py:64-81) for world-space it.p and ds.d."""
+        n = it_p.shape[0]
+        it_p = it_p.float().contiguous()
+        ds_d = ds_d.float().contiguous()
+        pdf = torch.empty(n, device=it_p.device, dtype=torch.float32)
+        L.check(self.lib.nemit_vmf_pdf_direction(C.byref(self._lobes), C.byref(self._frame), it_p.data_ptr(), ds_d.data_ptr(), n,
+                                                 pdf.data_ptr(), self._stream()), "nemit_vmf_pdf_direction")
+        return pdf
 
     def sample_direction(self, p: torch.Tensor, u: torch.Tensor):
         """p (N,3) shading points, u (N,2) in [0,1)^2 -> d (N,3) unit directions, pdf (N)."""

@@ -87,6 +87,28 @@ def sample_direction(position, weight, std, p, u):
     return d, mixture_pdf(position, weight, std, p, d), idx
 
 
+def sample_direction_world(position, weight, std, it_p, u, to_world, bsphere_center, bsphere_radius):
+    """VonMisesFisherEmitter.sample_direction as the emitter runs it (vMF.py:24-56): world-space it.p, to_world (4,4).
+    Returns the DirectionSample fields d, pdf, dist, p."""
+    W = torch.as_tensor(to_world, dtype=torch.float32)
+    Wi = torch.linalg.inv(W.double()).float()
+    p = it_p @ Wi[:3, :3].t() + Wi[:3, 3]                               # transform_affine of a point
+    d_local, _, _ = sample_direction(position, weight, std, p, u)
+    d = d_local @ W[:3, :3].t()                                        # ... of a vector
+    d = d / d.norm(dim=-1, keepdim=True)
+    radius = torch.clamp((it_p - torch.as_tensor(bsphere_center, dtype=torch.float32)).norm(dim=-1), min=float(bsphere_radius))
+    dist = 2.0 * radius
+    return {"d": d, "pdf": pdf_direction_world(position, weight, std, it_p, d, to_world), "dist": dist,
+            "p": it_p + d * dist[:, None]}
+
+
+def pdf_direction_world(position, weight, std, it_p, ds_d, to_world):
+    """vMF.py:64-81: d = normalize(W^-1 ds.d), p = W^-1 it.p."""
+    Wi = torch.linalg.inv(torch.as_tensor(to_world, dtype=torch.float64)).float()
+    d = ds_d @ Wi[:3, :3].t()
+    return mixture_pdf(position, weight, std, it_p @ Wi[:3, :3].t() + Wi[:3, 3], d)
+
+
 def make_lobes(K=64, seed=3):
     """positions U([-1,2]^3), std U(0.05,0.5), weights ~ Dirichlet(1)."""
     g = torch.Generator().manual_seed(seed)

@@ -92,3 +92,24 @@ def test_point_lights_to_vmf_lobes_chain(spec, params_factory):
         d, pdf = V.sample_direction(torch.rand(512, 3, device=DEV), torch.rand(512, 2, device=DEV))
         assert bool(torch.isfinite(pdf).all())
     assert len(adjoint) == 1
+
+
+@pytest.mark.gpu
+def test_cluster_light_initialisation_edge_cases():
+    """the initial means must not depend on torch.multinomial's limits: fewer weighted points than clusters
+    (compensate_pc leaves masked points in place with weight 0) and clouds beyond 2^24 points."""
+    from nerf_emitter_b200.light_clusters import cluster_light
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(5000, 3, generator=g).cuda()
+    w = torch.zeros(5000).cuda()
+    w[:20] = torch.rand(20, generator=g).cuda() + 0.1            # 20 weighted points, 64 clusters asked for
+    out = cluster_light(x, w, n_cluster=64, n_trials=1, max_iter=10)
+    assert out["position"].shape == (64, 3) and torch.isfinite(out["position"]).all() and torch.isfinite(out["std"]).all()
+    assert abs(float(out["weight"].sum()) - 1.0) < 1e-4
+    with pytest.raises(ValueError):
+        cluster_light(x, torch.zeros(5000).cuda(), n_cluster=8)
+    n = (1 << 24) + 1000
+    xb = torch.rand(n, 3, device="cuda")
+    wb = torch.rand(n, device="cuda")
+    out = cluster_light(xb, wb, n_cluster=16, n_trials=1, max_iter=3)
+    assert out["position"].shape == (16, 3) and torch.isfinite(out["position"]).all()
