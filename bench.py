@@ -64,10 +64,10 @@ OWN_BOUND = {"k_sample_levels": ("l1_gather", "gather_coherent", LOADS_SAMPLING,
                                      "reduction lane-ops the table scatter issued (counted on the device) vs the "
                                      "random red.global.add lane-op rate")}
 # dram__bytes_read.sum + dram__bytes_write.sum per launch OF THE SIZE THE BENCH LAUNCHES, from the committed ncu --set full
-# captures (profiles/r2_ncu_*): (rays per launch, bytes)
-NCU_TRAFFIC = {"k_sample_levels": (1 << 18, 31.6e6), "k_field_forward_tc": (1 << 18, 255.2e6),
+# captures (profiles/r2_ncu_step_summary.txt): (rays per launch, bytes)
+NCU_TRAFFIC = {"k_sample_levels": (1 << 18, 14.5e6), "k_field_forward_tc": (1 << 18, 111.6e6),
                "k_field_forward": (1 << 16, 63.9e6),
-               "k_field_forward<adjoint_seed>": (1 << 16, 3.13e9), "k_field_backward_tc": (1 << 16, 2.43e9)}
+               "k_field_forward<adjoint_seed>": (1 << 16, 1.774e9), "k_field_backward_tc": (1 << 16, 1.584e9)}
 
 METRIC = {"fwd": "NeRF-emitter rays/sec fwd (nerfacto 256/96/48 samples)",
           "fwd+bwd": "NeRF-emitter rays/sec fwd+bwd (nerfacto 256/96/48 samples)",

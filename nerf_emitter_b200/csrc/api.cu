@@ -440,6 +440,13 @@ static void offset_levels(SampleArgs& S, const NemitLevelsOut* L, int64_t off) {
   if (L->inds2) S.inds2 = L->inds2 + off * (kS2 + 1);
 }
 
+// the proposal sampling pass of one chunk (the fast sampler first refreshes its packed-half table copies: one more launch)
+static cudaError_t launch_sampler(NemitHandle* h, const ModelDev& M, const SampleArgs& S, cudaStream_t st, int64_t n) {
+  const bool fast = h->sampler == NEMIT_SAMPLER_FAST;
+  if (fast) h->launches++;
+  return timed_launch(h, NEMIT_K_SAMPLE, st, n, [&] { return launch_sample_levels(M, S, st, fast); });
+}
+
 static int chunk_edges(NemitHandle* h, const ModelDev& M, const NemitRays* rays, int64_t off, int64_t n, char* ws,
                        const WsLayout& L, bool need_s1, cudaStream_t st, ChunkEdges* out) {
   if (rays->kept_t_edges2 && (!need_s1 || rays->kept_s_edges1)) {
@@ -453,7 +460,7 @@ static int chunk_edges(NemitHandle* h, const ModelDev& M, const NemitRays* rays,
   S.t_edges2 = reinterpret_cast<float*>(ws + L.t_edges2);
   S.s_edges2 = reinterpret_cast<float*>(ws + L.s_edges2);
   S.s_edges1 = need_s1 ? reinterpret_cast<float*>(ws + L.s_edges1) : nullptr;
-  cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, st, n, [&] { return launch_sample_levels(M, S, st, h->sampler == NEMIT_SAMPLER_FAST); });
+  cudaError_t e = launch_sampler(h, M, S, st, n);
   if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
   out->t_edges2 = S.t_edges2; out->s_edges2 = S.s_edges2; out->s_edges1 = S.s_edges1;
   return NEMIT_OK;
@@ -471,7 +478,7 @@ extern "C" int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const 
     SampleArgs S;
     fill_sample_args(h, S, rays, off, n);
     offset_levels(S, out, off);
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, n, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
+    cudaError_t e = launch_sampler(h, h->M, S, (cudaStream_t)stream, n);
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
   }
   return NEMIT_OK;
@@ -496,7 +503,7 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     float* t_edges = reinterpret_cast<float*>(ws + L.t_edges2);
     float* user_t = S.t_edges2;
     S.t_edges2 = t_edges;
-    cudaError_t e = timed_launch(h, NEMIT_K_SAMPLE, (cudaStream_t)stream, n, [&] { return launch_sample_levels(h->M, S, (cudaStream_t)stream, h->sampler == NEMIT_SAMPLER_FAST); });
+    cudaError_t e = launch_sampler(h, h->M, S, (cudaStream_t)stream, n);
     if (e != cudaSuccess) return cuda_fail(e, "k_sample_levels");
     if (user_t) {
       e = cudaMemcpyAsync(user_t, t_edges, sizeof(float) * n * (kS2 + 1), cudaMemcpyDeviceToDevice, (cudaStream_t)stream);
