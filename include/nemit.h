@@ -194,6 +194,13 @@ int nemit_bind_grads(NemitHandle* h, const NemitParams* g);
  * activations, weights and compositing are fp32 in both.  Default: FP32. */
 #define NEMIT_PRECISION_FP32 0
 #define NEMIT_PRECISION_FP16_TC 1
+/* fp32 MLP arithmetic ON the tensor cores (round 2), same kernels as NEMIT_PRECISION_FP16_TC with split operands: every
+ * operand element as bf16 pieces x0 + x1 (+ x2), a product = the sum of the piece products in one fp32 TMEM accumulator.
+ * Forward (nemit_forward and the seed pass of nemit_backward): three pieces = 24 significant bits, six MMAs per layer.
+ * Reverse (k_field_backward_tc): two pieces = 16 bits, three MMAs per product, with the ReLU masks decided by the
+ * 24-bit forward - so the discontinuous part of the derivative is the fp32 one and the rest is smooth at ~1e-5.
+ * nemit_jvp stays on the fp32 FMA path in every mode. */
+#define NEMIT_PRECISION_SPLIT_TC 2
 int nemit_set_precision(NemitHandle* h, int32_t precision);
 
 /* Arithmetic of the proposal-network sampler (ProposalNetworkSampler, NS/model_components/ray_samplers.py:584-626):

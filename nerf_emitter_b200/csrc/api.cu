@@ -275,7 +275,7 @@ extern "C" int nemit_set_sampler(NemitHandle* h, int32_t sampler) {
 }
 extern "C" int nemit_set_precision(NemitHandle* h, int32_t precision) {
   if (!h) return fail(NEMIT_E_INVALID, "nemit_set_precision: null handle%s");
-  if (precision != NEMIT_PRECISION_FP32 && precision != NEMIT_PRECISION_FP16_TC)
+  if (precision != NEMIT_PRECISION_FP32 && precision != NEMIT_PRECISION_FP16_TC && precision != NEMIT_PRECISION_SPLIT_TC)
     return fail(NEMIT_E_INVALID, "nemit_set_precision: unknown precision%s");
   h->precision = precision;
   return NEMIT_OK;
@@ -288,7 +288,7 @@ static size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct WsLayout {
   size_t t_edges2, s_edges2, s_edges1, host_stage, bwd, total;
-  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles, act_tiles, seeds4;   // inside the backward block
+  size_t g_sigma, g_rgbs, weights2, ray_grad, g_absmax, enc_tiles, jac_tiles, act_tiles, seeds4, masks4;   // inside the backward block
 };
 static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   size_t off = base;
@@ -305,7 +305,9 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   // tensor-core backward: per sample of the backward sub-chunk the encoding row (64 B), its Jacobian (192 B), the
   // operand rows H1 / IN (192 B) and the pre-activation seeds (16 B), kept by the seed pass (H2 / H3 are recomputed)
   const size_t bc = (size_t)(c < kBwdChunkRays ? c : kBwdChunkRays);
-  const size_t tiles = (bc * kS2 + 127) / 128 + 3;
+  // (+8 tiles of slack: a launch may write up to 3 tiles past its rays, and the split-operand mode runs two launches of
+  // half the rays with tiles of twice the size in the same space, see bwd_sub_chunk)
+  const size_t tiles = (bc * kS2 + 127) / 128 + 8;
   if (L) L->enc_tiles = off;
   off += align_up(tiles * (size_t)kEncTileBytes);
   if (L) L->jac_tiles = off;
@@ -314,8 +316,19 @@ static size_t backward_chunk_bytes(int64_t c, WsLayout* L, size_t base) {
   off += align_up(tiles * (size_t)kActTileBytes);
   if (L) L->seeds4 = off;
   off += align_up(tiles * 128 * 16);
+  if (L) L->masks4 = off;
+  off += align_up(tiles * 128 * 16);
   return off - base;
 }
+// rays per reverse-mode launch group: the kept tiles of NEMIT_PRECISION_SPLIT_TC are twice as large (bf16 hi | lo pieces,
+// fp32 Jacobian), so that mode walks the chunk in sub-chunks of half the rays inside the same workspace
+static int64_t bwd_sub_chunk(const NemitHandle* h, int64_t n_total) {
+  int64_t bc = n_total < kBwdChunkRays ? n_total : kBwdChunkRays;
+  if (h->precision == NEMIT_PRECISION_SPLIT_TC) bc = bc / 2 > 0 ? bc / 2 : 1;
+  return bc;
+}
+static int tc_pieces(const NemitHandle* h) { return h->precision == NEMIT_PRECISION_SPLIT_TC ? 2 : 1; }
+static bool tc_mode(const NemitHandle* h) { return h->precision != NEMIT_PRECISION_FP32; }
 static WsLayout ws_layout(int64_t n) {
   int64_t c = n < kChunkRays ? n : kChunkRays;
   if (c < 1) c = 1;
@@ -517,8 +530,8 @@ extern "C" int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, 
     F.rgb = rgb + off * 3;
     F.accumulation = accumulation ? accumulation + off : nullptr;
     F.weights2 = (levels && levels->weights2) ? levels->weights2 + off * kS2 : nullptr;
-    if (h->precision == NEMIT_PRECISION_FP16_TC)
-      e = timed_launch(h, NEMIT_K_FIELD_TC, (cudaStream_t)stream, n, [&] { return launch_field_forward_tc(h->M, F, (cudaStream_t)stream); });
+    if (tc_mode(h))
+      e = timed_launch(h, NEMIT_K_FIELD_TC, (cudaStream_t)stream, n, [&] { return launch_field_forward_tc(h->M, F, (cudaStream_t)stream, tc_pieces(h)); });
     else
       e = timed_launch(h, NEMIT_K_FIELD_FWD, (cudaStream_t)stream, n, [&] { return launch_field_forward(h->M, F, (cudaStream_t)stream); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
@@ -718,8 +731,9 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
   char* ws = static_cast<char*>(workspace);
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
-  for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
-    int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
+  const int64_t sub = bwd_sub_chunk(h, rays->n);
+  for (int64_t off = 0; off < rays->n; off += sub) {
+    int64_t n = rays->n - off < sub ? rays->n - off : sub;
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
     float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
     float* weights2 = reinterpret_cast<float*>(ws + L.weights2);
@@ -737,16 +751,17 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     F.t_edges2 = t_edges; F.s_edges2 = s_edges; F.grad_rgb = grad_rgb;
     F.g_sigma = g_sigma; F.g_rgbs = g_rgbs; F.weights2 = weights2; F.reg_chunk = chunk_rays;
     float* g_absmax = reinterpret_cast<float*>(ws + L.g_absmax);
-    if (h->precision == NEMIT_PRECISION_FP16_TC) {
+    if (tc_mode(h)) {
       if ((e = cudaMemsetAsync(g_absmax, 0, sizeof(float), st)) != cudaSuccess) return cuda_fail(e, "memset g_absmax");
       F.g_absmax = g_absmax;
       F.enc_tiles = reinterpret_cast<uint8_t*>(ws + L.enc_tiles);
       F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
       F.act_tiles = reinterpret_cast<uint8_t*>(ws + L.act_tiles);
       F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
+      F.masks4 = reinterpret_cast<uint4*>(ws + L.masks4);
     }
-    if (h->precision == NEMIT_PRECISION_FP16_TC)
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(h->M, F, st); });
+    if (tc_mode(h))
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(h->M, F, st, tc_pieces(h)); });
     else
       e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed(h->M, F, st); });
     if (e != cudaSuccess) return cuda_fail(e, "k_field_forward<adjoint>");
@@ -761,14 +776,15 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     B.G.head_w0 = h->G.head_w0; B.G.head_b0 = h->G.head_b0; B.G.head_w1 = h->G.head_w1; B.G.head_b1 = h->G.head_b1;
     B.G.head_w2 = h->G.head_w2; B.G.head_b2 = h->G.head_b2; B.G.appearance = h->G.appearance;
     B.t_edges2 = t_edges; B.g_sigma = g_sigma; B.g_rgbs = g_rgbs; B.ray_grad = ray_grad; B.loss_scale = loss_scale;
-    if (h->precision == NEMIT_PRECISION_FP16_TC) {
+    if (tc_mode(h)) {
       B.g_absmax = g_absmax;
       B.enc_tiles = reinterpret_cast<const uint8_t*>(ws + L.enc_tiles);
       B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
       B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
       B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
+      B.masks4 = reinterpret_cast<const uint4*>(ws + L.masks4);
       B.red_ops = h->profile ? h->counters : nullptr;
-      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(h->M, B, st); });
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(h->M, B, st, tc_pieces(h)); });
     } else {
       e = timed_launch(h, NEMIT_K_FIELD_BWD, st, n, [&] { return launch_field_backward(h->M, B, st); });
     }
@@ -879,9 +895,10 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
   cudaError_t e;
   ModelDev M = h->M;
   M.distortion_mult = 0.f;           // the objective is the brightness alone (nerfacto.py:562-568): no regularisers
-  const bool tc = h->precision == NEMIT_PRECISION_FP16_TC;
-  for (int64_t off = 0; off < rays->n; off += kBwdChunkRays) {
-    int64_t n = rays->n - off < kBwdChunkRays ? rays->n - off : kBwdChunkRays;
+  const bool tc = tc_mode(h);
+  const int64_t sub = bwd_sub_chunk(h, rays->n);
+  for (int64_t off = 0; off < rays->n; off += sub) {
+    int64_t n = rays->n - off < sub ? rays->n - off : sub;
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
     float* g_rgbs = reinterpret_cast<float*>(ws + L.g_rgbs);
     float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
@@ -905,7 +922,8 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
       F.jac_tiles = reinterpret_cast<uint8_t*>(ws + L.jac_tiles);
       F.act_tiles = reinterpret_cast<uint8_t*>(ws + L.act_tiles);
       F.seeds4 = reinterpret_cast<float4*>(ws + L.seeds4);
-      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(M, F, st); });
+      F.masks4 = reinterpret_cast<uint4*>(ws + L.masks4);
+      e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed_tc(M, F, st, tc_pieces(h)); });
     } else {
       e = timed_launch(h, NEMIT_K_FIELD_SEED, st, n, [&] { return launch_field_adjoint_seed(M, F, st); });
     }
@@ -922,7 +940,8 @@ extern "C" int nemit_point_lights(NemitHandle* h, const NemitRays* rays, const f
       B.jac_tiles = reinterpret_cast<const uint8_t*>(ws + L.jac_tiles);
       B.act_tiles = reinterpret_cast<const uint8_t*>(ws + L.act_tiles);
       B.seeds4 = reinterpret_cast<const float4*>(ws + L.seeds4);
-      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(M, B, st); });
+      B.masks4 = reinterpret_cast<const uint4*>(ws + L.masks4);
+      e = timed_launch(h, NEMIT_K_FIELD_BWD_TC, st, n, [&] { return launch_field_backward_tc(M, B, st, tc_pieces(h)); });
     } else {
       e = timed_launch(h, NEMIT_K_FIELD_BWD, st, n, [&] { return launch_field_backward(M, B, st); });
     }

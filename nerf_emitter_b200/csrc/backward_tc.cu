@@ -84,38 +84,51 @@ constexpr int kScatterUnroll = NEMIT_SCATTER_UNROLL;
 #endif
 constexpr int kScatterGroups = NEMIT_SCATTER_GROUPS;
 constexpr int kScatterThreads = 128 * kScatterGroups;
-constexpr int kComputeThreads = 256;
-constexpr int kBwdThreads = kComputeThreads + kScatterThreads;
-// register split: the CTA is launched with 168 registers per thread (65536 / 384 rounded down to a multiple of 8), i.e. a
-// pool of 64512; the scatter warpgroup shrinks and the two compute warpgroups grow out of what it released (setmaxnreg).
-// The split must fit the POOL, not the register file: a setmaxnreg.inc that cannot be served blocks for ever.
-constexpr int kLaunchRegs = kScatterGroups == 1 ? 168 : 128;
-constexpr int kComputeRegs = kScatterGroups == 1 ? 200 : 192;
-constexpr int kScatterRegs = kScatterGroups == 1 ? 104 : 64;
-static_assert(kComputeThreads * kComputeRegs + kScatterThreads * kScatterRegs <= kBwdThreads * kLaunchRegs, "register pool of the CTA");
+// NP = 1: fp16 operands, two compute halves.  NP = 2: the fp32-accurate mode (bf16 hi | lo operand pieces, tc_common.cuh):
+// the operand buffers are twice as large, so ONE compute half per CTA (its chain is not overlapped with a second one; the
+// scatter warps still run beside it).
+// Register split: the CTA is launched with kLaunchRegs per thread (65536 / threads rounded down to a multiple of 8), i.e.
+// a pool of threads x kLaunchRegs; the scatter warpgroups shrink and the compute warpgroups grow out of what they released
+// (setmaxnreg).  The split must fit the POOL, not the register file: a setmaxnreg.inc that cannot be served blocks for ever.
+template <int NP>
+struct BwdCfg {
+  static constexpr int kHalves = NP == 1 ? 2 : 1;
+  static constexpr int kComputeThreads = 128 * kHalves;
+  static constexpr int kThreads = kComputeThreads + kScatterThreads;
+  static constexpr int kLaunchRegs = kThreads == 512 ? 128 : (kThreads == 384 ? 168 : 255);
+  static constexpr int kComputeRegs = NP == 1 ? (kScatterGroups == 1 ? 200 : 192) : 232;
+  static constexpr int kScatterRegs = NP == 1 ? (kScatterGroups == 1 ? 104 : 64) : 64;
+  static_assert(kThreads == 512 || kThreads == 384, "launch register count is derived for 384 / 512 threads");
+  static_assert(kComputeThreads * kComputeRegs + kScatterThreads * kScatterRegs <= kThreads * kLaunchRegs, "register pool of the CTA");
+};
 #ifndef NEMIT_BWD_AGGREGATE
 #define NEMIT_BWD_AGGREGATE 1          // sum the contributions of runs of lanes that fall into the same grid cell before the red
 #endif
 
+// one-piece sizes of the operand buffers (piece p of a buffer sits p * size after piece 0)
+constexpr uint32_t kPcB1 = 64 * 32 * 2, kPcB2 = 16 * 64 * 2, kPcB3 = 64 * 32 * 2, kPcB4 = 64 * 64 * 2, kPcB5 = 16 * 64 * 2;
+constexpr uint32_t kPcE = 128 * 32 * 2, kPcH = 128 * 64 * 2, kPcIn = 128 * 32 * 2, kPcGs = 128 * 16 * 2;
+template <int NP>
 struct BwdTcCommon {
-  alignas(128) uint8_t b1[64 * 32 * 2];   // base layer 0   (64 x 32)   forward K-major layout, rows = outputs
-  alignas(128) uint8_t b2[16 * 64 * 2];   // base layer 1   (16 x 64)
-  alignas(128) uint8_t b3[64 * 32 * 2];   // head layer 0   (64 x [SH16 | geo15 | 0])
-  alignas(128) uint8_t b4[64 * 64 * 2];   // head layer 1   (64 x 64)
-  alignas(128) uint8_t b5[16 * 64 * 2];   // head layer 2   (3 rows used of 16)
-  alignas(128) uint8_t ones[8 * 128 * 2]; // MN-major 8 x 128 operand of fp16 ones
+  alignas(128) uint8_t b1[NP * kPcB1];    // base layer 0   (64 x 32)   forward K-major layout, rows = outputs
+  alignas(128) uint8_t b2[NP * kPcB2];    // base layer 1   (16 x 64)
+  alignas(128) uint8_t b3[NP * kPcB3];    // head layer 0   (64 x [SH16 | geo15 | 0])
+  alignas(128) uint8_t b4[NP * kPcB4];    // head layer 1   (64 x 64)
+  alignas(128) uint8_t b5[NP * kPcB5];    // head layer 2   (3 rows used of 16)
+  alignas(128) uint8_t ones[8 * 128 * 2]; // MN-major 8 x 128 operand of ones (fp16 or bf16: one piece, exact)
   float app[kApp];
   float bias_h0[64];                      // head layer 0 bias with the appearance columns folded in (as the forward)
   float bias_h1[64];
   uint32_t tmem_slot;
 };
+template <int NP>
 struct BwdTcHalf {
-  alignas(128) uint8_t e[128 * 32 * 2];   // hash encoding
-  alignas(128) uint8_t h1[128 * 64 * 2];  // base hidden         -> its gradient
-  alignas(128) uint8_t in[128 * 32 * 2];  // [SH16 | geo15 | 1]
-  alignas(128) uint8_t h2[128 * 64 * 2];  // head hidden 1       -> its gradient
-  alignas(128) uint8_t h3[128 * 64 * 2];  // head hidden 2       -> its gradient
-  alignas(128) uint8_t gs[128 * 16 * 2];  // d rgb pre-activation (3 of 16), later d [raw | geo15]
+  alignas(128) uint8_t e[NP * kPcE];      // hash encoding
+  alignas(128) uint8_t h1[NP * kPcH];     // base hidden         -> its gradient
+  alignas(128) uint8_t in[NP * kPcIn];    // [SH16 | geo15 | 1]
+  alignas(128) uint8_t h2[NP * kPcH];     // head hidden 1       -> its gradient
+  alignas(128) uint8_t h3[NP * kPcH];     // head hidden 2       -> its gradient
+  alignas(128) uint8_t gs[NP * kPcGs];    // d rgb pre-activation (3 of 16), later d [raw | geo15]
   float dvec[64];
   float denc[32 * 128];                   // d encoding of the tile handed to the scatter warps, [column][sample]
   float pbuf[3 * 128];                    // its normalised sample positions, [axis][sample]
@@ -124,11 +137,11 @@ struct BwdTcHalf {
   alignas(8) uint64_t full_bar;           // 128 compute threads arrive: denc / pbuf of a tile are parked
   alignas(8) uint64_t empty_bar;          // the half's scatter threads arrive: the slot may be overwritten
 };
+template <int NP>
 struct BwdTcSmem {
-  BwdTcCommon c;
-  BwdTcHalf h[2];
+  BwdTcCommon<NP> c;
+  BwdTcHalf<NP> h[BwdCfg<NP>::kHalves];
 };
-constexpr uint32_t kTileLoadBytes = kEncTileBytes + kActTileBytes;
 
 __device__ __forceinline__ void half_sync(int half) {
   asm volatile("bar.sync %0, 128;" ::"r"(half + 1) : "memory");
@@ -139,8 +152,8 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 }
 
 // make the half's operand writes visible to the tensor core, let its thread 0 issue one commit group, wait for it
-template <class F>
-__device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t& phase, F&& issue) {
+template <class HalfT, class F>
+__device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& phase, F&& issue) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
   half_sync(half);
@@ -161,7 +174,8 @@ __device__ __forceinline__ void mma_step(BwdTcHalf* H, int half, int t, uint32_t
 //     run; the 16 corner contributions are summed over the run with a segmented shuffle scan and the last lane issues them;
 //   * corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices differ in
 //     bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
-__device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int lane, int group, const ModelDev& M,
+template <class HalfT>
+__device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, int group, const ModelDev& M,
                                              float2* table, float gscale, uint32_t& nred) {
   const float p[3] = {H->pbuf[smp], H->pbuf[128 + smp], H->pbuf[256 + smp]};
 #ifndef NEMIT_BWD_SCATTER_FROM
@@ -229,31 +243,36 @@ __device__ __forceinline__ void scatter_tile(const BwdTcHalf* H, int smp, int la
   }
 }
 
-// forward recompute of a head hidden layer: accumulator row + bias, ReLU -> fp16 operand row (k_field_forward_tc's
+// forward recompute of a head hidden layer: accumulator row + bias, ReLU -> operand row (k_field_forward_tc's
 // epilogue_hidden, same arithmetic in the same order)
-__device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* buf, int row) {
+// With split operands (NP = 2) the ReLU decision is the seed pass's (24 significant bits there, 16 here): unit n is active
+// iff bit n of `mask` is set, whatever the sign of this pass's own pre-activation (they differ only within ~1e-5 of zero).
+template <int NP>
+__device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* buf, int row, uint2 mask) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
   tc::tmem_ld_wait();
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
+    const uint32_t mw = (c >> 1) ? mask.y : mask.x;
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
-      uint32_t w[4];
+      float x[8];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int j = hh * 8 + q * 2;
-        const float x0 = fmaxf(v[c][j] + bias[c * 16 + j], 0.f), x1 = fmaxf(v[c][j + 1] + bias[c * 16 + j + 1], 0.f);
-        w[q] = tc::pack_h2(x0, x1);
+      for (int q = 0; q < 8; ++q) {
+        x[q] = fmaxf(v[c][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
+        if (NP > 1 && !((mw >> ((c & 1) * 16 + hh * 8 + q)) & 1u)) x[q] = 0.f;
       }
-      *reinterpret_cast<uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+      tc::store_chunk<NP, 128>(buf, kPcH, row, c * 2 + hh, x);
     }
   }
 }
 
-// hidden layer: accumulator row x (activation row > 0) -> fp16 gradient row written over the activation row
-__device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int row) {
+// hidden layer: accumulator row x (activation row > 0) -> gradient row written over the activation row
+// (USE_MASK: the activity comes from the seed pass's mask bits instead, see epi_fwd_hidden)
+template <int NP, bool USE_MASK = false>
+__device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int row, uint2 mask = make_uint2(0u, 0u)) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
@@ -262,45 +281,52 @@ __device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int
   for (int c = 0; c < 4; ++c) {
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
-      uint4* pr = reinterpret_cast<uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh));
-      const uint4 act = *pr;
+      const uint4 act = *reinterpret_cast<const uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh));
       const uint32_t aw[4] = {act.x, act.y, act.z, act.w};
-      uint32_t w[4];
+      float x[8];
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int j = hh * 8 + q * 2;
-        // post-ReLU fp16 activations are >= 0: a non-zero half pattern (sign bit aside) means the unit was active
-        const float x0 = (aw[q] & 0x00007fffu) ? v[c][j] : 0.f;
-        const float x1 = (aw[q] & 0x7fff0000u) ? v[c][j + 1] : 0.f;
-        w[q] = tc::pack_h2_sat(x0, x1);
+        if (USE_MASK) {
+          const uint32_t mw = ((c >> 1) ? mask.y : mask.x) >> ((c & 1) * 16 + j);
+          x[2 * q] = (mw & 1u) ? v[c][j] : 0.f;
+          x[2 * q + 1] = (mw & 2u) ? v[c][j + 1] : 0.f;
+        } else {
+          // post-ReLU activations are >= 0: a non-zero fp16 / bf16-hi pattern (sign bit aside) means the unit was active
+          x[2 * q] = (aw[q] & 0x00007fffu) ? v[c][j] : 0.f;
+          x[2 * q + 1] = (aw[q] & 0x7fff0000u) ? v[c][j + 1] : 0.f;
+        }
       }
-      *pr = make_uint4(w[0], w[1], w[2], w[3]);
+      tc::store_chunk<NP, 128, true>(buf, kPcH, row, c * 2 + hh, x);
     }
   }
 }
 
 }  // namespace
 
-__global__ void __launch_bounds__(kBwdThreads, 1)
+template <int NP>
+__global__ void __launch_bounds__(BwdCfg<NP>::kThreads, 1)
 k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldBwdArgs A) {
+  using Cfg = BwdCfg<NP>;
+  constexpr int kHalves = Cfg::kHalves, kComputeThreads = Cfg::kComputeThreads, kBwdThreads = Cfg::kThreads;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  BwdTcSmem* sm = reinterpret_cast<BwdTcSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  BwdTcSmem<NP>* sm = reinterpret_cast<BwdTcSmem<NP>*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
   const int tid = threadIdx.x, lane = tid & 31, wq = (tid >> 5) & 3;
-  // roles: threads [0, 256) = two compute halves of 128 (thread t = sample row t of the half's tile);
-  //        threads [256, ...) = scatter warpgroups (thread t = sample t of whichever half's parked tile is being drained)
+  // roles: threads [0, kComputeThreads) = compute halves of 128 (thread t = sample row t of the half's tile);
+  //        the rest = scatter warpgroups (thread t = sample t of whichever half's parked tile is being drained)
   const bool is_scatter = tid >= kComputeThreads;
   const int half = is_scatter ? 0 : tid >> 7;
   const int t = tid & 127;
-  BwdTcCommon* C = &sm->c;
-  BwdTcHalf* H = &sm->h[half];
+  BwdTcCommon<NP>* C = &sm->c;
+  BwdTcHalf<NP>* H = &sm->h[half];
 
   // ---- one-time setup ------------------------------------------------------------------------------
-  tc::stage_weight<64, 32>(C->b1, A.P.base_w0, 64, 32, 32, tid, kBwdThreads);
-  tc::stage_weight<16, 64>(C->b2, A.P.base_w1, 16, 64, 64, tid, kBwdThreads);
-  tc::stage_weight<64, 32>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, kBwdThreads);
-  tc::stage_weight<64, 64>(C->b4, A.P.head_w1, 64, 64, 64, tid, kBwdThreads);
-  tc::stage_weight<16, 64>(C->b5, A.P.head_w2, 3, 64, 64, tid, kBwdThreads);
-  for (int i = tid; i < 8 * 128; i += kBwdThreads) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3C00u;
+  tc::stage_weight_np<64, 32, NP>(C->b1, A.P.base_w0, 64, 32, 32, tid, kBwdThreads);
+  tc::stage_weight_np<16, 64, NP>(C->b2, A.P.base_w1, 16, 64, 64, tid, kBwdThreads);
+  tc::stage_weight_np<64, 32, NP>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, kBwdThreads);
+  tc::stage_weight_np<64, 64, NP>(C->b4, A.P.head_w1, 64, 64, 64, tid, kBwdThreads);
+  tc::stage_weight_np<16, 64, NP>(C->b5, A.P.head_w2, 3, 64, 64, tid, kBwdThreads);
+  for (int i = tid; i < 8 * 128; i += kBwdThreads) reinterpret_cast<uint16_t*>(C->ones)[i] = NP == 1 ? 0x3C00u : 0x3F80u;
   for (int i = tid; i < kApp; i += kBwdThreads) {
     C->app[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
@@ -326,9 +352,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   const uint32_t taddr = tm + ((uint32_t)(wq * 32) << 16);         // this warp's 32 TMEM lanes
   uint32_t phase = 0;
 
-  // gradient operand scale: power of two that maps the launch's largest seed to 16
+  // gradient operand scale: power of two that maps the launch's largest seed to 16 (fp16 operands; bf16 pieces have
+  // fp32's range and need none)
   float S = 1.f, invS = 1.f;
-  {
+  if (NP == 1) {
     const float gmax = A.g_absmax ? *A.g_absmax : 0.f;
     if (gmax > 0.f && gmax < 3.0e38f) {
       int e;
@@ -345,21 +372,22 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
   const int64_t n_samples = A.n * kS2;
   const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
-  const int64_t tile_stride = (int64_t)gridDim.x * 2;
+  const int64_t tile_stride = (int64_t)gridDim.x * kHalves;
+  constexpr uint32_t kTileLoadBytes = NP * (kEncTileBytes + kActTileBytes);
   const float gscale = invS * A.loss_scale;
 
   if (is_scatter) {
     // ---- scatter warps: drain the half's parked tiles into the gradient table ------------------------------------
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kScatterRegs));
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(Cfg::kScatterRegs));
     uint32_t nred = 0;               // reduction lane-ops this thread issued (reported when profiling)
     uint32_t j = 0;
     // half 0 owns tiles 2b, 2b + stride, ...; half 1 owns 2b + 1, ...: drained alternately, so that while one half's tile
     // is being scattered the other half parks its next one
-    for (int64_t tile = (int64_t)blockIdx.x * 2; tile < n_tiles; tile += tile_stride, ++j) {
+    for (int64_t tile = (int64_t)blockIdx.x * kHalves; tile < n_tiles; tile += tile_stride, ++j) {
 #pragma unroll 1
-      for (int hh = 0; hh < 2; ++hh) {
+      for (int hh = 0; hh < kHalves; ++hh) {
         if (tile + hh >= n_tiles) break;
-        BwdTcHalf* Hh = &sm->h[hh];
+        BwdTcHalf<NP>* Hh = &sm->h[hh];
         tc::mbar_wait(&Hh->full_bar, j & 1u);
         if (A.G.main_table)            // null: ray-gradient-only pass (nemit_point_lights), nothing to scatter
           scatter_tile(Hh, t, lane, (tid - kComputeThreads) >> 7, M, A.G.main_table, gscale, nred);
@@ -373,23 +401,24 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     }
   } else {
   // ---- compute halves -----------------------------------------------------------------------------------------------
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kComputeRegs));
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(Cfg::kComputeRegs));
   bool first = true;
   uint32_t ld_phase = 0;
   uint32_t slot_phase = 1;           // empty_bar parity to wait for: a fresh barrier passes parity 1 (slot free)
   // thread 0 of the half: one bulk copy per operand buffer of tile `tl`
   const uint64_t pol = tc::l2_evict_first_policy();
-  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * kEncTileBytes, 8192, &H->ld_bar, pol); };
-  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * kActTileBytes, 16384, &H->ld_bar, pol); };
-  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * kActTileBytes + 16384, 8192, &H->ld_bar, pol); };
+  // (the pieces of a buffer are adjacent in the kept tile exactly as in shared memory: one copy per buffer)
+  auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * (NP * kEncTileBytes), NP * 8192, &H->ld_bar, pol); };
+  auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * (NP * kActTileBytes), NP * 16384, &H->ld_bar, pol); };
+  auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * (NP * kActTileBytes) + NP * 16384, NP * 8192, &H->ld_bar, pol); };
   {
-    const int64_t tile0 = (int64_t)blockIdx.x * 2 + half;
+    const int64_t tile0 = (int64_t)blockIdx.x * kHalves + half;
     if (t == 0 && tile0 < n_tiles) {
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
       load_in(tile0); load_h1(tile0); load_e(tile0);
     }
   }
-  for (int64_t tile = (int64_t)blockIdx.x * 2 + half; tile < n_tiles; tile += tile_stride) {
+  for (int64_t tile = (int64_t)blockIdx.x * kHalves + half; tile < n_tiles; tile += tile_stride) {
     const int64_t next_tile = tile + tile_stride;
     const bool has_next = next_tile < n_tiles;
     const int64_t s = tile * kTileM + t;
@@ -404,6 +433,8 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
       seed = __ldcs(A.seeds4 + s);
     }
+    uint4 mk = make_uint4(0u, 0u, 0u, 0u);
+    if (NP > 1) mk = __ldcs(A.masks4 + tile * kTileM + t);      // ReLU masks of H2 | H3 as the seed pass decided them
     const float tsum = add_rn(t0, t1);
     float x[3], p[3], dirq[3];
     // Rotater.apply_frustums where the reverse pass sees rotated final samples (the light-point-cloud pass only, see backward.cu)
@@ -411,40 +442,43 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     const bool sel = contract_normalise(x, M, p);
 
     // d loss / d (rgb pre-activation): 3 of 16 columns
-    *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 0)) =
-        make_uint4(tc::pack_h2_sat(seed.x * S, seed.y * S), tc::pack_h2_sat(seed.z * S, 0.f), 0u, 0u);
-    *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, 1)) = make_uint4(0u, 0u, 0u, 0u);
+    {
+      const float g8[8] = {seed.x * S, seed.y * S, seed.z * S, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      tc::store_chunk<NP, 128, true>(H->gs, kPcGs, t, 0, g8);
+      tc::store_chunk<NP, 128>(H->gs, kPcGs, t, 1, z8);
+    }
     // this tile's operand buffers have landed
     tc::mbar_wait(&H->ld_bar, ld_phase);
     ld_phase ^= 1u;
 
     // ---- head hidden layers, forward again (H2, H3 are not kept) ------------------------------------------
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->in, 128), tc::op_kmajor(C->b3, 64), tc::idesc_f16(128, 64), 2, false);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->in, 128), kPcIn, tc::op_kmajor(C->b3, 64), kPcB3, tc::idesc_f16(128, 64), 2, false);
     });
-    epi_fwd_hidden(taddr + kColD0, C->bias_h0, H->h2, t);
+    epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h0, H->h2, t, make_uint2(mk.x, mk.y));
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_kmajor(C->b4, 64), tc::idesc_f16(128, 64), 4, false);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_kmajor(C->b4, 64), kPcB4, tc::idesc_f16(128, 64), 4, false);
     });
-    epi_fwd_hidden(taddr + kColD0, C->bias_h1, H->h3, t);
+    epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h1, H->h3, t, make_uint2(mk.z, mk.w));
 
     // ---- head MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColH2T, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColBH2, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b5, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+      tc::mma_chain_np<NP>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b5, 16), kPcB5, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
-    epi_bwd_hidden(taddr + kColD0, H->h3, t);
+    epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h3, t, make_uint2(mk.z, mk.w));
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColH1, tc::op_mnmajor(H->h3, 128), tc::op_mnmajor(H->h2, 128), tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColBH1, tc::op_mnmajor(H->h3, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h3, 128), tc::op_mnmajor(C->b4, 64), tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
+      tc::mma_chain_np<NP>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h3, 128), kPcH, tc::op_mnmajor(C->b4, 64), kPcB4, tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
     });
-    epi_bwd_hidden(taddr + kColD0, H->h2, t);
+    epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h2, t, make_uint2(mk.x, mk.y));
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColH0, tc::op_mnmajor(H->h2, 128), tc::op_mnmajor(H->in, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h2, 128), tc::op_mnmajor(C->b3, 64, 16), tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_mnmajor(C->b3, 64, 16), kPcB3, tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
     });
     if (t == 0 && has_next) {       // IN has no reader left: the next tile's copies start here
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
@@ -458,33 +492,33 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       g16[0] = seed.w * S;
 #pragma unroll
       for (int k = 0; k < 15; ++k) g16[k + 1] = v[k];
-      uint32_t w[4];
 #pragma unroll
       for (int hh = 0; hh < 2; ++hh) {
+        float x8[8];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2_sat(g16[hh * 8 + q * 2], g16[hh * 8 + q * 2 + 1]);
-        *reinterpret_cast<uint4*>(H->gs + tc::chunk_off<128>(t, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+        for (int q = 0; q < 8; ++q) x8[q] = g16[hh * 8 + q];
+        tc::store_chunk<NP, 128, true>(H->gs, kPcGs, t, hh, x8);
       }
     }
 
     // ---- base MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColB1T, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColBB1, op_ones_a, tc::op_mnmajor(H->gs, 128), tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->gs, 128), tc::op_mnmajor(C->b2, 16), tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+      tc::mma_chain_np<NP>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b2, 16), kPcB2, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
-    epi_bwd_hidden(taddr + kColD0, H->h1, t);
+    epi_bwd_hidden<NP>(taddr + kColD0, H->h1, t);
     // this tile's Jacobian rows: the loads fly under the last commit group
-    uint4 jn[12];
+    uint4 jn[12 * NP];               // NP = 1: fp16 pairs; NP = 2: fp32
     {
-      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * kJacTileBytes) + t;
+      const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * (NP * kJacTileBytes)) + t;
 #pragma unroll
-      for (int c = 0; c < 12; ++c) jn[c] = __ldcs(jp + c * 128);
+      for (int c = 0; c < 12 * NP; ++c) jn[c] = __ldcs(jp + c * 128);
     }
     mma_step(H, half, t, phase, [&] {
-      tc::mma_chain(tm + kColB0, tc::op_mnmajor(H->h1, 128), tc::op_mnmajor(H->e, 128), tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColBB0, tc::op_mnmajor(H->h1, 128), op_ones, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain(tm + kColD0, tc::op_kmajor(H->h1, 128), tc::op_mnmajor(C->b1, 64), tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
+      tc::mma_chain_np<NP>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h1, 128), kPcH, tc::op_mnmajor(C->b1, 64), kPcB1, tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
     });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 
@@ -502,14 +536,25 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
         tc::tmem_ld_wait();
 #pragma unroll
         for (int k = 0; k < 8; ++k) H->denc[(2 * l0 + k) * 128 + t] = valid ? g[k] : 0.f;
-        const uint4 ja = jn[(l0 >> 2) * 3], jb = jn[(l0 >> 2) * 3 + 1], jc = jn[(l0 >> 2) * 3 + 2];
-        const uint32_t wj[12] = {ja.x, ja.y, ja.z, ja.w, jb.x, jb.y, jb.z, jb.w, jc.x, jc.y, jc.z, jc.w};
+        uint32_t wj[12 * NP];
+#pragma unroll
+        for (int c = 0; c < 3 * NP; ++c) {
+          const uint4 q = jn[(l0 >> 2) * 3 * NP + c];
+          wj[4 * c] = q.x; wj[4 * c + 1] = q.y; wj[4 * c + 2] = q.z; wj[4 * c + 3] = q.w;
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float gx = g[2 * j], gy = g[2 * j + 1];
-          const float2 dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
-          const float2 dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
-          const float2 dz = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 2]));
+          float2 dx, dy, dz;
+          if (NP == 1) {
+            dx = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 0]));
+            dy = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 1]));
+            dz = __half22float2(*reinterpret_cast<const __half2*>(&wj[3 * j + 2]));
+          } else {
+            dx = make_float2(__uint_as_float(wj[6 * j + 0]), __uint_as_float(wj[6 * j + 1]));
+            dy = make_float2(__uint_as_float(wj[6 * j + 2]), __uint_as_float(wj[6 * j + 3]));
+            dz = make_float2(__uint_as_float(wj[6 * j + 4]), __uint_as_float(wj[6 * j + 5]));
+          }
           const float scs = M.main_grid.scal[l0 + j] * invS;
           gp[0] = fmaf(scs, gx * dx.x + gy * dx.y, gp[0]);
           gp[1] = fmaf(scs, gx * dy.x + gy * dy.y, gp[1]);
@@ -644,19 +689,23 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   if (tid < 32) tc::tmem_dealloc<512>(C->tmem_slot);
 }
 
-cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
-  if (A.n <= 0) return cudaSuccess;
+template <int NP>
+static cudaError_t launch_bwd_np(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
-  const size_t smem = sizeof(BwdTcSmem) + 128;
+  const size_t smem = sizeof(BwdTcSmem<NP>) + 128;
   if (attr_once.need()) {
-    cudaError_t e = cudaFuncSetAttribute(k_field_backward_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_field_backward_tc<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
   const int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
-  const int64_t pairs = (tiles + 1) / 2;
-  const int64_t ctas = pairs < 148 ? pairs : 148;      // persistent: one CTA (two halves, all of TMEM) per SM
-  k_field_backward_tc<<<(unsigned)ctas, kBwdThreads, smem, stream>>>(M, A);
+  const int64_t per_cta = (tiles + BwdCfg<NP>::kHalves - 1) / BwdCfg<NP>::kHalves;
+  const int64_t ctas = per_cta < 148 ? per_cta : 148;  // persistent: one CTA (its compute halves, all of TMEM) per SM
+  k_field_backward_tc<NP><<<(unsigned)ctas, BwdCfg<NP>::kThreads, smem, stream>>>(M, A);
   return cudaGetLastError();
+}
+cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream, int pieces) {
+  if (A.n <= 0) return cudaSuccess;
+  return pieces == 2 ? launch_bwd_np<2>(M, A, stream) : launch_bwd_np<1>(M, A, stream);
 }
 
 }  // namespace nemit

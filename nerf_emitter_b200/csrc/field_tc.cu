@@ -1,123 +1,145 @@
 // field_tc.cu - k_field_forward_tc: the main field with the 64-wide MLP chain on the 5th-generation tensor
-// cores (tcgen05.mma, fp16 operands, fp32 accumulation in TMEM).
+// cores (tcgen05.mma, fp16 or split-bf16 operands, fp32 accumulation in TMEM).
 //
-// One CTA = 128 threads = one 128-sample tile at a time (thread m owns sample row m: it gathers the row's hash
+// One group = 128 threads = one 128-sample tile at a time (thread m owns sample row m: it gathers the row's hash
 // encoding, and after every layer reads ITS accumulator row back from TMEM lane m, applies bias / ReLU in fp32,
-// and writes the fp16 row of the next layer's A operand).  The five GEMMs of a tile
+// and writes the row of the next layer's A operand).  The five GEMMs of a tile
 //     enc[128x32] W_b0^T -> h1[128x64] W_b1^T -> [raw | geo15] ;  [SH16 | geo15 | 0] W_h0'^T -> h2 W_h1^T -> h3 W_h2^T
 // are issued by one thread each (M = 128, N = 64 / 16, K = 32 / 64), the accumulator reuses the same 64 TMEM
 // columns, the weights stay resident in shared memory in the UMMA K-major layout for the CTA's lifetime.
-// Several CTAs per SM overlap one CTA's gather phase with another's MMA / epilogue phase.
+// Several groups per SM overlap one group's gather phase with another's MMA / epilogue phase.
 // Density activation, SafeExp, weights scan and composite stay in fp32 (same code as the fp32 kernel).
 //
-// Reference: NerfactoField.get_density / get_outputs (NS/fields/nerfacto_field.py:228-334); the reference runs
-// this MLP in fp16 under autocast / tiny-cuda-nn FullyFusedMLP (NS/models/base_model.py:305,
-// NS/field_components/mlp.py:117-144) - this is that "fp16 MLP" mode of BASELINE.json configs[1].
+// Operand precision (template NP):
+//   NP = 1  fp16 operands: the reference's own mixed-precision mode (torch.autocast / tiny-cuda-nn FullyFusedMLP,
+//           NS/models/base_model.py:305, NS/field_components/mlp.py:117-144), BASELINE.json configs[1]; one group per
+//           CTA, four CTAs per SM.
+//   NP = 3  fp32 arithmetic on the tensor cores: every operand as three bf16 pieces (24 significant bits), six MMAs per
+//           layer (tc_common.cuh).  The weights take 60 KB, so one CTA per SM holds them once for TWO groups of 128
+//           threads (named barriers, 64 TMEM columns each).  The seed pass of this mode keeps the two leading pieces
+//           of E / H1 / IN, the Jacobian in fp32 and the ReLU masks of the two head layers for k_field_backward_tc.
+//
+// Reference: NerfactoField.get_density / get_outputs (NS/fields/nerfacto_field.py:228-334), MLP
+// (NS/field_components/mlp.py:163-183).
 #include "kernels.h"
 #include "field_common.cuh"
 #include "tc_common.cuh"
 
 namespace nemit {
 
+constexpr uint32_t kAPiece = 128 * 64 * 2;
+template <int NP, int NG>
 struct TcSmem {
-  // fp16 B operands (UMMA K-major layout, rows = output features)
-  alignas(128) uint8_t b1[64 * 32 * 2];   // base layer 0   (64 x 32)
-  alignas(128) uint8_t b2[16 * 64 * 2];   // base layer 1   (16 x 64)
-  alignas(128) uint8_t b3[64 * 32 * 2];   // head layer 0   (64 x [SH16 | geo15 | 0])
-  alignas(128) uint8_t b4[64 * 64 * 2];   // head layer 1   (64 x 64)
-  alignas(128) uint8_t b5[16 * 64 * 2];   // head layer 2   (3 rows used of 16)
-  alignas(128) uint8_t a[128 * 64 * 2];   // A operand of the current layer (128 x K<=64)
+  // B operands (UMMA K-major layout, rows = output features), piece p at p * (one-piece size)
+  alignas(128) uint8_t b1[NP * 64 * 32 * 2];   // base layer 0   (64 x 32)
+  alignas(128) uint8_t b2[NP * 16 * 64 * 2];   // base layer 1   (16 x 64)
+  alignas(128) uint8_t b3[NP * 64 * 32 * 2];   // head layer 0   (64 x [SH16 | geo15 | 0])
+  alignas(128) uint8_t b4[NP * 64 * 64 * 2];   // head layer 1   (64 x 64)
+  alignas(128) uint8_t b5[NP * 16 * 64 * 2];   // head layer 2   (3 rows used of 16)
+  struct Group {
+    alignas(128) uint8_t a[NP * kAPiece];      // A operand of the current layer (128 x K<=64)
+    float sigma[kGroupSamples];
+    float rgb[kGroupSamples * 3];
+    float t_edge[kRaysPerGroup * (kS2 + 1)];
+    float ray_o[kRaysPerGroup * 3];
+    float ray_d[kRaysPerGroup * 3];
+    float s_edge[kRaysPerGroup * (kS2 + 1)];   // adjoint-seed mode only
+    alignas(8) uint64_t mbar;
+  } g[NG];
   float bias_b0[64], bias_b1[16], bias_h0[64], bias_h1[64], bias_h2[4];
-  float sigma[kGroupSamples];
-  float rgb[kGroupSamples * 3];
-  float t_edge[kRaysPerGroup * (kS2 + 1)];
-  float ray_o[kRaysPerGroup * 3];
-  float ray_d[kRaysPerGroup * 3];
   float app_tmp[kApp];
-  float s_edge[kRaysPerGroup * (kS2 + 1)];   // adjoint-seed mode only
-  alignas(8) uint64_t mbar;
   uint32_t tmem_slot;
-  int seed_max_bits;                         // adjoint-seed mode: max seed magnitude of this CTA (float bits)
+  int seed_max_bits;                           // adjoint-seed mode: max seed magnitude of this CTA (float bits)
 };
 
-using tc::stage_weight;
+// all threads of one group (the whole CTA when it has one group)
+template <int NG>
+__device__ __forceinline__ void group_sync(int grp) {
+  if (NG == 1) __syncthreads();
+  else asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
+}
 
-// accumulator row (64 columns) -> +bias, ReLU -> fp16 row of the next A operand (8 K-chunks)
-__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row,
-                                                uint4* keep = nullptr) {
+// accumulator row (64 columns) -> +bias, ReLU -> operand row of the next layer (8 K-chunks); returns the ReLU mask
+template <int NP>
+__device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
   tc::tmem_ld_wait();
+  uint32_t m[2] = {0u, 0u};
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
 #pragma unroll
     for (int hh = 0; hh < 2; ++hh) {
-      uint32_t w[4];
+      float x[8];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        int j = hh * 8 + q * 2;
-        float x0 = fmaxf(v[c][j] + bias[c * 16 + j], 0.f), x1 = fmaxf(v[c][j + 1] + bias[c * 16 + j + 1], 0.f);
-        w[q] = tc::pack_h2(x0, x1);
+      for (int q = 0; q < 8; ++q) {
+        x[q] = fmaxf(v[c][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
+        if (NP > 1) m[c >> 1] |= (x[q] > 0.f ? 1u : 0u) << ((c & 1) * 16 + hh * 8 + q);
       }
-      *reinterpret_cast<uint4*>(a + tc::chunk_off<128>(row, c * 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
-      if (keep) __stcs(keep + (c * 2 + hh) * 128 + row, make_uint4(w[0], w[1], w[2], w[3]));   // same layout, for the backward
+      tc::store_chunk<NP, 128>(a, kAPiece, row, c * 2 + hh, x);
     }
   }
+  return make_uint2(m[0], m[1]);
 }
 
-// make this thread's A-operand writes visible to the tensor core, then let one thread issue the layer
-template <int N, int K>
-__device__ __forceinline__ void run_layer(TcSmem* sm, const uint8_t* b, uint32_t tmem, uint32_t& phase, int tid,
-                                          uint8_t* keep = nullptr, uint32_t keep_bytes = 0, uint64_t policy = 0) {
+// make this thread's A-operand writes visible to the tensor core, then let one thread of the group issue the layer
+template <int N, int K, int NP, int NG>
+__device__ __forceinline__ void run_layer(typename TcSmem<NP, NG>::Group* G, const uint8_t* b, uint32_t tmem, uint32_t& phase,
+                                          int gt, int grp, uint8_t* keep = nullptr, uint32_t keep_bytes = 0, uint64_t policy = 0) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
-  __syncthreads();
-  if (tid == 0) {
+  group_sync<NG>(grp);
+  if (gt == 0) {
     tc::tc_fence_after();
-    tc::issue_layer<N, K>(tmem, sm->a, b, &sm->mbar);
+    tc::mma_chain_np<NP>(tmem, tc::op_kmajor(G->a, 128), kAPiece, tc::op_kmajor(b, N), N * K * 2, tc::idesc_f16(128, N), K / 16, false);
+    tc::mma_commit(&G->mbar);
     if (keep) {
-      // adjoint-seed mode: the A operand (= this layer's input rows, already in the tile layout) goes to the
-      // workspace through the TMA engine; the operand buffer is reused once the engine has read it
-      tc::bulk_s2g(keep, sm->a, keep_bytes, policy);
+      // adjoint-seed mode: the A operand (= this layer's input rows, already in the tile layout) goes to the workspace
+      // through the TMA engine - the fp16 operand, or the two leading bf16 pieces; the operand buffer is reused once the
+      // engine has read it
+#pragma unroll
+      for (int p = 0; p < (NP > 1 ? 2 : 1); ++p) tc::bulk_s2g(keep + p * keep_bytes, G->a + p * kAPiece, keep_bytes, policy);
       tc::bulk_wait_read();
     }
   }
-  tc::mbar_wait(&sm->mbar, phase);
+  tc::mbar_wait(&G->mbar, phase);
   phase ^= 1u;
   tc::tc_fence_after();
-  if (keep) __syncthreads();
+  if (keep) group_sync<NG>(grp);
 }
 
 // MODE 0: forward.  MODE 1: first pass of the backward (same forward, then the per-ray composite adjoint).
-template <int MODE>
-__global__ void __launch_bounds__(128)
+template <int MODE, int NP, int NG>
+__global__ void __launch_bounds__(128 * NG)
 k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  TcSmem* sm = reinterpret_cast<TcSmem*>(smem_raw);
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  using Smem = TcSmem<NP, NG>;
+  Smem* sm = reinterpret_cast<Smem*>(smem_raw);
+  constexpr int kThreads = 128 * NG;
+  constexpr int SP = NP > 1 ? 2 : 1;           // operand pieces kept for the backward
+  const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 7, gt = tid & 127, wq = gt >> 5;
+  typename Smem::Group* G = &sm->g[grp];
 
-  // ---- one-time setup: weights -> fp16 operands, biases, effective head bias, TMEM, mbarrier ------------
-  stage_weight<64, 32>(sm->b1, A.P.base_w0, 64, 32, 32, tid, 128);
-  stage_weight<16, 64>(sm->b2, A.P.base_w1, 16, 64, 64, tid, 128);
-  stage_weight<64, 32>(sm->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, 128);
-  stage_weight<64, 64>(sm->b4, A.P.head_w1, 64, 64, 64, tid, 128);
-  stage_weight<16, 64>(sm->b5, A.P.head_w2, 3, 64, 64, tid, 128);
-  for (int i = tid; i < 64; i += 128) { sm->bias_b0[i] = A.P.base_b0[i]; sm->bias_h1[i] = A.P.head_b1[i]; }
-  for (int i = tid; i < 16; i += 128) sm->bias_b1[i] = A.P.base_b1[i];
-  for (int i = tid; i < 4; i += 128) sm->bias_h2[i] = i < 3 ? A.P.head_b2[i] : 0.f;
-  for (int i = tid; i < kApp; i += 128) {
+  // ---- one-time setup: weights -> operands, biases, effective head bias, TMEM, mbarriers ------------
+  tc::stage_weight_np<64, 32, NP>(sm->b1, A.P.base_w0, 64, 32, 32, tid, kThreads);
+  tc::stage_weight_np<16, 64, NP>(sm->b2, A.P.base_w1, 16, 64, 64, tid, kThreads);
+  tc::stage_weight_np<64, 32, NP>(sm->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, kThreads);
+  tc::stage_weight_np<64, 64, NP>(sm->b4, A.P.head_w1, 64, 64, 64, tid, kThreads);
+  tc::stage_weight_np<16, 64, NP>(sm->b5, A.P.head_w2, 3, 64, 64, tid, kThreads);
+  for (int i = tid; i < 64; i += kThreads) { sm->bias_b0[i] = A.P.base_b0[i]; sm->bias_h1[i] = A.P.head_b1[i]; }
+  for (int i = tid; i < 16; i += kThreads) sm->bias_b1[i] = A.P.base_b1[i];
+  for (int i = tid; i < 4; i += kThreads) sm->bias_h2[i] = i < 3 ? A.P.head_b2[i] : 0.f;
+  for (int i = tid; i < kApp; i += kThreads) {
     sm->app_tmp[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
-  if (tid == 0) {
-    tc::mbar_init(&sm->mbar, 1);
-    tc::fence_mbar_init();
-    sm->seed_max_bits = 0;
-  }
+  if (gt == 0) tc::mbar_init(&G->mbar, 1);
+  if (tid == 0) sm->seed_max_bits = 0;
+  if (gt == 0) tc::fence_mbar_init();
   float seed_max = 0.f;
-  if (wid == 0) tc::tmem_alloc<64>(&sm->tmem_slot);
+  if (tid < 32) tc::tmem_alloc<64 * NG>(&sm->tmem_slot);
   __syncthreads();
-  for (int n = tid; n < 64; n += 128) {
+  for (int n = tid; n < 64; n += kThreads) {
     float b = A.P.head_b0[n];
     for (int k = 0; k < kApp; ++k) b = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], sm->app_tmp[k], b);
     sm->bias_h0[n] = b;
@@ -125,37 +147,37 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem = sm->tmem_slot;
-  const uint32_t taddr = tmem + ((uint32_t)(wid * 32) << 16);   // this warp's 32 TMEM lanes
+  const uint32_t tmem = sm->tmem_slot + (uint32_t)grp * 64;      // this group's 64 columns
+  const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16);     // this warp's 32 TMEM lanes
   uint32_t phase = 0;
   const uint64_t policy = MODE == 1 ? tc::l2_evict_first_policy() : 0;
 
   const int64_t n_groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
-  for (int64_t g = blockIdx.x; g < n_groups; g += gridDim.x) {
+  for (int64_t g = (int64_t)blockIdx.x * NG + grp; g < n_groups; g += (int64_t)gridDim.x * NG) {
     const int64_t r0 = g * kRaysPerGroup;
     const int rays_here = (int)min((int64_t)kRaysPerGroup, A.n - r0);
-    __syncthreads();
-    if (tid < kRaysPerGroup) {
+    group_sync<NG>(grp);
+    if (gt < kRaysPerGroup) {
       float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
-      if (tid < rays_here) load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r0 + tid,
-                                    ray_scale(M, A), o, d);
+      if (gt < rays_here) load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + r0 + gt,
+                                   ray_scale(M, A), o, d);
 #pragma unroll
-      for (int k = 0; k < 3; ++k) { sm->ray_o[tid * 3 + k] = o[k]; sm->ray_d[tid * 3 + k] = d[k]; }
+      for (int k = 0; k < 3; ++k) { G->ray_o[gt * 3 + k] = o[k]; G->ray_d[gt * 3 + k] = d[k]; }
     }
-    for (int i = tid; i < kRaysPerGroup * (kS2 + 1); i += 128) {
+    for (int i = gt; i < kRaysPerGroup * (kS2 + 1); i += 128) {
       int rr = i / (kS2 + 1);
-      sm->t_edge[i] = rr < rays_here ? A.t_edges2[r0 * (kS2 + 1) + i] : 0.f;
-      if (MODE == 1) sm->s_edge[i] = rr < rays_here ? A.s_edges2[r0 * (kS2 + 1) + i] : 0.f;
+      G->t_edge[i] = rr < rays_here ? A.t_edges2[r0 * (kS2 + 1) + i] : 0.f;
+      if (MODE == 1) G->s_edge[i] = rr < rays_here ? A.s_edges2[r0 * (kS2 + 1) + i] : 0.f;
     }
-    __syncthreads();
+    group_sync<NG>(grp);
 
     for (int tile = 0; tile < kGroupSamples / kTileM; ++tile) {
-      const int s = tile * kTileM + tid;
+      const int s = tile * kTileM + gt;
       const int rr = s / kS2, si = s % kS2;
-      const float t0 = sm->t_edge[rr * (kS2 + 1) + si], t1 = sm->t_edge[rr * (kS2 + 1) + si + 1];
+      const float t0 = G->t_edge[rr * (kS2 + 1) + si], t1 = G->t_edge[rr * (kS2 + 1) + si + 1];
       const float tsum = add_rn(t0, t1);
       float x[3], p[3], dirq[3];
-      rot_sample(A.rot, &sm->ray_o[rr * 3], &sm->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
+      rot_sample(A.rot, &G->ray_o[rr * 3], &G->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
       // ---- hash encoding: 4 levels = 8 values = one 16-byte K-chunk of this thread's A row ------------
@@ -168,51 +190,65 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
           level_cell<true>(p, M.main_grid.scal[l0 + j], M.main_grid.table_mask, (uint32_t)(l0 + j) * M.main_grid.table_size, cell[j]);
           gather_cell(A.P.main_table, cell[j], v[j]);
         }
-        uint32_t w[4];
+        float e8[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           float2 r = blend_cell(v[j], cell[j]);
-          w[j] = tc::pack_h2(r.x, r.y);
+          e8[2 * j] = r.x; e8[2 * j + 1] = r.y;
         }
-        *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, l0 >> 2)) = make_uint4(w[0], w[1], w[2], w[3]);
+        tc::store_chunk<NP, 128>(G->a, kAPiece, gt, l0 >> 2, e8);
         if (MODE == 1 && A.enc_tiles) {
-          // keep the row and its Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles)
-          uint32_t wj[12];
+          // keep the row's Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles): per level
+          // dx.xy dy.xy dz.xy, as fp16 pairs (NP = 1: 12 chunks per row) or in fp32 (split operands: 24 chunks per row)
+          if (NP == 1) {
+            uint32_t wj[12];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float2 dx, dy, dz;
-            blend_cell_grad(v[j], cell[j], dx, dy, dz);
-            wj[3 * j + 0] = tc::pack_h2_sat(dx.x, dx.y);
-            wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
-            wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
+            for (int j = 0; j < 4; ++j) {
+              float2 dx, dy, dz;
+              blend_cell_grad(v[j], cell[j], dx, dy, dz);
+              wj[3 * j + 0] = tc::pack_h2_sat(dx.x, dx.y);
+              wj[3 * j + 1] = tc::pack_h2_sat(dy.x, dy.y);
+              wj[3 * j + 2] = tc::pack_h2_sat(dz.x, dz.y);
+            }
+            uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * kJacTileBytes) + (l0 >> 2) * 3 * 128 + gt;
+            __stcs(jp, make_uint4(wj[0], wj[1], wj[2], wj[3]));
+            __stcs(jp + 128, make_uint4(wj[4], wj[5], wj[6], wj[7]));
+            __stcs(jp + 256, make_uint4(wj[8], wj[9], wj[10], wj[11]));
+          } else {
+            float4* jp = reinterpret_cast<float4*>(A.jac_tiles + tile_id * (2 * kJacTileBytes)) + (l0 >> 2) * 6 * 128 + gt;
+#pragma unroll
+            for (int j = 0; j < 4; j += 2) {
+              float2 dx0, dy0, dz0, dx1, dy1, dz1;
+              blend_cell_grad(v[j], cell[j], dx0, dy0, dz0);
+              blend_cell_grad(v[j + 1], cell[j + 1], dx1, dy1, dz1);
+              __stcs(jp + (3 * (j >> 1) + 0) * 128, make_float4(dx0.x, dx0.y, dy0.x, dy0.y));
+              __stcs(jp + (3 * (j >> 1) + 1) * 128, make_float4(dz0.x, dz0.y, dx1.x, dx1.y));
+              __stcs(jp + (3 * (j >> 1) + 2) * 128, make_float4(dy1.x, dy1.y, dz1.x, dz1.y));
+            }
           }
-          uint4* jp = reinterpret_cast<uint4*>(A.jac_tiles + tile_id * kJacTileBytes) + (l0 >> 2) * 3 * 128 + tid;
-          __stcs(jp, make_uint4(wj[0], wj[1], wj[2], wj[3]));
-          __stcs(jp + 128, make_uint4(wj[4], wj[5], wj[6], wj[7]));
-          __stcs(jp + 256, make_uint4(wj[8], wj[9], wj[10], wj[11]));
         }
       }
-      // adjoint-seed mode keeps the activations (fp16 operand rows) for k_field_backward_tc
+      // adjoint-seed mode keeps the activations (operand rows) for k_field_backward_tc: [H1 pieces | IN pieces]
       uint8_t* act = nullptr;
-      if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * kActTileBytes;
+      if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * (SP * kActTileBytes);
       // ---- base MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32>(sm, sm->b1, tmem, phase, tid, act ? A.enc_tiles + tile_id * kEncTileBytes : nullptr, 8192, policy);
-      epilogue_hidden(taddr, sm->bias_b0, sm->a, tid);
-      run_layer<16, 64>(sm, sm->b2, tmem, phase, tid, act, 16384, policy);
+      run_layer<64, 32, NP, NG>(G, sm->b1, tmem, phase, gt, grp, act ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr, 8192, policy);
+      epilogue_hidden<NP>(taddr, sm->bias_b0, G->a, gt);
+      run_layer<16, 64, NP, NG>(G, sm->b2, tmem, phase, gt, grp, act, 16384, policy);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
         tc::tmem_ld_wait();
         const float raw = v[0] + sm->bias_b1[0];
-        sm->sigma[s] = sel ? expf(raw) : 0.f;                         // trunc_exp * selector, fp32
+        G->sigma[s] = sel ? expf(raw) : 0.f;                          // trunc_exp * selector, fp32
         float c[16];
         sh16((dirq[0] + 1.f) * 0.5f, (dirq[1] + 1.f) * 0.5f, (dirq[2] + 1.f) * 0.5f, c);
-        uint32_t w[4];
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
+          float x8[8];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(c[hh * 8 + q * 2], c[hh * 8 + q * 2 + 1]);
-          *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+          for (int q = 0; q < 8; ++q) x8[q] = c[hh * 8 + q];
+          tc::store_chunk<NP, 128>(G->a, kAPiece, gt, hh, x8);
         }
         float gfe[16];
 #pragma unroll
@@ -220,36 +256,39 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         gfe[15] = MODE == 1 ? 1.f : 0.f;   // pad column (zero weights); the backward's wgrad reads it as a ones column
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
+          float x8[8];
 #pragma unroll
-          for (int q = 0; q < 4; ++q) w[q] = tc::pack_h2(gfe[hh * 8 + q * 2], gfe[hh * 8 + q * 2 + 1]);
-          *reinterpret_cast<uint4*>(sm->a + tc::chunk_off<128>(tid, 2 + hh)) = make_uint4(w[0], w[1], w[2], w[3]);
+          for (int q = 0; q < 8; ++q) x8[q] = gfe[hh * 8 + q];
+          tc::store_chunk<NP, 128>(G->a, kAPiece, gt, 2 + hh, x8);
         }
       }
       // ---- head MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32>(sm, sm->b3, tmem, phase, tid, act ? act + 16384 : nullptr, 8192, policy);
-      epilogue_hidden(taddr, sm->bias_h0, sm->a, tid);
-      // H2 / H3 are not kept: the backward recomputes them from IN (kernels.h)
-      run_layer<64, 64>(sm, sm->b4, tmem, phase, tid);
-      epilogue_hidden(taddr, sm->bias_h1, sm->a, tid);
-      run_layer<16, 64>(sm, sm->b5, tmem, phase, tid);
+      run_layer<64, 32, NP, NG>(G, sm->b3, tmem, phase, gt, grp, act ? act + SP * 16384 : nullptr, 8192, policy);
+      const uint2 m2 = epilogue_hidden<NP>(taddr, sm->bias_h0, G->a, gt);
+      // H2 / H3 are not kept: the backward recomputes them from IN (kernels.h); with split operands its recompute has
+      // 16 significant bits where this pass has 24, so the ReLU masks decided HERE are handed over
+      run_layer<64, 64, NP, NG>(G, sm->b4, tmem, phase, gt, grp);
+      const uint2 m3 = epilogue_hidden<NP>(taddr, sm->bias_h1, G->a, gt);
+      if (MODE == 1 && NP > 1 && A.masks4) __stcs(A.masks4 + tile_id * 128 + gt, make_uint4(m2.x, m2.y, m3.x, m3.y));
+      run_layer<16, 64, NP, NG>(G, sm->b5, tmem, phase, gt, grp);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
         tc::tmem_ld_wait();
 #pragma unroll
         for (int j = 0; j < 3; ++j)
-          sm->rgb[s * 3 + j] = expf(fminf(v[j] + sm->bias_h2[j] + M.rgb_bias, 88.f));   // SafeExp
+          G->rgb[s * 3 + j] = expf(fminf(v[j] + sm->bias_h2[j] + M.rgb_bias, 88.f));   // SafeExp
       }
       // the next tile's gather overwrites A: the last MMA has completed (waited above); TMEM loads are done
       tc::tc_fence_before();
-      __syncthreads();
+      group_sync<NG>(grp);
     }
 
     // composite: warp w handles rays w and w+4; lane handles samples lane and lane+32 (fp32, as field.cu)
-    for (int rr = wid; rr < rays_here; rr += 4) {
+    for (int rr = wq; rr < rays_here; rr += 4) {
       if (MODE == 1) {
-        seed_max = fmaxf(seed_max, composite_adjoint_ray<true>(M, A, &sm->t_edge[rr * (kS2 + 1)], &sm->s_edge[rr * (kS2 + 1)],
-                                                         &sm->sigma[rr * kS2], &sm->rgb[rr * kS2 * 3], r0 + rr, lane));
+        seed_max = fmaxf(seed_max, composite_adjoint_ray<true>(M, A, &G->t_edge[rr * (kS2 + 1)], &G->s_edge[rr * (kS2 + 1)],
+                                                         &G->sigma[rr * kS2], &G->rgb[rr * kS2 * 3], r0 + rr, lane));
         continue;
       }
       float ds[2], w[2];
@@ -258,8 +297,8 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         int si = k * 32 + lane;
         ds[k] = 0.f;
         if (si < kS2) {
-          float t0 = sm->t_edge[rr * (kS2 + 1) + si], t1 = sm->t_edge[rr * (kS2 + 1) + si + 1];
-          ds[k] = mul_rn(sub_rn(t1, t0), sm->sigma[rr * kS2 + si]);
+          float t0 = G->t_edge[rr * (kS2 + 1) + si], t1 = G->t_edge[rr * (kS2 + 1) + si + 1];
+          ds[k] = mul_rn(sub_rn(t1, t0), G->sigma[rr * kS2 + si]);
         }
       }
       weights_from_ds<2>(ds, w, lane);
@@ -268,7 +307,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       for (int k = 0; k < 2; ++k) {
         int si = k * 32 + lane;
         if (si < kS2) {
-          const float* c = &sm->rgb[(rr * kS2 + si) * 3];
+          const float* c = &G->rgb[(rr * kS2 + si) * 3];
           float r = c[0], gg = c[1], b = c[2];
           if (!A.training) { r = nan_to_num(r); gg = nan_to_num(gg); b = nan_to_num(b); }
           cr = fmaf(w[k], r, cr); cg = fmaf(w[k], gg, cg); cb = fmaf(w[k], b, cb);
@@ -278,7 +317,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       }
       cr = warp_sum(cr); cg = warp_sum(cg); cb = warp_sum(cb); acc = warp_sum(acc);
       if (lane == 0) {
-        const float* last = &sm->rgb[(rr * kS2 + kS2 - 1) * 3];
+        const float* last = &G->rgb[(rr * kS2 + kS2 - 1) * 3];
         float lr = last[0], lg = last[1], lb = last[2];
         if (!A.training) { lr = nan_to_num(lr); lg = nan_to_num(lg); lb = nan_to_num(lb); }
         float bg = 1.f - acc;
@@ -297,28 +336,30 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   if (MODE == 1 && A.g_absmax && tid == 0) atomicMax(reinterpret_cast<int*>(A.g_absmax), sm->seed_max_bits);
-  if (wid == 0) tc::tmem_dealloc<64>(tmem);
+  if (tid < 32) tc::tmem_dealloc<64 * NG>(sm->tmem_slot);
 }
 
-template <int MODE>
+template <int MODE, int NP, int NG>
 static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
-  size_t smem = sizeof(TcSmem) + 128;
+  size_t smem = sizeof(TcSmem<NP, NG>) + 128;
   if (attr_once.need()) {
-    cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE, NP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
-  int64_t ctas = groups < 148 * 4 ? groups : 148 * 4;     // persistent: 4 CTAs per SM share the tensor core
-  k_field_forward_tc<MODE><<<(unsigned)ctas, 128, smem, stream>>>(M, A);
+  const int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
+  // persistent: the groups of an SM (4 CTAs of one with fp16 operands, one CTA of two with split operands) share its
+  // tensor core
+  const int64_t want = (groups + NG - 1) / NG, cap = 148 * (NP == 1 ? 4 : 1);
+  k_field_forward_tc<MODE, NP, NG><<<(unsigned)(want < cap ? want : cap), 128 * NG, smem, stream>>>(M, A);
   return cudaGetLastError();
 }
-cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
-  return launch_tc_mode<0>(M, A, stream);
+cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces) {
+  return pieces > 1 ? launch_tc_mode<0, 3, 2>(M, A, stream) : launch_tc_mode<0, 1, 1>(M, A, stream);
 }
-cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
-  return launch_tc_mode<1>(M, A, stream);
+cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces) {
+  return pieces > 1 ? launch_tc_mode<1, 3, 2>(M, A, stream) : launch_tc_mode<1, 1, 1>(M, A, stream);
 }
 
 }  // namespace nemit

@@ -103,6 +103,10 @@ struct FieldArgs : RayArgs {
   // d loss / d (rgb pre-activation xyz, density pre-activation w) per sample, i.e. the seeds with the SafeExp /
   // trunc_exp derivatives and the selector already applied (written instead of g_sigma / g_rgbs when set)
   float4* seeds4;
+  // split-operand tensor-core mode only: the ReLU masks of the two head hidden layers per sample (bits 0..63 = H2 units,
+  // 64..127 = H3 units), decided by the seed pass at 24 significant bits and applied by k_field_backward_tc, whose own
+  // recompute of H2 / H3 has 16
+  uint4* masks4;
   // light-point-cloud pass (SdfNerfactoModel.get_point_lights, NS/models/sdf_nerfacto.py:189-212): the adjoint seed is
   // the same luminance weight vector for every ray (calc_brightness_grad, NS/models/nerfacto.py:547-573), the pass also
   // writes the composited rgb and the "contrib" depth (DepthRenderer, NS/model_components/renderers.py:389-397)
@@ -135,6 +139,7 @@ struct FieldBwdArgs : RayArgs {
   const uint8_t* jac_tiles;
   const uint8_t* act_tiles;
   const float4* seeds4;
+  const uint4* masks4;           // split-operand mode: see FieldArgs
   unsigned long long* red_ops;   // or null: device counter of the reduction lane-ops the table scatter issues (profiling)
 };
 
@@ -244,12 +249,13 @@ cudaError_t launch_emitter_local_rays(const float* m34, const float* bmin, const
                                       float* o_out, float* v_out, float* near_out, cudaStream_t stream);
 cudaError_t launch_sample_levels(const ModelDev& M, const SampleArgs& A, cudaStream_t stream, bool fast = false);
 cudaError_t launch_field_forward(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
-cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
-cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
+// pieces = 1: fp16 operands; 2: fp32 arithmetic through split bf16 operands (forward: 3 pieces; reverse: 2 + the forward's ReLU masks)
+cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces = 1);
+cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces = 1);
 cudaError_t launch_field_adjoint_seed(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_jvp(const ModelDev& M, const FieldArgs& A, cudaStream_t stream);
 cudaError_t launch_field_backward(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
-cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream);
+cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream, int pieces = 1);
 cudaError_t launch_prop_backward(const ModelDev& M, const PropBwdArgs& A, cudaStream_t stream);
 cudaError_t launch_finalize_ray_grads(const ModelDev& M, const FinalizeArgs& A, cudaStream_t stream);
 cudaError_t launch_hash_encode(const GridDev& G, const float2* table, const float* x, int64_t n, float* out,

@@ -9,6 +9,7 @@
 // One tcgen05.mma of kind::f16 consumes K = 16, i.e. two K-chunks; k-step j starts at byte 2 * j * LBO.
 // The accumulator D (M = 128 rows, N fp32 columns) sits in TMEM: row m = lane m, column n = column n.
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -203,6 +204,90 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
 // saturating variant for gradient operands: +-inf would poison a whole accumulator column
 __device__ __forceinline__ uint32_t pack_h2_sat(float a, float b) {
   return pack_h2(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
+}
+
+// ---- split precision (NP = 2, 3) ---------------------------------------------------------------------
+// "fp32 on the tensor cores": every operand element is carried as NP bf16 pieces x0 + x1 (+ x2) with x0 = rn_bf16(x),
+// x1 = rn_bf16(x - x0), x2 = rn_bf16(x - x0 - x1): 16 (NP = 2) or 24 (NP = 3) significant bits and fp32's exponent range,
+// so no operand scaling is needed.  Each piece has its own buffer in the SAME layout as the fp16 operand, and a product
+// A * B is the sum of the piece products A_i B_j with i + j < NP (3 or 6 MMAs into one fp32 accumulator, smallest terms
+// first; the dropped terms are below 2^-8NP of the product).  NP = 1 is the fp16 path.
+template <int NP>
+struct OpFmt { static constexpr uint32_t bits = (1u << 7) | (1u << 10); };         // a_format = b_format = BF16
+template <>
+struct OpFmt<1> { static constexpr uint32_t bits = 0u; };                          // a_format = b_format = F16
+
+__device__ __forceinline__ uint32_t bf16x2_rn(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+// one pair of operand elements -> w[0] (the fp16 pair, or the leading bf16 pair), w[1], w[2] (the lower bf16 pieces);
+// SAT clamps to the finite range first (gradient operands: +-inf would poison a whole accumulator column)
+template <int NP, bool SAT = false>
+__device__ __forceinline__ void pack_pair(float a, float b, uint32_t (&w)[3]) {
+  if (NP == 1) {
+    w[0] = SAT ? pack_h2_sat(a, b) : pack_h2(a, b);
+  } else {
+    if (SAT) { a = fminf(fmaxf(a, -3.0e38f), 3.0e38f); b = fminf(fmaxf(b, -3.0e38f), 3.0e38f); }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      w[p] = bf16x2_rn(a, b);
+      if (p + 1 < NP) { a -= __uint_as_float(w[p] << 16); b -= __uint_as_float(w[p] & 0xffff0000u); }
+    }
+  }
+}
+// eight consecutive K elements of row `row` (= the 16-byte chunk kc) of an R-row operand; piece p at buf + p * piece_bytes
+template <int NP, int R, bool SAT = false>
+__device__ __forceinline__ void store_chunk(uint8_t* buf, uint32_t piece_bytes, int row, int kc, const float (&x)[8]) {
+  uint32_t w[4][3];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) pack_pair<NP, SAT>(x[2 * q], x[2 * q + 1], w[q]);
+#pragma unroll
+  for (int p = 0; p < NP; ++p)
+    *reinterpret_cast<uint4*>(buf + p * piece_bytes + chunk_off<R>(row, kc)) = make_uint4(w[0][p], w[1][p], w[2][p], w[3][p]);
+}
+// D (+)= A * B^T with NP-piece operands: piece p of an operand sits p * (a_piece | b_piece) bytes after piece 0; a piece
+// stride of 0 says the operand has one piece only (exactly representable values: the ones operand)
+template <int NP>
+__device__ __forceinline__ void mma_chain_np(uint32_t d_tmem, const Operand& a, uint32_t a_piece, const Operand& b,
+                                             uint32_t b_piece, uint32_t idesc, int ksteps, bool accumulate) {
+  const uint32_t id = idesc | OpFmt<NP>::bits;
+  bool acc = accumulate;
+#pragma unroll
+  for (int order = NP - 1; order >= 0; --order) {          // order = i + j: the small products first
+#pragma unroll
+    for (int i = 0; i <= order; ++i) {
+      const int j = order - i;
+      if ((i > 0 && a_piece == 0) || (j > 0 && b_piece == 0)) continue;
+      Operand ai = a, bj = b;
+      ai.addr += i * a_piece;
+      bj.addr += j * b_piece;
+      mma_chain(d_tmem, ai, bj, id, ksteps, acc);
+      acc = true;
+    }
+  }
+}
+
+// W (rows x cols_src, torch (out,in) layout, fp32) -> K-major operand buffer(s) with R rows and K columns (fp16, or
+// NP bf16 pieces R * K * 2 bytes apart); entries outside [rows, cols_used) are zero.
+template <int R, int K, int NP>
+__device__ __forceinline__ void stage_weight_np(uint8_t* dst, const float* __restrict__ W, int rows, int cols_src,
+                                                int cols_used, int tid, int nthreads) {
+  for (int i = tid; i < R * K; i += nthreads) {
+    int n = i / K, k = i % K;
+    float v = (n < rows && k < cols_used) ? W[n * cols_src + k] : 0.f;
+    uint8_t* at = dst + chunk_off<R>(n, k >> 3) + (k & 7) * 2;
+    if (NP == 1) {
+      *reinterpret_cast<__half*>(at) = __float2half_rn(v);
+    } else {
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        const __nv_bfloat16 piece = __float2bfloat16_rn(v);
+        *reinterpret_cast<__nv_bfloat16*>(at + p * (R * K * 2)) = piece;
+        v -= __bfloat162float(piece);
+      }
+    }
+  }
 }
 
 // W (rows x cols_src, torch (out,in) layout, fp32) -> fp16 K-major operand buffer with R rows and K columns;

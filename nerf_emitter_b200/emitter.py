@@ -182,8 +182,10 @@ class NerfEmitter:
         return self.allreduce_blob(self.flat_grads, group, scale)
 
     def set_precision(self, precision: str = "fp32"):
-        """'fp32' = exact FMA path (parity mode); 'fp16' = fp16-operand tensor-core MLP (tcgen05, fp32 accumulate)."""
-        code = {"fp32": 0, "fp16": 1}[precision]
+        """'fp32' = exact FMA path (parity mode); 'fp16' = fp16-operand tensor-core MLP (tcgen05, fp32 accumulate);
+        'split' = fp32 MLP arithmetic on the tensor cores through split bf16 operands (forward: three pieces = 24
+        significant bits; reverse: two pieces + the forward's ReLU masks)."""
+        code = {"fp32": 0, "fp16": 1, "split": 2}[precision]
         L.check(self.lib.nemit_set_precision(self._h, code), "nemit_set_precision")
         self.precision = precision
         return self

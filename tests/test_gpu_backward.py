@@ -11,15 +11,18 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-3
 
 
-@pytest.fixture(scope="module")
-def emitters(spec, params_factory):
+# every test of this module runs twice: on the fp32 FMA kernels and on the tensor-core kernels with split bf16 operands
+# (NEMIT_PRECISION_SPLIT_TC) - the same 1e-3 gates hold for both
+@pytest.fixture(scope="module", params=["fp32", "split"])
+def emitters(request, spec, params_factory):
     from nerf_emitter_b200 import NerfEmitter
     cache = {}
 
     def get(seed, scale):
         if (seed, scale) not in cache:
             cache[(seed, scale)] = NerfEmitter(params_factory(seed, scale), spec, device=torch.device("cuda:0"))
-        return cache[(seed, scale)]
+        return cache[(seed, scale)].set_precision(request.param).set_sampler("exact")
+    get.mode = request.param
     return get
 
 
@@ -142,7 +145,8 @@ def test_backward_end_to_end_default_init_4096(prg, spec, params_factory, emitte
     +-1 ulp of the origins).  Measured on B200: 98.3 - 98.5 % of the rays within 1e-3, worst ray 0.11 (training) / 0.02
     (eval).  Gate: >= 97 % within 1e-3, none beyond 0.25, and the share of deviating rays not above twice the
     reference's own; parameter gradients (sums over all rays) within max(1e-3, 4 x the reference's own movement).
-    The every-ray strict gate is test_derivatives_strict_given_same_samples."""
+    The every-ray strict gate is test_derivatives_strict_given_same_samples.
+    The split-operand tensor-core mode runs the same gates."""
     from oracle.nerfacto_oracle import OracleEmitter
     P = params_factory(0, 1.0)
     O = OracleEmitter(P, spec)

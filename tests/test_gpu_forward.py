@@ -11,15 +11,17 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-3
 
 
-@pytest.fixture(scope="module")
-def emitters(spec, params_factory):
+# every test of this module runs twice: on the fp32 FMA kernels and on the tensor-core kernels with split bf16 operands
+# (NEMIT_PRECISION_SPLIT_TC) - the same 1e-3 gates hold for both
+@pytest.fixture(scope="module", params=["fp32", "split"])
+def emitters(request, spec, params_factory):
     from nerf_emitter_b200 import NerfEmitter
     cache = {}
 
     def get(seed, scale):
         if (seed, scale) not in cache:
             cache[(seed, scale)] = NerfEmitter(params_factory(seed, scale), spec, device=torch.device("cuda:0"))
-        return cache[(seed, scale)]
+        return cache[(seed, scale)].set_precision(request.param).set_sampler("exact")
     return get
 
 
