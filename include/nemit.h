@@ -223,6 +223,16 @@ int nemit_forward(NemitHandle* h, const NemitRays* rays, float* rgb, float* accu
                   const NemitLevelsOut* levels_or_null, void* workspace, size_t workspace_bytes,
                   void* stream);
 
+/* nemit_forward for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  The call allocates
+ * nothing and takes no workspace: its scratch (the final sample edges, 49 floats per ray) is a static device array of
+ * NEMIT_NOALLOC_MAX_RAYS rays = 3.06 MiB that every GPU loading the library holds until exit.  rays->n above the maximum
+ * is rejected with NEMIT_E_INVALID.  Same results as nemit_forward (same kernels); rgb (N,3) only, no per-level outputs,
+ * no profile records.  All calls share the one array: calls that overlap on a GPU (different streams) race - serialise
+ * them. */
+#define NEMIT_NOALLOC_MAX_RAYS 16384
+int nemit_forward_noalloc(NemitHandle* h, const NemitRays* rays, float* rgb, void* stream);
+
 /* proposal loop only: ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) */
 int nemit_sample_levels(NemitHandle* h, const NemitRays* rays, const NemitLevelsOut* out,
                         void* workspace, size_t workspace_bytes, void* stream);

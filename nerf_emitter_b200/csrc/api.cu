@@ -1,5 +1,6 @@
 // api.cu - the C ABI of libnerfemitter.so (include/nemit.h): handle, argument checks, chunking,
 // workspace carving, kernel launches.  No torch types, no allocation of parameter memory.
+#include <mutex>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -1180,4 +1181,63 @@ extern "C" int nemit_vmf_pdf_direction(const NemitVmfLobes* lobes, const NemitVm
   cudaError_t e = launch_vmf_pdf(lobes->position, lobes->weight, lobes->std, lobes->num_lobes, it_p, ds_d, n, pdf,
                                  (cudaStream_t)stream, &F);
   return e == cudaSuccess ? NEMIT_OK : cuda_fail(e, "k_vmf_pdf");
+}
+
+// ---------------------------------------------------------------------------------------------
+// allocation-free forward (no counterpart in the reference)
+// ---------------------------------------------------------------------------------------------
+// nemit_forward without a caller-provided workspace, for callers that cannot allocate device memory (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc).  The one piece of scratch the forward needs - the final sample
+// edges t_edges2 that k_sample_levels writes and k_field_forward(_tc) reads, (n, 49) floats - lives in a file-scope device
+// array of NEMIT_NOALLOC_MAX_RAYS x 49 floats = 3.06 MiB, held by every GPU that loads the library until exit.
+// In host code `g_noalloc_edges` is only a stand-in for the symbol: its device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and it is that pointer which goes to the kernels.
+// Nothing in the array has to start at zero (the sampler writes rows [0, n) before the field kernel reads exactly those
+// rows), so no clearing pass; every call shares the array and calls that overlap on one GPU (two streams) race on it.
+static __device__ __align__(256) float g_noalloc_edges[(size_t)NEMIT_NOALLOC_MAX_RAYS * (kS2 + 1)];
+
+static cudaError_t noalloc_edges_ptr(int device, float** out) {
+  static float* ptr[64] = {};
+  static std::mutex mu;
+  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_edges);      // the calling thread's current device = `device`
+    if (e != cudaSuccess) return e;
+    ptr[device] = static_cast<float*>(p);
+  }
+  *out = ptr[device];
+  return cudaSuccess;
+}
+
+extern "C" int nemit_forward_noalloc(NemitHandle* h, const NemitRays* rays, float* rgb, void* stream) {
+  int rc = check_rays(h, rays, "nemit_forward_noalloc");
+  if (rc) return rc;
+  if (rays->n > NEMIT_NOALLOC_MAX_RAYS)
+    return fail(NEMIT_E_INVALID, "nemit_forward_noalloc: %s", "more rays than NEMIT_NOALLOC_MAX_RAYS (16384): split the batch or use nemit_forward");
+  if (rays->n == 0) return NEMIT_OK;
+  if (!rgb) return fail(NEMIT_E_INVALID, "nemit_forward_noalloc: null rgb output%s");
+  DeviceGuard guard(h->device);
+  float* t_edges = nullptr;
+  cudaError_t e = noalloc_edges_ptr(h->device, &t_edges);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_edges)");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t n = rays->n;
+  SampleArgs S;
+  fill_sample_args(h, S, rays, 0, n);
+  S.t_edges2 = t_edges;
+  const bool fast = h->sampler == NEMIT_SAMPLER_FAST;
+  if ((e = launch_sample_levels(h->M, S, st, fast)) != cudaSuccess) return cuda_fail(e, "k_sample_levels");
+  h->launches += fast ? 2 : 1;       // (no event bracketing here: the profile ring creates its events on first use)
+  FieldArgs F;
+  memset(&F, 0, sizeof(F));
+  fill_ray_args(h, F, rays, 0, n, true);
+  fill_field_params(h->P, F.P);
+  F.t_edges2 = t_edges;
+  F.rgb = rgb;
+  e = tc_mode(h) ? launch_field_forward_tc(h->M, F, st, tc_pieces(h)) : launch_field_forward(h->M, F, st);
+  if (e != cudaSuccess) return cuda_fail(e, "k_field_forward");
+  h->launches++;
+  return NEMIT_OK;
 }

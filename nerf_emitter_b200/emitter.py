@@ -349,6 +349,17 @@ class NerfEmitter:
         aux["accumulation"] = acc
         return rgb, aux
 
+    def render_noalloc(self, o3n: torch.Tensor, v3n: torch.Tensor, rgb_out: torch.Tensor, near=0.0, camera_idx: int = 0,
+                       jitter=None):
+        """nemit_forward_noalloc: the forward with its scratch in a static device array of the library (at most
+        lib.NOALLOC_MAX_RAYS rays); no device allocation in the call - the caller passes the output too."""
+        n = o3n.shape[1]
+        if not rgb_out.is_cuda or rgb_out.dtype != torch.float32 or not rgb_out.is_contiguous() or rgb_out.shape != (n, 3):
+            raise ValueError("rgb_out must be a contiguous fp32 (N, 3) device tensor")
+        R = self._rays(o3n, v3n, near, camera_idx, jitter, False)
+        L.check(self.lib.nemit_forward_noalloc(self._h, C.byref(R), _ptr(rgb_out), self._stream()), "nemit_forward_noalloc")
+        return rgb_out
+
     def sample_levels(self, o3n, v3n, near=0.0, camera_idx: int = 0, jitter=None, edges_only: bool = False,
                       nerf_layout: bool = False):
         """ProposalNetworkSampler.generate_ray_samples (ray_samplers.py:584-626) for emitter rays.

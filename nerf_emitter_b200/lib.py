@@ -141,6 +141,7 @@ SYMBOLS = {
     "nemit_vmf_pdf_direction": (C.c_int, [C.POINTER(NemitVmfLobes), C.POINTER(NemitVmfFrame), C.c_void_p, C.c_void_p,
                                           C.c_int64, C.c_void_p, C.c_void_p]),
     "nemit_forward_host": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "nemit_forward_noalloc": (C.c_int, [_H, C.POINTER(NemitRays), C.c_void_p, C.c_void_p]),
     "nemit_launch_count": (C.c_int64, [_H]),
     "nemit_set_sampler": (C.c_int, [_H, C.c_int32]),
     "nemit_profile_enable": (C.c_int, [_H, C.c_int32]),
@@ -157,6 +158,7 @@ SYMBOLS = {
 }
 
 MICROBENCH_KINDS = ["gather_l1miss", "gather_l1hit", "gather_coherent", "red", "l2_read"]
+NOALLOC_MAX_RAYS = 16384        # NEMIT_NOALLOC_MAX_RAYS
 UNIQUE_ID_BYTES = 128
 
 PROFILE_KINDS = ["k_sample_levels", "k_field_forward", "k_field_forward<adjoint_seed>", "k_field_backward",
