@@ -15,9 +15,13 @@
 //           NS/models/base_model.py:305, NS/field_components/mlp.py:117-144), BASELINE.json configs[1]; one group per
 //           CTA, four CTAs per SM.
 //   NP = 3  fp32 arithmetic on the tensor cores: every operand as three bf16 pieces (24 significant bits), six MMAs per
-//           layer (tc_common.cuh).  The weights take 60 KB, so one CTA per SM holds them once for TWO groups of 128
-//           threads (named barriers, 64 TMEM columns each).  The seed pass of this mode keeps the two leading pieces
-//           of E / H1 / IN, the Jacobian in fp32 and the ReLU masks of the two head layers for k_field_backward_tc.
+//           layer (tc_common.cuh).  The weights take 60 KB of shared memory, so one CTA per SM holds them once for THREE
+//           groups of 128 threads (named barriers), and the A operand does not go through shared memory at all: a thread
+//           writes its row of the three pieces straight into TENSOR MEMORY (tcgen05.st; lane = row, 32 columns per
+//           piece) and the MMAs take A from there (the .ts form) - 64 accumulator + 96 operand columns per group, 480
+//           of the SM's 512.  The seed pass of this mode keeps the two leading pieces of E / H1 / IN (written by the
+//           threads in the tile layout), the Jacobian in fp32 and the ReLU masks of the two head layers for
+//           k_field_backward_tc.
 //
 // Reference: NerfactoField.get_density / get_outputs (NS/fields/nerfacto_field.py:228-334), MLP
 // (NS/field_components/mlp.py:163-183).
@@ -28,7 +32,13 @@
 namespace nemit {
 
 constexpr uint32_t kAPiece = 128 * 64 * 2;
-template <int NP, int NG>
+constexpr uint32_t kAPieceCols = 32;            // A in tensor memory: 64 K-elements of 16 bits per row and piece
+#ifndef NEMIT_SPLIT_ATM
+#define NEMIT_SPLIT_ATM 1                       // split-operand mode: A operand in tensor memory (0: in shared memory, two groups)
+#endif
+constexpr bool kSplitAtm = NEMIT_SPLIT_ATM != 0;
+constexpr int kSplitGroups = kSplitAtm ? 3 : 2;
+template <int NP, int NG, bool ATM>
 struct TcSmem {
   // B operands (UMMA K-major layout, rows = output features), piece p at p * (one-piece size)
   alignas(128) uint8_t b1[NP * 64 * 32 * 2];   // base layer 0   (64 x 32)
@@ -37,7 +47,7 @@ struct TcSmem {
   alignas(128) uint8_t b4[NP * 64 * 64 * 2];   // head layer 1   (64 x 64)
   alignas(128) uint8_t b5[NP * 16 * 64 * 2];   // head layer 2   (3 rows used of 16)
   struct Group {
-    alignas(128) uint8_t a[NP * kAPiece];      // A operand of the current layer (128 x K<=64)
+    alignas(128) uint8_t a[ATM ? 128 : NP * kAPiece];   // A operand of the current layer (128 x K<=64) unless it lives in TMEM
     float sigma[kGroupSamples];
     float rgb[kGroupSamples * 3];
     float t_edge[kRaysPerGroup * (kS2 + 1)];
@@ -59,9 +69,34 @@ __device__ __forceinline__ void group_sync(int grp) {
   else asm volatile("bar.sync %0, 128;" ::"r"(grp + 1) : "memory");
 }
 
+// where a thread's row of the next A operand goes: the shared-memory operand buffer (the stash copy is then made from
+// there by the TMA engine, run_layer), or this thread's TMEM lane (ATM; the kept pieces are then stored from registers)
+template <int NP, bool ATM>
+struct AOut {
+  uint8_t* smem;         // !ATM
+  uint32_t taddr;        // ATM: column base of piece 0, this warp's lanes
+  int row;
+  uint8_t* keep;         // ATM: tile of the kept operand in the workspace, or null
+  uint32_t keep_bytes;   // ATM: bytes of one kept piece
+  __device__ __forceinline__ void put(int kc, const float (&x)[8]) const {
+    if (!ATM) {
+      tc::store_chunk<NP, 128>(smem, kAPiece, row, kc, x);
+    } else {
+      uint32_t w[4][3];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) tc::pack_pair<NP>(x[2 * q], x[2 * q + 1], w[q]);
+#pragma unroll
+      for (int p = 0; p < NP; ++p) {
+        tc::tmem_st4(taddr + p * kAPieceCols + kc * 4, w[0][p], w[1][p], w[2][p], w[3][p]);
+        if (keep && p < 2) __stcs(reinterpret_cast<uint4*>(keep + p * keep_bytes) + kc * 128 + row, make_uint4(w[0][p], w[1][p], w[2][p], w[3][p]));
+      }
+    }
+  }
+};
+
 // accumulator row (64 columns) -> +bias, ReLU -> operand row of the next layer (8 K-chunks); returns the ReLU mask
-template <int NP>
-__device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* a, int row) {
+template <int NP, bool ATM>
+__device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, const AOut<NP, ATM>& out) {
   float v[4][16];
 #pragma unroll
   for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
@@ -77,16 +112,32 @@ __device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __
         x[q] = fmaxf(v[c][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
         if (NP > 1) m[c >> 1] |= (x[q] > 0.f ? 1u : 0u) << ((c & 1) * 16 + hh * 8 + q);
       }
-      tc::store_chunk<NP, 128>(a, kAPiece, row, c * 2 + hh, x);
+      out.put(c * 2 + hh, x);
     }
   }
   return make_uint2(m[0], m[1]);
 }
 
 // make this thread's A-operand writes visible to the tensor core, then let one thread of the group issue the layer
-template <int N, int K, int NP, int NG>
-__device__ __forceinline__ void run_layer(typename TcSmem<NP, NG>::Group* G, const uint8_t* b, uint32_t tmem, uint32_t& phase,
+template <int N, int K, int NP, int NG, bool ATM>
+__device__ __forceinline__ void run_layer(typename TcSmem<NP, NG, ATM>::Group* G, const uint8_t* b, uint32_t tmem, uint32_t& phase,
                                           int gt, int grp, uint8_t* keep = nullptr, uint32_t keep_bytes = 0, uint64_t policy = 0) {
+  if (ATM) {
+    // the rows were written with tcgen05.st: complete them, order them before the barrier; D = columns [0, 64), A pieces
+    // from column 64 (the kept pieces went out from the registers, AOut::put)
+    tc::tmem_st_wait();
+    tc::tc_fence_before();
+    group_sync<NG>(grp);
+    if (gt == 0) {
+      tc::tc_fence_after();
+      tc::mma_chain_np_ts<NP>(tmem, tmem + 64, kAPieceCols, tc::op_kmajor(b, N), N * K * 2, tc::idesc_f16(128, N), K / 16, false);
+      tc::mma_commit(&G->mbar);
+    }
+    tc::mbar_wait(&G->mbar, phase);
+    phase ^= 1u;
+    tc::tc_fence_after();
+    return;
+  }
   tc::fence_proxy_async();
   tc::tc_fence_before();
   group_sync<NG>(grp);
@@ -114,7 +165,11 @@ template <int MODE, int NP, int NG>
 __global__ void __launch_bounds__(128 * NG)
 k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  using Smem = TcSmem<NP, NG>;
+  constexpr bool ATM = NP > 1 && kSplitAtm;    // A operand in tensor memory
+  constexpr int kGroupCols = ATM ? 64 + NP * (int)kAPieceCols : 64;
+  constexpr int kAllocCols = NG * kGroupCols <= 64 ? 64 : (NG * kGroupCols <= 128 ? 128 : (NG * kGroupCols <= 256 ? 256 : 512));
+  static_assert(NG * kGroupCols <= 512, "tensor memory of one SM");
+  using Smem = TcSmem<NP, NG, ATM>;
   Smem* sm = reinterpret_cast<Smem*>(smem_raw);
   constexpr int kThreads = 128 * NG;
   constexpr int SP = NP > 1 ? 2 : 1;           // operand pieces kept for the backward
@@ -137,7 +192,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   if (tid == 0) sm->seed_max_bits = 0;
   if (gt == 0) tc::fence_mbar_init();
   float seed_max = 0.f;
-  if (tid < 32) tc::tmem_alloc<64 * NG>(&sm->tmem_slot);
+  if (tid < 32) tc::tmem_alloc<kAllocCols>(&sm->tmem_slot);
   __syncthreads();
   for (int n = tid; n < 64; n += kThreads) {
     float b = A.P.head_b0[n];
@@ -147,7 +202,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem = sm->tmem_slot + (uint32_t)grp * 64;      // this group's 64 columns
+  const uint32_t tmem = sm->tmem_slot + (uint32_t)grp * kGroupCols;   // this group's columns: accumulator, then A pieces
   const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16);     // this warp's 32 TMEM lanes
   uint32_t phase = 0;
   const uint64_t policy = MODE == 1 ? tc::l2_evict_first_policy() : 0;
@@ -180,6 +235,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       rot_sample(A.rot, &G->ray_o[rr * 3], &G->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
+      AOut<NP, ATM> aout{G->a, taddr + 64, gt, nullptr, 0};
       // ---- hash encoding: 4 levels = 8 values = one 16-byte K-chunk of this thread's A row ------------
 #pragma unroll 1
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
@@ -196,7 +252,9 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
           float2 r = blend_cell(v[j], cell[j]);
           e8[2 * j] = r.x; e8[2 * j + 1] = r.y;
         }
-        tc::store_chunk<NP, 128>(G->a, kAPiece, gt, l0 >> 2, e8);
+        aout.keep = (ATM && MODE == 1 && A.enc_tiles) ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr;
+        aout.keep_bytes = 8192;
+        aout.put(l0 >> 2, e8);
         if (MODE == 1 && A.enc_tiles) {
           // keep the row's Jacobian for the backward kernel (coalesced 16-byte stores, chunk-major tiles): per level
           // dx.xy dy.xy dz.xy, as fp16 pairs (NP = 1: 12 chunks per row) or in fp32 (split operands: 24 chunks per row)
@@ -232,9 +290,11 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       uint8_t* act = nullptr;
       if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * (SP * kActTileBytes);
       // ---- base MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32, NP, NG>(G, sm->b1, tmem, phase, gt, grp, act ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr, 8192, policy);
-      epilogue_hidden<NP>(taddr, sm->bias_b0, G->a, gt);
-      run_layer<16, 64, NP, NG>(G, sm->b2, tmem, phase, gt, grp, act, 16384, policy);
+      run_layer<64, 32, NP, NG, ATM>(G, sm->b1, tmem, phase, gt, grp, act ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr, 8192, policy);
+      aout.keep = ATM ? act : nullptr;
+      aout.keep_bytes = 16384;
+      epilogue_hidden<NP, ATM>(taddr, sm->bias_b0, aout);
+      run_layer<16, 64, NP, NG, ATM>(G, sm->b2, tmem, phase, gt, grp, act, 16384, policy);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
@@ -243,12 +303,14 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         G->sigma[s] = sel ? expf(raw) : 0.f;                          // trunc_exp * selector, fp32
         float c[16];
         sh16((dirq[0] + 1.f) * 0.5f, (dirq[1] + 1.f) * 0.5f, (dirq[2] + 1.f) * 0.5f, c);
+        aout.keep = (ATM && act) ? act + SP * 16384 : nullptr;
+        aout.keep_bytes = 8192;
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {
           float x8[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) x8[q] = c[hh * 8 + q];
-          tc::store_chunk<NP, 128>(G->a, kAPiece, gt, hh, x8);
+          aout.put(hh, x8);
         }
         float gfe[16];
 #pragma unroll
@@ -259,18 +321,19 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
           float x8[8];
 #pragma unroll
           for (int q = 0; q < 8; ++q) x8[q] = gfe[hh * 8 + q];
-          tc::store_chunk<NP, 128>(G->a, kAPiece, gt, 2 + hh, x8);
+          aout.put(2 + hh, x8);
         }
+        aout.keep = nullptr;
       }
       // ---- head MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32, NP, NG>(G, sm->b3, tmem, phase, gt, grp, act ? act + SP * 16384 : nullptr, 8192, policy);
-      const uint2 m2 = epilogue_hidden<NP>(taddr, sm->bias_h0, G->a, gt);
+      run_layer<64, 32, NP, NG, ATM>(G, sm->b3, tmem, phase, gt, grp, act ? act + SP * 16384 : nullptr, 8192, policy);
+      const uint2 m2 = epilogue_hidden<NP, ATM>(taddr, sm->bias_h0, aout);
       // H2 / H3 are not kept: the backward recomputes them from IN (kernels.h); with split operands its recompute has
       // 16 significant bits where this pass has 24, so the ReLU masks decided HERE are handed over
-      run_layer<64, 64, NP, NG>(G, sm->b4, tmem, phase, gt, grp);
-      const uint2 m3 = epilogue_hidden<NP>(taddr, sm->bias_h1, G->a, gt);
+      run_layer<64, 64, NP, NG, ATM>(G, sm->b4, tmem, phase, gt, grp);
+      const uint2 m3 = epilogue_hidden<NP, ATM>(taddr, sm->bias_h1, aout);
       if (MODE == 1 && NP > 1 && A.masks4) __stcs(A.masks4 + tile_id * 128 + gt, make_uint4(m2.x, m2.y, m3.x, m3.y));
-      run_layer<16, 64, NP, NG>(G, sm->b5, tmem, phase, gt, grp);
+      run_layer<16, 64, NP, NG, ATM>(G, sm->b5, tmem, phase, gt, grp);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
@@ -336,14 +399,14 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   if (MODE == 1 && A.g_absmax && tid == 0) atomicMax(reinterpret_cast<int*>(A.g_absmax), sm->seed_max_bits);
-  if (tid < 32) tc::tmem_dealloc<64 * NG>(sm->tmem_slot);
+  if (tid < 32) tc::tmem_dealloc<kAllocCols>(sm->tmem_slot);
 }
 
 template <int MODE, int NP, int NG>
 static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
-  size_t smem = sizeof(TcSmem<NP, NG>) + 128;
+  size_t smem = sizeof(TcSmem<NP, NG, (NP > 1 && kSplitAtm)>) + 128;
   if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE, NP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -356,10 +419,10 @@ static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStr
   return cudaGetLastError();
 }
 cudaError_t launch_field_forward_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces) {
-  return pieces > 1 ? launch_tc_mode<0, 3, 2>(M, A, stream) : launch_tc_mode<0, 1, 1>(M, A, stream);
+  return pieces > 1 ? launch_tc_mode<0, 3, kSplitGroups>(M, A, stream) : launch_tc_mode<0, 1, 1>(M, A, stream);
 }
 cudaError_t launch_field_adjoint_seed_tc(const ModelDev& M, const FieldArgs& A, cudaStream_t stream, int pieces) {
-  return pieces > 1 ? launch_tc_mode<1, 3, 2>(M, A, stream) : launch_tc_mode<1, 1, 1>(M, A, stream);
+  return pieces > 1 ? launch_tc_mode<1, 3, kSplitGroups>(M, A, stream) : launch_tc_mode<1, 1, 1>(M, A, stream);
 }
 
 }  // namespace nemit

@@ -157,6 +157,23 @@ __device__ __forceinline__ void mma_commit(uint64_t* bar) {
                : "memory");
 }
 
+// A operand from TENSOR MEMORY (the .ts form): row m of A = TMEM lane m, 32-bit column j of the operand = its K elements
+// (2j, 2j + 1) as a packed 16-bit pair, so one k-step of 16 reads 8 columns; `a_tmem` = column base, lane 0.
+__device__ __forceinline__ void mma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 32-bit, 4 consecutive columns: thread t of the warp writes lane (warp % 4) * 32 + t
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};" ::"r"(taddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // One GEMM of the MLP chain: D[128 x N] = A[128 x K] * B[N x K]^T, fp16 operands in the layout above
 // (A: LBO = 128*16, B: LBO = N*16), issued by the calling thread; completion arrives on `bar`.
 template <int N, int K>
@@ -263,6 +280,26 @@ __device__ __forceinline__ void mma_chain_np(uint32_t d_tmem, const Operand& a, 
       ai.addr += i * a_piece;
       bj.addr += j * b_piece;
       mma_chain(d_tmem, ai, bj, id, ksteps, acc);
+      acc = true;
+    }
+  }
+}
+
+// the same with the A operand in tensor memory: piece i of A at column a_tmem + i * a_piece_cols, 8 columns per k-step
+template <int NP>
+__device__ __forceinline__ void mma_chain_np_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t a_piece_cols, const Operand& b,
+                                                uint32_t b_piece, uint32_t idesc, int ksteps, bool accumulate) {
+  const uint32_t id = idesc | OpFmt<NP>::bits;
+  bool acc = accumulate;
+#pragma unroll
+  for (int order = NP - 1; order >= 0; --order) {
+#pragma unroll
+    for (int i = 0; i <= order; ++i) {
+      const int j = order - i;
+      for (int k = 0; k < ksteps; ++k) {
+        mma_f16_ts(d_tmem, a_tmem + i * a_piece_cols + 8 * k, smem_desc(b.addr + j * b_piece + k * b.step, b.lbo, b.sbo), id,
+                   (acc || k > 0) ? 1u : 0u);
+      }
       acc = true;
     }
   }
