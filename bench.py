@@ -306,7 +306,7 @@ class Timer:
         return float(t.item()) / steps
 
 
-def kernel_roofline(prof, ceilings):
+def kernel_roofline(prof, ceilings, ncu_traffic=True):
     """Per-kernel rates from the library's own CUDA-event records of the timed region (events on the launching stream
     around every launch; rays per launch as recorded at launch time) and the roofline object of the dominant kernel."""
     hbm, src = measured_peaks()
@@ -319,7 +319,7 @@ def kernel_roofline(prof, ceilings):
         v["algorithmic_bytes_per_ray"] = ALG_BYTES[k]
         v["achieved_gbs"] = ALG_BYTES[k] * rays / sec / 1e9
         v["frac_of_hbm_peak"] = v["achieved_gbs"] / hbm
-        if k in NCU_TRAFFIC:
+        if ncu_traffic and k in NCU_TRAFFIC:
             r0, b0 = NCU_TRAFFIC[k]
             v["traffic"] = b0 * v["rays_per_launch"] / r0
             v["traffic_over_algorithmic"] = v["traffic"] / (ALG_BYTES[k] * v["rays_per_launch"])
@@ -518,7 +518,7 @@ def bench_rays(args, E, T, rank, world, local, dist, dev, kind):
                     "through": "nemit_backward_host" if kind == "fwd+bwd" else "nemit_forward_host",
                     "note": "pinned host rays (+grad_out) in, host radiance (+ray grads) out, one C-ABI call per step, "
                             "copies on the compute stream"},
-            "roofline": kernel_roofline(prof, ceilings)}
+            "roofline": kernel_roofline(prof, ceilings, ncu_traffic=args.precision == "fp16")}
     if ceilings:
         line["ceilings"] = {k: v for k, v in ceilings.items()}
         line["ceilings"]["unit"] = "lane-ops/s (l2_read: bytes/s), nemit_microbench in this run"
@@ -645,8 +645,10 @@ def main():
     ap.add_argument("--rays", type=int, default=1 << 20, help="rays per GPU per step (default line and --config 2)")
     ap.add_argument("--ref-rays", type=int, default=4096, help="rays (samples) per step of the CPU reference arm")
     ap.add_argument("--mode", default=None, choices=["fwd", "fwd+bwd"])
-    ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32"],
-                    help="MLP arithmetic of the main field: fp16 tensor-core (BASELINE configs[1]) or exact fp32")
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "fp32", "split"],
+                    help="MLP arithmetic of the main field: fp16 tensor-core (BASELINE configs[1]), exact fp32 FMA kernels, or "
+                         "split = fp32 arithmetic on the tensor cores through bf16 operand pieces (ncu traffic constants "
+                         "are those of the fp16 mode and are left out of the line in the other modes)")
     ap.add_argument("--sampler", default=None, choices=["exact", "fast"],
                     help="proposal sampler arithmetic: exact = the reference's fp32 CPU arithmetic (bit-equal indices), "
                          "fast = packed-half proposal networks (autocast behaviour); default: fast with --precision fp16")

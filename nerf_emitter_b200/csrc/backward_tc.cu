@@ -151,15 +151,25 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(tc::smem_u32(bar)) : "memory");
 }
 
-// make the half's operand writes visible to the tensor core, let its thread 0 issue one commit group, wait for it
+// make the half's operand writes visible to the tensor core, let the issuers put the step's MMAs in flight, wait for all.
+// The chains of one step (weight gradient, bias gradient, data gradient) write DIFFERENT accumulators, so they are issued
+// by lane 0 of kIssuers different warps at the same time - one thread issues ~10 instructions per MMA (descriptors into
+// uniform registers), which at up to 52 MMAs per step was a visible part of the chain; every issuer commits to the same
+// mbarrier (count kIssuers).  A given accumulator is always fed by the same thread, so its MMAs stay ordered.
+#ifndef NEMIT_BWD_ISSUERS
+#define NEMIT_BWD_ISSUERS 3
+#endif
+constexpr int kIssuers = NEMIT_BWD_ISSUERS;
+static_assert(kIssuers == 1 || kIssuers == 3, "one issuing thread, or one per chain");
 template <class HalfT, class F>
 __device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& phase, F&& issue) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
   half_sync(half);
-  if (t == 0) {
+  if ((t & 31) == 0 && t < 32 * kIssuers) {
     tc::tc_fence_after();
-    issue();
+    if (kIssuers == 1) { issue(0); issue(1); issue(2); }
+    else issue(t >> 5);
     tc::mma_commit(&H->mbar);
   }
   tc::mbar_wait(&H->mbar, phase);
@@ -331,7 +341,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     C->app[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
   }
   if (!is_scatter && t == 0) {
-    tc::mbar_init(&H->mbar, 1);
+    tc::mbar_init(&H->mbar, kIssuers);
     tc::mbar_init(&H->ld_bar, 1);
     tc::mbar_init(&H->full_bar, 128);
     tc::mbar_init(&H->empty_bar, kScatterThreads);
@@ -453,32 +463,32 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     ld_phase ^= 1u;
 
     // ---- head hidden layers, forward again (H2, H3 are not kept) ------------------------------------------
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->in, 128), kPcIn, tc::op_kmajor(C->b3, 64), kPcB3, tc::idesc_f16(128, 64), 2, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->in, 128), kPcIn, tc::op_kmajor(C->b3, 64), kPcB3, tc::idesc_f16(128, 64), 2, false);
     });
     epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h0, H->h2, t, make_uint2(mk.x, mk.y));
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_kmajor(C->b4, 64), kPcB4, tc::idesc_f16(128, 64), 4, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_kmajor(C->b4, 64), kPcB4, tc::idesc_f16(128, 64), 4, false);
     });
     epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h1, H->h3, t, make_uint2(mk.z, mk.w));
 
     // ---- head MLP backward ---------------------------------------------------------------------------
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b5, 16), kPcB5, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 1) tc::mma_chain_np<NP>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b5, 16), kPcB5, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h3, t, make_uint2(mk.z, mk.w));
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h3, 128), kPcH, tc::op_mnmajor(C->b4, 64), kPcB4, tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 1) tc::mma_chain_np<NP>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h3, 128), kPcH, tc::op_mnmajor(C->b4, 64), kPcB4, tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
     });
     epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h2, t, make_uint2(mk.x, mk.y));
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 1) tc::mma_chain_np<NP>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_mnmajor(C->b3, 64, 16), kPcB3, tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_mnmajor(C->b3, 64, 16), kPcB3, tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
     });
     if (t == 0 && has_next) {       // IN has no reader left: the next tile's copies start here
       tc::mbar_expect_tx(&H->ld_bar, kTileLoadBytes);
@@ -502,10 +512,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
     }
 
     // ---- base MLP backward ---------------------------------------------------------------------------
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b2, 16), kPcB2, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 1) tc::mma_chain_np<NP>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b2, 16), kPcB2, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden<NP>(taddr + kColD0, H->h1, t);
     // this tile's Jacobian rows: the loads fly under the last commit group
@@ -515,10 +525,10 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 #pragma unroll
       for (int c = 0; c < 12 * NP; ++c) jn[c] = __ldcs(jp + c * 128);
     }
-    mma_step(H, half, t, phase, [&] {
-      tc::mma_chain_np<NP>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h1, 128), kPcH, tc::op_mnmajor(C->b1, 64), kPcB1, tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
+    mma_step(H, half, t, phase, [&](int c) {
+      if (c == 1) tc::mma_chain_np<NP>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h1, 128), kPcH, tc::op_mnmajor(C->b1, 64), kPcB1, tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
     });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }
 

@@ -7,7 +7,7 @@ spec = EmitterModelSpec()
 E = NerfEmitter(make_params(spec, 0, 1e3), spec)
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 18
 mode = sys.argv[2] if len(sys.argv) > 2 else "fwd"
-E.set_precision("fp16")
+E.set_precision(sys.argv[5] if len(sys.argv) > 5 else "fp16")
 E.set_sampler(sys.argv[3] if len(sys.argv) > 3 else "fast")
 reps = int(sys.argv[4]) if len(sys.argv) > 4 else 5
 g = torch.Generator().manual_seed(1)
