@@ -253,28 +253,44 @@ __device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, 
   }
 }
 
+// The epilogues walk the 64 accumulator columns in groups of kEpiCols x 16; with fewer than 4 the loop stays rolled
+// (code size: the kernel's instruction footprint is far beyond the instruction cache, ncu: no_inst stalls)
+#ifndef NEMIT_EPI_COLS
+#define NEMIT_EPI_COLS 1
+#endif
+constexpr int kEpiCols = NEMIT_EPI_COLS;
+#if NEMIT_EPI_COLS == 4
+#define NEMIT_EPI_LOOP _Pragma("unroll")
+#else
+#define NEMIT_EPI_LOOP _Pragma("unroll 1")
+#endif
+
 // forward recompute of a head hidden layer: accumulator row + bias, ReLU -> operand row (k_field_forward_tc's
 // epilogue_hidden, same arithmetic in the same order)
 // With split operands (NP = 2) the ReLU decision is the seed pass's (24 significant bits there, 16 here): unit n is active
 // iff bit n of `mask` is set, whatever the sign of this pass's own pre-activation (they differ only within ~1e-5 of zero).
 template <int NP>
 __device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __restrict__ bias, uint8_t* buf, int row, uint2 mask) {
-  float v[4][16];
+  NEMIT_EPI_LOOP
+  for (int c0 = 0; c0 < 4; c0 += kEpiCols) {
+    float v[kEpiCols][16];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
-  tc::tmem_ld_wait();
+    for (int cc = 0; cc < kEpiCols; ++cc) tc::tmem_ld16(taddr + (c0 + cc) * 16, v[cc]);
+    tc::tmem_ld_wait();
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    const uint32_t mw = (c >> 1) ? mask.y : mask.x;
+    for (int cc = 0; cc < kEpiCols; ++cc) {
+      const int c = c0 + cc;
+      const uint32_t mw = ((c >> 1) ? mask.y : mask.x) >> ((c & 1) * 16);
 #pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      float x[8];
+      for (int hh = 0; hh < 2; ++hh) {
+        float x[8];
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        x[q] = fmaxf(v[c][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
-        if (NP > 1 && !((mw >> ((c & 1) * 16 + hh * 8 + q)) & 1u)) x[q] = 0.f;
+        for (int q = 0; q < 8; ++q) {
+          x[q] = fmaxf(v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
+          if (NP > 1 && !((mw >> (hh * 8 + q)) & 1u)) x[q] = 0.f;
+        }
+        tc::store_chunk<NP, 128>(buf, kPcH, row, c * 2 + hh, x);
       }
-      tc::store_chunk<NP, 128>(buf, kPcH, row, c * 2 + hh, x);
     }
   }
 }
@@ -283,31 +299,39 @@ __device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __re
 // (USE_MASK: the activity comes from the seed pass's mask bits instead, see epi_fwd_hidden)
 template <int NP, bool USE_MASK = false>
 __device__ __forceinline__ void epi_bwd_hidden(uint32_t taddr, uint8_t* buf, int row, uint2 mask = make_uint2(0u, 0u)) {
-  float v[4][16];
+  NEMIT_EPI_LOOP
+  for (int c0 = 0; c0 < 4; c0 += kEpiCols) {
+    float v[kEpiCols][16];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
-  tc::tmem_ld_wait();
+    for (int cc = 0; cc < kEpiCols; ++cc) tc::tmem_ld16(taddr + (c0 + cc) * 16, v[cc]);
+    tc::tmem_ld_wait();
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+    for (int cc = 0; cc < kEpiCols; ++cc) {
+      const int c = c0 + cc;
+      const uint32_t mc = ((c >> 1) ? mask.y : mask.x) >> ((c & 1) * 16);
 #pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      const uint4 act = *reinterpret_cast<const uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh));
-      const uint32_t aw[4] = {act.x, act.y, act.z, act.w};
-      float x[8];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int j = hh * 8 + q * 2;
-        if (USE_MASK) {
-          const uint32_t mw = ((c >> 1) ? mask.y : mask.x) >> ((c & 1) * 16 + j);
-          x[2 * q] = (mw & 1u) ? v[c][j] : 0.f;
-          x[2 * q + 1] = (mw & 2u) ? v[c][j + 1] : 0.f;
-        } else {
-          // post-ReLU activations are >= 0: a non-zero fp16 / bf16-hi pattern (sign bit aside) means the unit was active
-          x[2 * q] = (aw[q] & 0x00007fffu) ? v[c][j] : 0.f;
-          x[2 * q + 1] = (aw[q] & 0x7fff0000u) ? v[c][j + 1] : 0.f;
+      for (int hh = 0; hh < 2; ++hh) {
+        uint32_t aw[4] = {0u, 0u, 0u, 0u};
+        if (!USE_MASK) {
+          const uint4 act = *reinterpret_cast<const uint4*>(buf + tc::chunk_off<128>(row, c * 2 + hh));
+          aw[0] = act.x; aw[1] = act.y; aw[2] = act.z; aw[3] = act.w;
         }
+        float x[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int j = hh * 8 + q * 2;
+          if (USE_MASK) {
+            const uint32_t mw = mc >> j;
+            x[2 * q] = (mw & 1u) ? v[cc][j] : 0.f;
+            x[2 * q + 1] = (mw & 2u) ? v[cc][j + 1] : 0.f;
+          } else {
+            // post-ReLU activations are >= 0: a non-zero fp16 / bf16-hi pattern (sign bit aside) means the unit was active
+            x[2 * q] = (aw[q] & 0x00007fffu) ? v[cc][j] : 0.f;
+            x[2 * q + 1] = (aw[q] & 0x7fff0000u) ? v[cc][j + 1] : 0.f;
+          }
+        }
+        tc::store_chunk<NP, 128, true>(buf, kPcH, row, c * 2 + hh, x);
       }
-      tc::store_chunk<NP, 128, true>(buf, kPcH, row, c * 2 + hh, x);
     }
   }
 }

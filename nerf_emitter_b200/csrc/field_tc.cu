@@ -94,25 +94,45 @@ struct AOut {
   }
 };
 
-// accumulator row (64 columns) -> +bias, ReLU -> operand row of the next layer (8 K-chunks); returns the ReLU mask
+// accumulator row (64 columns) -> +bias, ReLU -> operand row of the next layer (8 K-chunks); returns the ReLU mask.
+// The columns are walked in groups of kFwdEpiCols x 16; with fewer than 4 the loop stays rolled (code size: the tile loop
+// is several times the 32 KB instruction cache, and the groups / CTAs of an SM sit in different phases of it)
+#ifndef NEMIT_FWD_EPI_COLS
+#define NEMIT_FWD_EPI_COLS 2
+#endif
+constexpr int kFwdEpiCols = NEMIT_FWD_EPI_COLS;
+#if NEMIT_FWD_EPI_COLS == 4
+#define NEMIT_FWD_EPI_LOOP _Pragma("unroll")
+#else
+#define NEMIT_FWD_EPI_LOOP _Pragma("unroll 1")
+#endif
 template <int NP, bool ATM>
 __device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __restrict__ bias, const AOut<NP, ATM>& out) {
-  float v[4][16];
-#pragma unroll
-  for (int c = 0; c < 4; ++c) tc::tmem_ld16(taddr + c * 16, v[c]);
-  tc::tmem_ld_wait();
   uint32_t m[2] = {0u, 0u};
+  NEMIT_FWD_EPI_LOOP
+  for (int c0 = 0; c0 < 4; c0 += kFwdEpiCols) {
+    float v[kFwdEpiCols][16];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+    for (int cc = 0; cc < kFwdEpiCols; ++cc) tc::tmem_ld16(taddr + (c0 + cc) * 16, v[cc]);
+    tc::tmem_ld_wait();
 #pragma unroll
-    for (int hh = 0; hh < 2; ++hh) {
-      float x[8];
+    for (int cc = 0; cc < kFwdEpiCols; ++cc) {
+      const int c = c0 + cc;
+      uint32_t mc = 0u;
 #pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        x[q] = fmaxf(v[c][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
-        if (NP > 1) m[c >> 1] |= (x[q] > 0.f ? 1u : 0u) << ((c & 1) * 16 + hh * 8 + q);
+      for (int hh = 0; hh < 2; ++hh) {
+        float x[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          x[q] = fmaxf(v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
+          if (NP > 1) mc |= (x[q] > 0.f ? 1u : 0u) << (hh * 8 + q);
+        }
+        out.put(c * 2 + hh, x);
       }
-      out.put(c * 2 + hh, x);
+      if (NP > 1) {
+        if (c >> 1) m[1] |= mc << ((c & 1) * 16);
+        else m[0] |= mc << ((c & 1) * 16);
+      }
     }
   }
   return make_uint2(m[0], m[1]);

@@ -205,6 +205,9 @@ __device__ __forceinline__ Operand op_mnmajor(const void* buf, int rows, int fir
 // D (+)= A * B^T over `ksteps` k-steps of 16; the first k-step overwrites D unless `accumulate`
 __device__ __forceinline__ void mma_chain(uint32_t d_tmem, const Operand& a, const Operand& b, uint32_t idesc, int ksteps,
                                           bool accumulate) {
+#ifdef NEMIT_MMA_ROLL           // keep the k-step loop rolled (code size; a kernel sets it before including this header)
+#pragma unroll 1
+#endif
   for (int j = 0; j < ksteps; ++j)
     mma_f16_ss(d_tmem, smem_desc(a.addr + j * a.step, a.lbo, a.sbo), smem_desc(b.addr + j * b.step, b.lbo, b.sbo), idesc,
                (accumulate || j > 0) ? 1u : 0u);

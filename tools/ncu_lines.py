@@ -45,6 +45,7 @@ for r in rows:
     elif cur is not None and cur["hdr"] and r and r[0].startswith("0x"):
         cur["rows"].append(r)
 def norm(x):
+    x = re.sub(r"\((int|bool|unsigned int)\)", "", x)          # ncu prints template arguments as <(int)2>, c++filt as <2>
     return re.sub(r"\(.*", "", x).replace("nemit::", "").replace("void ", "").replace(" ", "")
 demangled = {norm(subprocess.run(["c++filt", f], capture_output=True, text=True).stdout.strip()): f for f in line_of}
 for b in blocks:
