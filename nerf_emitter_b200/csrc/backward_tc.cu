@@ -160,6 +160,15 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 #define NEMIT_BWD_ISSUERS 3
 #endif
 constexpr int kIssuers = NEMIT_BWD_ISSUERS;
+// which chains keep their k-step loops rolled (weight-gradient / bias-gradient chains: issued beside the data-gradient
+// chain by their own threads, so their issue rate is off the critical path; the instruction footprint is not)
+#ifndef NEMIT_BWD_ROLL_W
+#define NEMIT_BWD_ROLL_W 0
+#endif
+#ifndef NEMIT_BWD_ROLL_B
+#define NEMIT_BWD_ROLL_B 0
+#endif
+constexpr bool kRollW = NEMIT_BWD_ROLL_W != 0, kRollB = NEMIT_BWD_ROLL_B != 0;
 static_assert(kIssuers == 1 || kIssuers == 3, "one issuing thread, or one per chain");
 template <class HalfT, class F>
 __device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& phase, F&& issue) {
@@ -498,19 +507,19 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
     // ---- head MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&](int c) {
-      if (c == 1) tc::mma_chain_np<NP>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
-      if (c == 2) tc::mma_chain_np<NP>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 1) tc::mma_chain_np<NP, kRollW>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP, kRollB>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b5, 16), kPcB5, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h3, t, make_uint2(mk.z, mk.w));
     mma_step(H, half, t, phase, [&](int c) {
-      if (c == 1) tc::mma_chain_np<NP>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
-      if (c == 2) tc::mma_chain_np<NP>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 1) tc::mma_chain_np<NP, kRollW>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP, kRollB>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h3, 128), kPcH, tc::op_mnmajor(C->b4, 64), kPcB4, tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
     });
     epi_bwd_hidden<NP, (NP > 1)>(taddr + kColD0, H->h2, t, make_uint2(mk.x, mk.y));
     mma_step(H, half, t, phase, [&](int c) {
-      if (c == 1) tc::mma_chain_np<NP>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      if (c == 1) tc::mma_chain_np<NP, kRollW>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
       // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
       if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_mnmajor(C->b3, 64, 16), kPcB3, tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
     });
@@ -537,8 +546,8 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
 
     // ---- base MLP backward ---------------------------------------------------------------------------
     mma_step(H, half, t, phase, [&](int c) {
-      if (c == 1) tc::mma_chain_np<NP>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
-      if (c == 2) tc::mma_chain_np<NP>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      if (c == 1) tc::mma_chain_np<NP, kRollW>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP, kRollB>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
       if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b2, 16), kPcB2, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
     });
     epi_bwd_hidden<NP>(taddr + kColD0, H->h1, t);
@@ -550,8 +559,8 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
       for (int c = 0; c < 12 * NP; ++c) jn[c] = __ldcs(jp + c * 128);
     }
     mma_step(H, half, t, phase, [&](int c) {
-      if (c == 1) tc::mma_chain_np<NP>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
-      if (c == 2) tc::mma_chain_np<NP>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+      if (c == 1) tc::mma_chain_np<NP, kRollW>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+      if (c == 2) tc::mma_chain_np<NP, kRollB>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
       if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h1, 128), kPcH, tc::op_mnmajor(C->b1, 64), kPcB1, tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
     });
     if (t == 0 && has_next) { load_h1(next_tile); load_e(next_tile); }

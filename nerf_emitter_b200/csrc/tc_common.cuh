@@ -202,15 +202,21 @@ __device__ __forceinline__ Operand op_kmajor(const void* buf, int rows) {
 __device__ __forceinline__ Operand op_mnmajor(const void* buf, int rows, int first_col = 0) {
   return Operand{smem_u32(buf) + (uint32_t)(first_col >> 3) * (uint32_t)rows * 16u, 128u, (uint32_t)rows * 16u, 256u};
 }
-// D (+)= A * B^T over `ksteps` k-steps of 16; the first k-step overwrites D unless `accumulate`
+// D (+)= A * B^T over `ksteps` k-steps of 16; the first k-step overwrites D unless `accumulate`.  ROLL keeps the k-step
+// loop rolled (instruction footprint) - for chains whose issue rate is not on the critical path
+template <bool ROLL = false>
 __device__ __forceinline__ void mma_chain(uint32_t d_tmem, const Operand& a, const Operand& b, uint32_t idesc, int ksteps,
                                           bool accumulate) {
-#ifdef NEMIT_MMA_ROLL           // keep the k-step loop rolled (code size; a kernel sets it before including this header)
+  if (ROLL) {
 #pragma unroll 1
-#endif
-  for (int j = 0; j < ksteps; ++j)
-    mma_f16_ss(d_tmem, smem_desc(a.addr + j * a.step, a.lbo, a.sbo), smem_desc(b.addr + j * b.step, b.lbo, b.sbo), idesc,
-               (accumulate || j > 0) ? 1u : 0u);
+    for (int j = 0; j < ksteps; ++j)
+      mma_f16_ss(d_tmem, smem_desc(a.addr + j * a.step, a.lbo, a.sbo), smem_desc(b.addr + j * b.step, b.lbo, b.sbo), idesc,
+                 (accumulate || j > 0) ? 1u : 0u);
+  } else {
+    for (int j = 0; j < ksteps; ++j)
+      mma_f16_ss(d_tmem, smem_desc(a.addr + j * a.step, a.lbo, a.sbo), smem_desc(b.addr + j * b.step, b.lbo, b.sbo), idesc,
+                 (accumulate || j > 0) ? 1u : 0u);
+  }
 }
 
 // byte offset of the 16-byte chunk (row r, K-chunk kc) of an operand with R rows
@@ -268,7 +274,7 @@ __device__ __forceinline__ void store_chunk(uint8_t* buf, uint32_t piece_bytes, 
 }
 // D (+)= A * B^T with NP-piece operands: piece p of an operand sits p * (a_piece | b_piece) bytes after piece 0; a piece
 // stride of 0 says the operand has one piece only (exactly representable values: the ones operand)
-template <int NP>
+template <int NP, bool ROLL = false>
 __device__ __forceinline__ void mma_chain_np(uint32_t d_tmem, const Operand& a, uint32_t a_piece, const Operand& b,
                                              uint32_t b_piece, uint32_t idesc, int ksteps, bool accumulate) {
   const uint32_t id = idesc | OpFmt<NP>::bits;
@@ -282,7 +288,7 @@ __device__ __forceinline__ void mma_chain_np(uint32_t d_tmem, const Operand& a, 
       Operand ai = a, bj = b;
       ai.addr += i * a_piece;
       bj.addr += j * b_piece;
-      mma_chain(d_tmem, ai, bj, id, ksteps, acc);
+      mma_chain<ROLL>(d_tmem, ai, bj, id, ksteps, acc);
       acc = true;
     }
   }
