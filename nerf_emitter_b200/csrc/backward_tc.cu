@@ -170,20 +170,24 @@ constexpr int kIssuers = NEMIT_BWD_ISSUERS;
 #endif
 constexpr bool kRollW = NEMIT_BWD_ROLL_W != 0, kRollB = NEMIT_BWD_ROLL_B != 0;
 static_assert(kIssuers == 1 || kIssuers == 3, "one issuing thread, or one per chain");
-template <class HalfT, class F>
-__device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& phase, F&& issue) {
+template <class F>
+__device__ __forceinline__ void mma_step_on(uint64_t* mbar, int group, int t, uint32_t& phase, F&& issue) {
   tc::fence_proxy_async();
   tc::tc_fence_before();
-  half_sync(half);
+  half_sync(group);
   if ((t & 31) == 0 && t < 32 * kIssuers) {
     tc::tc_fence_after();
     if (kIssuers == 1) { issue(0); issue(1); issue(2); }
     else issue(t >> 5);
-    tc::mma_commit(&H->mbar);
+    tc::mma_commit(mbar);
   }
-  tc::mbar_wait(&H->mbar, phase);
+  tc::mbar_wait(mbar, phase);
   phase ^= 1u;
   tc::tc_fence_after();
+}
+template <class HalfT, class F>
+__device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& phase, F&& issue) {
+  mma_step_on(&H->mbar, half, t, phase, issue);
 }
 
 // Table scatter of one parked tile, all 16 levels: run by the four scatter warps, thread = sample `smp` of the tile
@@ -732,6 +736,389 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
   if (tid < 32) tc::tmem_dealloc<512>(C->tmem_slot);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Split-operand backward, pipelined (NP = 2).  The doubled operand buffers leave room for ONE tile in flight per SM, so
+// instead of two halves that each run the whole chain, the chain of a tile is cut in two and run by two warpgroups as a
+// pipeline:
+//   HEAD warpgroup (threads   0..127): H2 / H3 recompute, head layers 2, 1, 0 backward  ->  d [raw | geo15] rows (gs2)
+//   BASE warpgroup (threads 128..255): base layers 1, 0 backward, d/d(position), per-ray sums, parks d enc for the scatter
+//   scatter warpgroups (threads 256..511) as before.
+// While BASE finishes tile i, HEAD is already on tile i + 1.  The two stages own disjoint operand buffers (HEAD: IN, H2, H3,
+// gs; BASE: H1, E, gs2), disjoint accumulators (BASE's work accumulator sits in columns 256..319) and their own barriers;
+// the hand-over is the 8 KB gs2 buffer behind an mbarrier pair.
+constexpr uint32_t kColD0B = 256;    // BASE stage work accumulator (128 x 64)
+struct BwdPipeSmem {
+  BwdTcCommon<2> c;
+  BwdTcHalf<2> h;                           // gs = HEAD's gradient operand, mbar / ld_bar = HEAD's
+  alignas(128) uint8_t gs2[2 * kPcGs];      // d [raw | geo15] rows handed from HEAD to BASE
+  alignas(8) uint64_t mbar_b;               // BASE's MMA commit groups
+  alignas(8) uint64_t ld_bar_b;             // BASE's bulk copies (H1, E)
+  alignas(8) uint64_t gs_full;              // 128 HEAD threads arrive: gs2 holds the rows of a tile
+  alignas(8) uint64_t gs_empty;             // 128 BASE threads arrive: gs2 has been consumed
+};
+constexpr int kPipeThreads = 256 + kScatterThreads;
+constexpr int kPipeLaunchRegs = 128, kPipeComputeRegs = 192, kPipeScatterRegs = 64;
+static_assert(kScatterThreads == 256, "the pipelined kernel is laid out for two scatter warpgroups");
+static_assert(256 * kPipeComputeRegs + kScatterThreads * kPipeScatterRegs <= kPipeThreads * kPipeLaunchRegs, "register pool of the CTA");
+
+__global__ void __launch_bounds__(kPipeThreads, 1)
+k_field_backward_tc_pipe(const __grid_constant__ ModelDev M, const __grid_constant__ FieldBwdArgs A) {
+  constexpr int NP = 2;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  BwdPipeSmem* sm = reinterpret_cast<BwdPipeSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
+  const int tid = threadIdx.x, lane = tid & 31, wq = (tid >> 5) & 3;
+  const int role = tid >> 7;               // 0 = HEAD, 1 = BASE, 2 / 3 = scatter groups
+  const int t = tid & 127;
+  BwdTcCommon<NP>* C = &sm->c;
+  BwdTcHalf<NP>* H = &sm->h;
+
+  // ---- one-time setup ------------------------------------------------------------------------------
+  tc::stage_weight_np<64, 32, NP>(C->b1, A.P.base_w0, 64, 32, 32, tid, kPipeThreads);
+  tc::stage_weight_np<16, 64, NP>(C->b2, A.P.base_w1, 16, 64, 64, tid, kPipeThreads);
+  tc::stage_weight_np<64, 32, NP>(C->b3, A.P.head_w0, 64, kHeadIn, kHeadK, tid, kPipeThreads);
+  tc::stage_weight_np<64, 64, NP>(C->b4, A.P.head_w1, 64, 64, 64, tid, kPipeThreads);
+  tc::stage_weight_np<16, 64, NP>(C->b5, A.P.head_w2, 3, 64, 64, tid, kPipeThreads);
+  for (int i = tid; i < 8 * 128; i += kPipeThreads) reinterpret_cast<uint16_t*>(C->ones)[i] = 0x3F80u;      // bf16 1.0
+  for (int i = tid; i < kApp; i += kPipeThreads) C->app[i] = appearance_component(A.P.appearance, M.num_images, A.app_row, i);
+  if (tid == 0) {
+    tc::mbar_init(&H->mbar, kIssuers);
+    tc::mbar_init(&sm->mbar_b, kIssuers);
+    tc::mbar_init(&H->ld_bar, 1);
+    tc::mbar_init(&sm->ld_bar_b, 1);
+    tc::mbar_init(&H->full_bar, 128);
+    tc::mbar_init(&H->empty_bar, kScatterThreads);
+    tc::mbar_init(&sm->gs_full, 128);
+    tc::mbar_init(&sm->gs_empty, 128);
+    tc::fence_mbar_init();
+  }
+  if (tid < 32) tc::tmem_alloc<512>(&C->tmem_slot);
+  for (int i = tid; i < 64; i += kPipeThreads) C->bias_h1[i] = A.P.head_b1[i];
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  for (int n = tid; n < 64; n += kPipeThreads) {         // as k_field_forward_tc: b0 + W0[:, 31:63] . appearance, same order
+    float b = A.P.head_b0[n];
+    for (int k = 0; k < kApp; ++k) b = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + k], C->app[k], b);
+    C->bias_h0[n] = b;
+  }
+  __syncthreads();
+  const uint32_t tm = C->tmem_slot;                                // lane 0
+  const uint32_t taddr = tm + ((uint32_t)(wq * 32) << 16);         // this warp's 32 TMEM lanes
+  uint32_t phase = 0;
+  const tc::Operand op_ones{tc::smem_u32(C->ones), 128u, 2048u, 256u};
+  const tc::Operand op_ones_a{tc::smem_u32(C->ones), 128u, 0u, 256u};
+  const int64_t n_samples = A.n * kS2;
+  const int64_t n_tiles = (n_samples + kTileM - 1) / kTileM;
+  const int64_t tile_stride = gridDim.x;
+  const float gscale = A.loss_scale;
+  const uint64_t pol = tc::l2_evict_first_policy();
+  bool first = true;
+
+  if (role >= 2) {
+    // ---- scatter warps ---------------------------------------------------------------------------------------------
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kPipeScatterRegs));
+    uint32_t nred = 0, j = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += tile_stride, ++j) {
+      tc::mbar_wait(&H->full_bar, j & 1u);
+      if (A.G.main_table) scatter_tile(H, t, lane, role - 2, M, A.G.main_table, gscale, nred);
+      mbar_arrive(&H->empty_bar);
+    }
+    if (A.red_ops) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) nred += __shfl_xor_sync(0xffffffffu, nred, o);
+      if (lane == 0) atomicAdd(A.red_ops, (unsigned long long)nred);
+    }
+  } else if (role == 0) {
+    // ---- HEAD warpgroup ----------------------------------------------------------------------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kPipeComputeRegs));
+    uint32_t ld_phase = 0, gs_phase = 1;      // gs_empty parity to wait for: a fresh barrier passes parity 1 (gs2 free)
+    auto load_in = [&](int64_t tl) { tc::bulk_g2s(H->in, A.act_tiles + tl * (NP * kActTileBytes) + NP * 16384, NP * 8192, &H->ld_bar, pol); };
+    if (t == 0 && (int64_t)blockIdx.x < n_tiles) {
+      tc::mbar_expect_tx(&H->ld_bar, NP * 8192);
+      load_in(blockIdx.x);
+    }
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += tile_stride) {
+      const int64_t next_tile = tile + tile_stride;
+      const int64_t s = tile * kTileM + t;
+      const bool valid = s < n_samples;
+      float4 seed = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (valid) seed = __ldcs(A.seeds4 + s);
+      const uint4 mk = __ldcs(A.masks4 + tile * kTileM + t);      // ReLU masks of H2 | H3 as the seed pass decided them
+      {
+        const float g8[8] = {seed.x, seed.y, seed.z, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const float z8[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        tc::store_chunk<NP, 128, true>(H->gs, kPcGs, t, 0, g8);
+        tc::store_chunk<NP, 128>(H->gs, kPcGs, t, 1, z8);
+      }
+      tc::mbar_wait(&H->ld_bar, ld_phase);
+      ld_phase ^= 1u;
+      // head hidden layers, forward again (H2, H3 are not kept)
+      mma_step_on(&H->mbar, 0, t, phase, [&](int c) {
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->in, 128), kPcIn, tc::op_kmajor(C->b3, 64), kPcB3, tc::idesc_f16(128, 64), 2, false);
+      });
+      epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h0, H->h2, t, make_uint2(mk.x, mk.y));
+      mma_step_on(&H->mbar, 0, t, phase, [&](int c) {
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_kmajor(C->b4, 64), kPcB4, tc::idesc_f16(128, 64), 4, false);
+      });
+      epi_fwd_hidden<NP>(taddr + kColD0, C->bias_h1, H->h3, t, make_uint2(mk.z, mk.w));
+      // head MLP backward
+      mma_step_on(&H->mbar, 0, t, phase, [&](int c) {
+        if (c == 1) tc::mma_chain_np<NP>(tm + kColH2T, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+        if (c == 2) tc::mma_chain_np<NP>(tm + kColBH2, op_ones_a, 0, tc::op_mnmajor(H->gs, 128), kPcGs, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->gs, 128), kPcGs, tc::op_mnmajor(C->b5, 16), kPcB5, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+      });
+      epi_bwd_hidden<NP, true>(taddr + kColD0, H->h3, t, make_uint2(mk.z, mk.w));
+      mma_step_on(&H->mbar, 0, t, phase, [&](int c) {
+        if (c == 1) tc::mma_chain_np<NP>(tm + kColH1, tc::op_mnmajor(H->h3, 128), kPcH, tc::op_mnmajor(H->h2, 128), kPcH, tc::idesc_f16_mj(64, 64, 1, 1), 8, !first);
+        if (c == 2) tc::mma_chain_np<NP>(tm + kColBH1, tc::op_mnmajor(H->h3, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h3, 128), kPcH, tc::op_mnmajor(C->b4, 64), kPcB4, tc::idesc_f16_mj(128, 64, 0, 1), 4, false);
+      });
+      epi_bwd_hidden<NP, true>(taddr + kColD0, H->h2, t, make_uint2(mk.x, mk.y));
+      mma_step_on(&H->mbar, 0, t, phase, [&](int c) {
+        if (c == 1) tc::mma_chain_np<NP>(tm + kColH0, tc::op_mnmajor(H->h2, 128), kPcH, tc::op_mnmajor(H->in, 128), kPcIn, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+        // geo-feature columns 16..31 only; SH carries no reverse-mode gradient (encodings.py:708)
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0, tc::op_kmajor(H->h2, 128), kPcH, tc::op_mnmajor(C->b3, 64, 16), kPcB3, tc::idesc_f16_mj(128, 16, 0, 1), 4, false);
+      });
+      if (t == 0 && next_tile < n_tiles) {        // IN has no reader left: the next tile's copy starts here
+        tc::mbar_expect_tx(&H->ld_bar, NP * 8192);
+        load_in(next_tile);
+      }
+      {
+        float v[16];
+        tc::tmem_ld16(taddr + kColD0, v);
+        tc::tmem_ld_wait();
+        float g16[16];
+        g16[0] = seed.w;
+#pragma unroll
+        for (int k = 0; k < 15; ++k) g16[k + 1] = v[k];
+        tc::mbar_wait(&sm->gs_empty, gs_phase);      // BASE has consumed the previous tile's rows
+        gs_phase ^= 1u;
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          float x8[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) x8[q] = g16[hh * 8 + q];
+          tc::store_chunk<NP, 128, true>(sm->gs2, kPcGs, t, hh, x8);
+        }
+        tc::fence_proxy_async();                     // the reader is BASE's tensor-core work
+        mbar_arrive(&sm->gs_full);
+      }
+      first = false;
+    }
+    // flush HEAD's weight-gradient accumulators
+    if (!first && A.G.main_table) {
+      tc::tc_fence_before();
+      half_sync(0);
+      tc::tc_fence_after();
+      const bool has = lane < 16;             // M = 64 accumulators: row r lives in lane (r / 16) * 32 + r % 16
+      const int r = wq * 16 + (lane & 15);
+      const float fs = A.loss_scale;
+      float v[16];
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        tc::tmem_ld16(taddr + kColH1 + c * 16, v);
+        tc::tmem_ld_wait();
+        if (has)
+          for (int i = 0; i < 16; ++i) atomicAdd(A.G.head_w1 + r * kHidden + c * 16 + i, fs * v[i]);
+      }
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        tc::tmem_ld16(taddr + kColH0 + c * 16, v);
+        tc::tmem_ld_wait();
+        if (has) {
+          for (int i = 0; i < 16; ++i) {
+            const int k = c * 16 + i;
+            if (k < kHeadK) {
+              atomicAdd(A.G.head_w0 + r * kHeadIn + k, fs * v[i]);
+            } else {
+              const float db = fs * v[i];     // ones column = d head_b0_eff; the appearance columns are rank-1 with it
+              H->dvec[r] = db;
+              atomicAdd(A.G.head_b0 + r, db);
+              for (int j = 0; j < kApp; ++j) atomicAdd(A.G.head_w0 + r * kHeadIn + kHeadK + j, db * C->app[j]);
+            }
+          }
+        }
+      }
+      {
+        float u[8];
+        tc::tmem_ld8(taddr + kColH2T, u);
+        tc::tmem_ld_wait();
+        if (has)
+          for (int n = 0; n < 3; ++n) atomicAdd(A.G.head_w2 + n * kHidden + r, fs * u[n]);
+        tc::tmem_ld8(taddr + kColBH1, u);
+        tc::tmem_ld_wait();
+        if (has) atomicAdd(A.G.head_b1 + r, fs * u[0]);
+        tc::tmem_ld8(taddr + kColBH2, u);
+        tc::tmem_ld_wait();
+        if (t == 0)
+          for (int n = 0; n < 3; ++n) atomicAdd(A.G.head_b2 + n, fs * u[n]);
+      }
+      half_sync(0);
+      if (t < kApp) {                         // appearance embedding (NS/fields/nerfacto_field.py:272-285)
+        float g = 0.f;
+        for (int n = 0; n < kHidden; ++n) g = fmaf(A.P.head_w0[n * kHeadIn + kHeadK + t], H->dvec[n], g);
+        appearance_component_grad(A.G.appearance, M.num_images, A.app_row, t, g);
+      }
+    }
+  } else {
+    // ---- BASE warpgroup ----------------------------------------------------------------------------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kPipeComputeRegs));
+    uint32_t ld_phase = 0, gs_phase = 0, slot_phase = 1;
+    auto load_e = [&](int64_t tl) { tc::bulk_g2s(H->e, A.enc_tiles + tl * (NP * kEncTileBytes), NP * 8192, &sm->ld_bar_b, pol); };
+    auto load_h1 = [&](int64_t tl) { tc::bulk_g2s(H->h1, A.act_tiles + tl * (NP * kActTileBytes), NP * 16384, &sm->ld_bar_b, pol); };
+    if (t == 0 && (int64_t)blockIdx.x < n_tiles) {
+      tc::mbar_expect_tx(&sm->ld_bar_b, NP * (8192 + 16384));
+      load_h1(blockIdx.x); load_e(blockIdx.x);
+    }
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += tile_stride) {
+      const int64_t next_tile = tile + tile_stride;
+      const int64_t s = tile * kTileM + t;
+      const bool valid = s < n_samples;
+      const int64_t rr = valid ? s / kS2 : 0;
+      const int si = valid ? (int)(s % kS2) : 0;
+      float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, t0 = 0.f, t1 = 0.f;
+      if (valid) {
+        load_ray(A.o, A.v, A.near_per_ray, A.near_scalar, A.n_total, A.ray_offset + rr, ray_scale(M, A), o, d);
+        t0 = A.t_edges2[rr * (kS2 + 1) + si];
+        t1 = A.t_edges2[rr * (kS2 + 1) + si + 1];
+      }
+      const float tsum = add_rn(t0, t1);
+      float x[3], p[3], dirq[3];
+      const bool rotated = rot_sample(A.rot, o, d, tsum, x, dirq);
+      const bool sel = contract_normalise(x, M, p);
+      tc::mbar_wait(&sm->ld_bar_b, ld_phase);
+      ld_phase ^= 1u;
+      tc::mbar_wait(&sm->gs_full, gs_phase);       // HEAD's d [raw | geo15] rows of this tile
+      gs_phase ^= 1u;
+      mma_step_on(&sm->mbar_b, 1, t, phase, [&](int c) {
+        if (c == 1) tc::mma_chain_np<NP>(tm + kColB1T, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(sm->gs2, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+        if (c == 2) tc::mma_chain_np<NP>(tm + kColBB1, op_ones_a, 0, tc::op_mnmajor(sm->gs2, 128), kPcGs, tc::idesc_f16_mj(64, 16, 1, 1), 8, !first);
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0B, tc::op_kmajor(sm->gs2, 128), kPcGs, tc::op_mnmajor(C->b2, 16), kPcB2, tc::idesc_f16_mj(128, 64, 0, 1), 1, false);
+      });
+      mbar_arrive(&sm->gs_empty);                  // every reader of gs2 (the commit group above) has completed
+      epi_bwd_hidden<NP>(taddr + kColD0B, H->h1, t);
+      // this tile's Jacobian rows (fp32): the loads fly under the last commit group
+      uint4 jn[12 * NP];
+      {
+        const uint4* jp = reinterpret_cast<const uint4*>(A.jac_tiles + tile * (NP * kJacTileBytes)) + t;
+#pragma unroll
+        for (int c = 0; c < 12 * NP; ++c) jn[c] = __ldcs(jp + c * 128);
+      }
+      mma_step_on(&sm->mbar_b, 1, t, phase, [&](int c) {
+        if (c == 1) tc::mma_chain_np<NP>(tm + kColB0, tc::op_mnmajor(H->h1, 128), kPcH, tc::op_mnmajor(H->e, 128), kPcE, tc::idesc_f16_mj(64, 32, 1, 1), 8, !first);
+        if (c == 2) tc::mma_chain_np<NP>(tm + kColBB0, tc::op_mnmajor(H->h1, 128), kPcH, op_ones, 0, tc::idesc_f16_mj(64, 8, 1, 1), 8, !first);
+        if (c == 0) tc::mma_chain_np<NP>(tm + kColD0B, tc::op_kmajor(H->h1, 128), kPcH, tc::op_mnmajor(C->b1, 64), kPcB1, tc::idesc_f16_mj(128, 32, 0, 1), 4, false);
+      });
+      if (t == 0 && next_tile < n_tiles) {
+        tc::mbar_expect_tx(&sm->ld_bar_b, NP * (8192 + 16384));
+        load_h1(next_tile); load_e(next_tile);
+      }
+      // hash grid backward: d/d(position) here, the table scatter of this tile is handed to the scatter warps
+      {
+        float gp[3] = {0.f, 0.f, 0.f};
+        tc::mbar_wait(&H->empty_bar, slot_phase);
+        slot_phase ^= 1u;
+        H->pbuf[t] = p[0]; H->pbuf[128 + t] = p[1]; H->pbuf[256 + t] = p[2];
+#pragma unroll
+        for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
+          float g[8];
+          tc::tmem_ld8(taddr + kColD0B + 2 * l0, g);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 8; ++k) H->denc[(2 * l0 + k) * 128 + t] = valid ? g[k] : 0.f;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float gx = g[2 * j], gy = g[2 * j + 1];
+            // rows of level l0 + j: dx.xy dy.xy dz.xy = six consecutive floats of the row's 24 per four levels
+            const uint4 qa = jn[(l0 >> 2) * 6 + (6 * j) / 4], qb = jn[(l0 >> 2) * 6 + (6 * j) / 4 + 1];
+            const uint32_t w8[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+            const int b0 = (6 * j) % 4;
+            const float dxx = __uint_as_float(w8[b0]), dxy = __uint_as_float(w8[b0 + 1]), dyx = __uint_as_float(w8[b0 + 2]),
+                        dyy = __uint_as_float(w8[b0 + 3]), dzx = __uint_as_float(w8[b0 + 4]), dzy = __uint_as_float(w8[b0 + 5]);
+            const float scs = M.main_grid.scal[l0 + j];
+            gp[0] = fmaf(scs, gx * dxx + gy * dxy, gp[0]);
+            gp[1] = fmaf(scs, gx * dyx + gy * dyy, gp[1]);
+            gp[2] = fmaf(scs, gx * dzx + gy * dzy, gp[2]);
+          }
+        }
+        float v6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (valid && sel) {
+          float gx[3];
+          contract_vjp(x, sel, gp, gx);
+          if (rotated) {
+            float gr[3];
+            rot_transpose(A.rot, gx, gr);
+            gx[0] = gr[0]; gx[1] = gr[1]; gx[2] = gr[2];
+          }
+          const float tmid = tsum * 0.5f;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) { v6[k] = gx[k]; v6[3 + k] = gx[k] * tmid; }
+        }
+        {
+          const long long r_any = s / kS2;
+          const long long r_first = __shfl_sync(0xffffffffu, r_any, 0), r_last = __shfl_sync(0xffffffffu, r_any, 31);
+          const bool lo = r_any == r_first;
+          float a6[6], b6[6];
+#pragma unroll
+          for (int k = 0; k < 6; ++k) { a6[k] = lo ? v6[k] : 0.f; b6[k] = lo ? 0.f : v6[k]; }
+#pragma unroll
+          for (int of = 16; of > 0; of >>= 1) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+              a6[k] += __shfl_xor_sync(0xffffffffu, a6[k], of);
+              b6[k] += __shfl_xor_sync(0xffffffffu, b6[k], of);
+            }
+          }
+          if (lane == 0 && r_first < A.n) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) atomicAdd(A.ray_grad + r_first * 6 + k, a6[k]);
+          }
+          if (lane == 31 && r_last != r_first && r_last < A.n) {
+#pragma unroll
+            for (int k = 0; k < 6; ++k) atomicAdd(A.ray_grad + r_last * 6 + k, b6[k]);
+          }
+        }
+        mbar_arrive(&H->full_bar);
+      }
+      first = false;
+    }
+    // flush BASE's weight-gradient accumulators
+    if (!first && A.G.main_table) {
+      tc::tc_fence_before();
+      half_sync(1);
+      tc::tc_fence_after();
+      const bool has = lane < 16;
+      const int r = wq * 16 + (lane & 15);
+      const float fs = A.loss_scale;
+      float v[16];
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        tc::tmem_ld16(taddr + kColB0 + c * 16, v);
+        tc::tmem_ld_wait();
+        if (has)
+          for (int i = 0; i < 16; ++i) atomicAdd(A.G.base_w0 + r * kMainEnc + c * 16 + i, fs * v[i]);
+      }
+      tc::tmem_ld16(taddr + kColB1T, v);
+      tc::tmem_ld_wait();
+      if (has)
+        for (int n = 0; n < 16; ++n) atomicAdd(A.G.base_w1 + n * kHidden + r, fs * v[n]);
+      {
+        float u[8];
+        tc::tmem_ld8(taddr + kColBB0, u);
+        tc::tmem_ld_wait();
+        if (has) atomicAdd(A.G.base_b0 + r, fs * u[0]);
+      }
+      tc::tmem_ld16(taddr + kColBB1, v);
+      tc::tmem_ld_wait();
+      if (t == 0)
+        for (int n = 0; n < 16; ++n) atomicAdd(A.G.base_b1 + n, fs * v[n]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (tid < 32) tc::tmem_dealloc<512>(C->tmem_slot);
+}
+
 template <int NP>
 static cudaError_t launch_bwd_np(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
@@ -746,9 +1133,24 @@ static cudaError_t launch_bwd_np(const ModelDev& M, const FieldBwdArgs& A, cudaS
   k_field_backward_tc<NP><<<(unsigned)ctas, BwdCfg<NP>::kThreads, smem, stream>>>(M, A);
   return cudaGetLastError();
 }
+#ifndef NEMIT_SPLIT_BWD_PIPE
+#define NEMIT_SPLIT_BWD_PIPE 1         // split operands: 1 = the pipelined kernel (HEAD / BASE warpgroups), 0 = one compute half
+#endif
+static cudaError_t launch_bwd_pipe(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream) {
+  static DeviceOnce attr_once;
+  const size_t smem = sizeof(BwdPipeSmem) + 128;
+  if (attr_once.need()) {
+    cudaError_t e = cudaFuncSetAttribute(k_field_backward_tc_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  const int64_t tiles = (A.n * kS2 + kTileM - 1) / kTileM;
+  k_field_backward_tc_pipe<<<(unsigned)(tiles < 148 ? tiles : 148), kPipeThreads, smem, stream>>>(M, A);
+  return cudaGetLastError();
+}
 cudaError_t launch_field_backward_tc(const ModelDev& M, const FieldBwdArgs& A, cudaStream_t stream, int pieces) {
   if (A.n <= 0) return cudaSuccess;
-  return pieces == 2 ? launch_bwd_np<2>(M, A, stream) : launch_bwd_np<1>(M, A, stream);
+  if (pieces == 2) return NEMIT_SPLIT_BWD_PIPE ? launch_bwd_pipe(M, A, stream) : launch_bwd_np<2>(M, A, stream);
+  return launch_bwd_np<1>(M, A, stream);
 }
 
 }  // namespace nemit

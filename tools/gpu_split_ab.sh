@@ -1,9 +1,11 @@
 cd $GRAFT_REPO_ROOT
-for v in "" rb rwb; do
-  lib=""; [ -n "$v" ] && lib=nerf_emitter_b200/libnerfemitter_$v.so
-  echo "== lib: ${v:-default}"
-  for prec in split fp16; do
-    samp=exact; [ $prec = fp16 ] && samp=fast
-    NEMIT_LIB=$lib timeout 300 python tools/kernel_times.py 262144 fwd+bwd $samp 3 $prec 2>&1 | tail -1 | sed "s/.*k_field_backward_tc': '\([^']*\)'.*step \(.*\)/  $prec bwd \1  step \2/"
-  done
-done
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -q -x 2>&1 | grep -v "^$" | tail -3
+timeout 600 python bench.py --precision split --no-cpu-baseline > gpurun_out/bench_split.json 2> gpurun_out/bench_split.err; echo "bench split rc=$?"
+python - <<'PY'
+import json
+for f in ('gpurun_out/bench_split.json',):
+    d=json.load(open(f))
+    print(f, d['value'], d['ms_per_step'], d['e2e']['value'], d.get('forward',{}).get('value'), d.get('train_primal_backward',{}).get('value'))
+    for k,v in d['roofline']['kernels'].items(): print('  ',k, round(v['ms_per_launch'],3), v['launches'], round(v['share'],3))
+PY
