@@ -733,6 +733,8 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
   cudaStream_t st = (cudaStream_t)stream;
   cudaError_t e;
   const int64_t sub = bwd_sub_chunk(h, rays->n);
+  ChunkEdges E0;
+  int64_t edges_of = -1;
   for (int64_t off = 0; off < rays->n; off += sub) {
     int64_t n = rays->n - off < sub ? rays->n - off : sub;
     float* g_sigma = reinterpret_cast<float*>(ws + L.g_sigma);
@@ -740,8 +742,17 @@ extern "C" int nemit_backward(NemitHandle* h, const NemitRays* rays, const float
     float* weights2 = reinterpret_cast<float*>(ws + L.weights2);
     float* ray_grad = reinterpret_cast<float*>(ws + L.ray_grad);
     const bool prop_pass = proposal_requires_grad && h->M.interlevel_mult != 0.f;
-    ChunkEdges E;
-    if ((rc = chunk_edges(h, h->M, rays, off, n, ws, L, prop_pass, st, &E))) return rc;
+    // the sample edges are produced once per chunk of kBwdChunkRays rays, also when the mode walks it in smaller sub-chunks
+    const int64_t outer = off / kBwdChunkRays * kBwdChunkRays;
+    if (outer != edges_of) {
+      const int64_t n_outer = rays->n - outer < kBwdChunkRays ? rays->n - outer : kBwdChunkRays;
+      if ((rc = chunk_edges(h, h->M, rays, outer, n_outer, ws, L, prop_pass, st, &E0))) return rc;
+      edges_of = outer;
+    }
+    ChunkEdges E = E0;
+    E.t_edges2 += (off - outer) * (kS2 + 1);
+    E.s_edges2 += (off - outer) * (kS2 + 1);
+    if (E.s_edges1) E.s_edges1 += (off - outer) * (kS1 + 1);
     const float* t_edges = E.t_edges2;
     const float* s_edges = E.s_edges2;
     // pass 1: forward of the 48-sample stage + composite adjoint
