@@ -226,11 +226,23 @@ __device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, 
     bool issue = act;
 #if NEMIT_BWD_AGGREGATE
     {
-      // cell key: the integer cell coordinates (resolutions <= 2048: 11 bits each); inactive lanes get a key of their own
+      // cell key: the integer cell coordinates, 11 + 11 + 10 bits in one word; on the levels whose resolution exceeds 1024
+      // the eleventh bit of z travels in a second word.  Lanes that must stay alone get a key of their own: inactive ones,
+      // and samples that sit EXACTLY on a grid plane (a zero fractional coordinate): their ceil corner coincides with the
+      // floor corner, so their 8 indices are not those of the cell's other samples although the integer coordinates agree -
+      // as the last lane of a run they would send the run's ceil-corner sums to the floor-corner entries (seen on 1 of
+      // 49 152 sample-levels of a 64-ray batch, tools/diag_table_grad.py).
       const int y0 = (int)floorf(mul_rn(p[1], sc)), z0 = (int)floorf(mul_rn(p[2], sc));
-      const uint32_t key = act ? ((uint32_t)x0 | ((uint32_t)y0 << 11) | ((uint32_t)z0 << 22)) : (0xffffffe0u | (uint32_t)lane);
-      const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
-      const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0 || key != prev);
+      const bool alone = !act || cell.fx == 0.f || cell.fy == 0.f || cell.fz == 0.f;
+      const uint32_t key = alone ? (0xffffffe0u | (uint32_t)lane) : ((uint32_t)x0 | ((uint32_t)y0 << 11) | ((uint32_t)z0 << 22));
+      const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);        // (every lane takes part: no short-circuit around it)
+      bool head = lane == 0 || key != prev;
+      if (sc > 1023.f) {                 // warp-uniform
+        const uint32_t zhi = alone ? 0xffu : ((uint32_t)z0 >> 10);
+        const uint32_t prev_zhi = __shfl_up_sync(0xffffffffu, zhi, 1);
+        head = head || zhi != prev_zhi;
+      }
+      const uint32_t heads = __ballot_sync(0xffffffffu, head);
       if (heads != 0xffffffffu) {        // at least one run of two or more lanes in this warp
         const int start = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));      // first lane of my run
         const bool tail = lane == 31 || ((heads >> (lane + 1)) & 1u);
