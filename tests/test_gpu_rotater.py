@@ -23,15 +23,16 @@ def _emitter(P, spec, rot, ids):
     return E
 
 
+@pytest.mark.parametrize("precision", ["fp32", "split"])
 @pytest.mark.parametrize("kind", ["sphere", "box"])
-def test_rotated_frustums_match_reference_golden(kind, spec, params_factory):
+def test_rotated_frustums_match_reference_golden(kind, precision, spec, params_factory):
     from oracle.nerfacto_oracle import OracleEmitter
     from oracle.rotater_fixture import rotaters
     G = load_golden("rotater_stress")
     P = params_factory(int(G["param_seed"]), float(G["table_scale"]))
     ids = [int(x) for x in G["rotation_ids"]]
     rot = rotaters()[kind]
-    E = _emitter(P, spec, rot, ids)
+    E = _emitter(P, spec, rot, ids).set_precision(precision)
     O = OracleEmitter(P, spec, always_use_camera_indices=True, rotation_ids=ids, rotater=rot)
     o, v, do, dv, gout = (T(G[k]) for k in ("o", "v", "do", "dv", "grad_out"))
     jit = [T(G["jitter"][:, i:i + 1]).contiguous() for i in range(3)]

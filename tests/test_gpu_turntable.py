@@ -13,7 +13,7 @@ DEV = "cuda:0"
 APP = "field.embedding_appearance.embedding.weight"
 
 
-@pytest.mark.parametrize("precision", ["fp32", "fp16"])
+@pytest.mark.parametrize("precision", ["fp32", "fp16", "split"])
 def test_turntable_forward_and_embedding_gradient_match_reference_golden(precision, spec, params_factory):
     from nerf_emitter_b200 import NerfEmitter
     from oracle.nerfacto_oracle import OracleEmitter
@@ -24,7 +24,7 @@ def test_turntable_forward_and_embedding_gradient_match_reference_golden(precisi
     E.set_appearance_mode(always_use_camera_indices=True, rotation_ids=ids).eval()
     O = OracleEmitter(P, spec, always_use_camera_indices=True, rotation_ids=ids)
     o, v, gout = T(G["o"]), T(G["v"]), T(G["grad_out"])
-    tol = TOL if precision == "fp32" else 2e-2
+    tol = TOL if precision != "fp16" else 2e-2      # split = fp32 arithmetic on the tensor cores: the fp32 gates
     for cam in (4, 9):
         rgb = E.render(o.to(DEV), v.to(DEV), camera_idx=cam).cpu()
         assert rel_err(rgb, G["rgb_cam%d" % cam]) < tol, (cam, rel_err(rgb, G["rgb_cam%d" % cam]))
@@ -36,7 +36,7 @@ def test_turntable_forward_and_embedding_gradient_match_reference_golden(precisi
         go, gv = E.backward(o.to(DEV), v.to(DEV), gout.to(DEV), camera_idx=cam, chunk_rays=o.shape[1],
                             proposal_requires_grad=False)
         torch.cuda.synchronize()
-        if precision == "fp32":
+        if precision != "fp16":
             assert rel_err(go.cpu(), ref_go) < tol and rel_err(gv.cpu(), ref_gv) < tol
         else:       # fp16 mode: ReLU masks of single samples move (tests/test_gpu_backward.py)
             per_ray = torch.maximum((go.cpu() - ref_go).abs().max(0).values / ref_go.abs().max(),
