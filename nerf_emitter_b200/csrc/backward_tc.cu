@@ -95,10 +95,10 @@ struct BwdCfg {
   static constexpr int kHalves = NP == 1 ? 2 : 1;
   static constexpr int kComputeThreads = 128 * kHalves;
   static constexpr int kThreads = kComputeThreads + kScatterThreads;
-  static constexpr int kLaunchRegs = kThreads == 512 ? 128 : (kThreads == 384 ? 168 : 255);
-  static constexpr int kComputeRegs = NP == 1 ? (kScatterGroups == 1 ? 200 : 192) : 232;
+  static constexpr int kLaunchRegs = kThreads == 640 ? 96 : (kThreads == 512 ? 128 : (kThreads == 384 ? 168 : 255));
+  static constexpr int kComputeRegs = NP == 1 ? (kScatterGroups == 1 ? 200 : (kScatterGroups == 2 ? 192 : 144)) : 232;
   static constexpr int kScatterRegs = NP == 1 ? (kScatterGroups == 1 ? 104 : 64) : 64;
-  static_assert(kThreads == 512 || kThreads == 384, "launch register count is derived for 384 / 512 threads");
+  static_assert(kThreads == 640 || kThreads == 512 || kThreads == 384, "launch register count is derived for 384 / 512 / 640 threads");
   static_assert(kComputeThreads * kComputeRegs + kScatterThreads * kScatterRegs <= kThreads * kLaunchRegs, "register pool of the CTA");
 };
 #ifndef NEMIT_BWD_AGGREGATE
@@ -198,7 +198,7 @@ __device__ __forceinline__ void mma_step(HalfT* H, int half, int t, uint32_t& ph
 //   * corners (2q, 2q+1) differ in x only (ceil, floor); for an even floor coordinate the two hashed indices differ in
 //     bit 0 only, i.e. they are the two halves of one aligned 16-byte pair: one red.v4.f32.
 template <class HalfT>
-__device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, int group, const ModelDev& M,
+__device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, int group, int groups, const ModelDev& M,
                                              float2* table, float gscale, uint32_t& nred) {
   const float p[3] = {H->pbuf[smp], H->pbuf[128 + smp], H->pbuf[256 + smp]};
 #ifndef NEMIT_BWD_SCATTER_FROM
@@ -208,7 +208,7 @@ __device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, 
 #define NEMIT_BWD_SCATTER_TO 16        // experiments only: one past the last level that is scattered
 #endif
 #pragma unroll 1
-  for (int l = NEMIT_BWD_SCATTER_FROM + group; l < NEMIT_BWD_SCATTER_TO; l += kScatterGroups) {
+  for (int l = NEMIT_BWD_SCATTER_FROM + group; l < NEMIT_BWD_SCATTER_TO; l += groups) {
     const float gx = H->denc[(2 * l) * 128 + smp], gy = H->denc[(2 * l + 1) * 128 + smp];
     const bool act = gx != 0.f || gy != 0.f;
     if (!__any_sync(0xffffffffu, act)) continue;
@@ -449,7 +449,7 @@ k_field_backward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ 
         BwdTcHalf<NP>* Hh = &sm->h[hh];
         tc::mbar_wait(&Hh->full_bar, j & 1u);
         if (A.G.main_table)            // null: ray-gradient-only pass (nemit_point_lights), nothing to scatter
-          scatter_tile(Hh, t, lane, (tid - kComputeThreads) >> 7, M, A.G.main_table, gscale, nred);
+          scatter_tile(Hh, t, lane, (tid - kComputeThreads) >> 7, kScatterGroups, M, A.G.main_table, gscale, nred);
         mbar_arrive(&Hh->empty_bar);   // release: the reads of denc / pbuf above are done
       }
     }
@@ -768,10 +768,10 @@ struct BwdPipeSmem {
   alignas(8) uint64_t gs_full;              // 128 HEAD threads arrive: gs2 holds the rows of a tile
   alignas(8) uint64_t gs_empty;             // 128 BASE threads arrive: gs2 has been consumed
 };
-constexpr int kPipeThreads = 256 + kScatterThreads;
+constexpr int kPipeScatterThreads = 256;         // two scatter warpgroups
+constexpr int kPipeThreads = 256 + kPipeScatterThreads;
 constexpr int kPipeLaunchRegs = 128, kPipeComputeRegs = 192, kPipeScatterRegs = 64;
-static_assert(kScatterThreads == 256, "the pipelined kernel is laid out for two scatter warpgroups");
-static_assert(256 * kPipeComputeRegs + kScatterThreads * kPipeScatterRegs <= kPipeThreads * kPipeLaunchRegs, "register pool of the CTA");
+static_assert(256 * kPipeComputeRegs + kPipeScatterThreads * kPipeScatterRegs <= kPipeThreads * kPipeLaunchRegs, "register pool of the CTA");
 
 __global__ void __launch_bounds__(kPipeThreads, 1)
 k_field_backward_tc_pipe(const __grid_constant__ ModelDev M, const __grid_constant__ FieldBwdArgs A) {
@@ -798,7 +798,7 @@ k_field_backward_tc_pipe(const __grid_constant__ ModelDev M, const __grid_consta
     tc::mbar_init(&H->ld_bar, 1);
     tc::mbar_init(&sm->ld_bar_b, 1);
     tc::mbar_init(&H->full_bar, 128);
-    tc::mbar_init(&H->empty_bar, kScatterThreads);
+    tc::mbar_init(&H->empty_bar, kPipeScatterThreads);
     tc::mbar_init(&sm->gs_full, 128);
     tc::mbar_init(&sm->gs_empty, 128);
     tc::fence_mbar_init();
@@ -832,7 +832,7 @@ k_field_backward_tc_pipe(const __grid_constant__ ModelDev M, const __grid_consta
     uint32_t nred = 0, j = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += tile_stride, ++j) {
       tc::mbar_wait(&H->full_bar, j & 1u);
-      if (A.G.main_table) scatter_tile(H, t, lane, role - 2, M, A.G.main_table, gscale, nred);
+      if (A.G.main_table) scatter_tile(H, t, lane, role - 2, 2, M, A.G.main_table, gscale, nred);
       mbar_arrive(&H->empty_bar);
     }
     if (A.red_ops) {
