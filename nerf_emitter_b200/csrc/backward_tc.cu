@@ -214,11 +214,12 @@ __device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, 
     if (!__any_sync(0xffffffffu, act)) continue;
     LevelCell cell;
     const float sc = M.main_grid.scal[l];
-    level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)l * M.main_grid.table_size, cell);
+    uint32_t c0[3];
+    level_cell<true>(p, sc, M.main_grid.table_mask, (uint32_t)l * M.main_grid.table_size, cell, c0);
     float cw[8];
     corner_weights(cell, cw);
     const float gxs = gx * gscale, gys = gy * gscale;
-    const int x0 = (int)floorf(mul_rn(p[0], sc));
+    const uint32_t x0 = c0[0];
     const bool pair = ((x0 & 1) == 0) && (cell.idx[0] != cell.idx[1]);
     float w[16];                         // (corner c, feature f) -> w[2c + f]
 #pragma unroll
@@ -232,13 +233,13 @@ __device__ __forceinline__ void scatter_tile(const HalfT* H, int smp, int lane, 
       // floor corner, so their 8 indices are not those of the cell's other samples although the integer coordinates agree -
       // as the last lane of a run they would send the run's ceil-corner sums to the floor-corner entries (seen on 1 of
       // 49 152 sample-levels of a 64-ray batch, tools/diag_table_grad.py).
-      const int y0 = (int)floorf(mul_rn(p[1], sc)), z0 = (int)floorf(mul_rn(p[2], sc));
+      const uint32_t y0 = c0[1], z0 = c0[2];
       const bool alone = !act || cell.fx == 0.f || cell.fy == 0.f || cell.fz == 0.f;
-      const uint32_t key = alone ? (0xffffffe0u | (uint32_t)lane) : ((uint32_t)x0 | ((uint32_t)y0 << 11) | ((uint32_t)z0 << 22));
+      const uint32_t key = alone ? (0xffffffe0u | (uint32_t)lane) : (x0 | (y0 << 11) | (z0 << 22));
       const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);        // (every lane takes part: no short-circuit around it)
       bool head = lane == 0 || key != prev;
       if (sc > 1023.f) {                 // warp-uniform
-        const uint32_t zhi = alone ? 0xffu : ((uint32_t)z0 >> 10);
+        const uint32_t zhi = alone ? 0xffu : (z0 >> 10);
         const uint32_t prev_zhi = __shfl_up_sync(0xffffffffu, zhi, 1);
         head = head || zhi != prev_zhi;
       }

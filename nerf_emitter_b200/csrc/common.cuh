@@ -196,9 +196,10 @@ __device__ __forceinline__ void floor_ceil_small(float x, float& fl, uint32_t& i
 // ALU_FLOOR: floor / ceil / float->int through floor_ceil_small instead of the conversion unit.  Measured: the field
 // kernels (XU 13 %, ALU 17 % busy) gain 3 % (3.37 -> 3.28 ms per 2^18 rays), the sampler (ALU 42 % busy) loses 6 %,
 // so only the field kernels ask for it.  Both variants give bit-identical cells.
+// (cell0, when given, receives the integer coordinates of the cell's floor corner)
 template <bool ALU_FLOOR = false>
 __device__ __forceinline__ void level_cell(const float p[3], float scale, uint32_t mask, uint32_t level_off,
-                                           LevelCell& c) {
+                                           LevelCell& c, uint32_t* cell0 = nullptr) {
   float xs = mul_rn(p[0], scale), ys = mul_rn(p[1], scale), zs = mul_rn(p[2], scale);
   float xf, yf, zf;
   uint32_t x0, y0, z0, x1, y1, z1;
@@ -213,6 +214,7 @@ __device__ __forceinline__ void level_cell(const float p[3], float scale, uint32
     floor_ceil_small(xs, xf, x0, x1); floor_ceil_small(ys, yf, y0, y1); floor_ceil_small(zs, zf, z0, z1);
   }
   c.fx = sub_rn(xs, xf); c.fy = sub_rn(ys, yf); c.fz = sub_rn(zs, zf);
+  if (cell0) { cell0[0] = x0; cell0[1] = y0; cell0[2] = z0; }
   uint32_t hx0 = x0, hx1 = x1;
   uint32_t hy0 = y0 * NEMIT_PRIME_Y, hy1 = y1 * NEMIT_PRIME_Y;
   uint32_t hz0 = z0 * NEMIT_PRIME_Z, hz1 = z1 * NEMIT_PRIME_Z;

@@ -17,7 +17,7 @@ def E(spec, params_factory):
     return NerfEmitter(params_factory(0, 1e3), spec, device=torch.device("cuda:0"))
 
 
-@pytest.mark.parametrize("precision,sampler", [("fp32", "exact"), ("fp16", "fast")])
+@pytest.mark.parametrize("precision,sampler", [("fp32", "exact"), ("fp16", "fast"), ("split", "exact")])
 @pytest.mark.parametrize("prg", [False, True])
 def test_backward_with_kept_edges_equals_resampling(E, precision, sampler, prg):
     """base_model.py:299,327-328: the reference's adjoint re-derives the primal's samples from restored generator state;

@@ -21,7 +21,7 @@ def _call_noalloc(E, L, o, v, rgb, near, camera_idx):
     return E.lib.nemit_forward_noalloc(E._h, C.byref(R), C.c_void_p(rgb.data_ptr()), E._stream())
 
 
-@pytest.mark.parametrize("precision,sampler", [("fp32", "exact"), ("fp16", "fast")])
+@pytest.mark.parametrize("precision,sampler", [("fp32", "exact"), ("fp16", "fast"), ("split", "exact")])
 def test_forward_noalloc_matches_forward_twice(spec, params_factory, precision, sampler):
     from nerf_emitter_b200 import NerfEmitter
     from nerf_emitter_b200 import lib as L
