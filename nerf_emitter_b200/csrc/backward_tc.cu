@@ -312,10 +312,10 @@ __device__ __forceinline__ void epi_fwd_hidden(uint32_t taddr, const float* __re
         float x[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          x[q] = fmaxf(v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
-          if (NP > 1 && !((mw >> (hh * 8 + q)) & 1u)) x[q] = 0.f;
+          x[q] = v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q];           // ReLU: in the conversion (NP = 1), by the mask (NP = 2)
+          if (NP > 1) x[q] = ((mw >> (hh * 8 + q)) & 1u) ? fmaxf(x[q], 0.f) : 0.f;
         }
-        tc::store_chunk<NP, 128>(buf, kPcH, row, c * 2 + hh, x);
+        tc::store_chunk<NP, 128, false, (NP == 1)>(buf, kPcH, row, c * 2 + hh, x);
       }
     }
   }

@@ -78,13 +78,14 @@ struct AOut {
   int row;
   uint8_t* keep;         // ATM: tile of the kept operand in the workspace, or null
   uint32_t keep_bytes;   // ATM: bytes of one kept piece
+  template <bool RELU = false>
   __device__ __forceinline__ void put(int kc, const float (&x)[8]) const {
     if (!ATM) {
-      tc::store_chunk<NP, 128>(smem, kAPiece, row, kc, x);
+      tc::store_chunk<NP, 128, false, RELU>(smem, kAPiece, row, kc, x);
     } else {
       uint32_t w[4][3];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) tc::pack_pair<NP>(x[2 * q], x[2 * q + 1], w[q]);
+      for (int q = 0; q < 4; ++q) tc::pack_pair<NP, false, RELU>(x[2 * q], x[2 * q + 1], w[q]);
 #pragma unroll
       for (int p = 0; p < NP; ++p) {
         tc::tmem_st4(taddr + p * kAPieceCols + kc * 4, w[0][p], w[1][p], w[2][p], w[3][p]);
@@ -124,10 +125,10 @@ __device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __
         float x[8];
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          x[q] = fmaxf(v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q], 0.f);
+          x[q] = v[cc][hh * 8 + q] + bias[c * 16 + hh * 8 + q];          // the ReLU sits in the conversion (F2FP.RELU)
           if (NP > 1) mc |= (x[q] > 0.f ? 1u : 0u) << (hh * 8 + q);
         }
-        out.put(c * 2 + hh, x);
+        out.template put<true>(c * 2 + hh, x);
       }
       if (NP > 1) {
         if (c >> 1) m[1] |= mc << ((c & 1) * 16);

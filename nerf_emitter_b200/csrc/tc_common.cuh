@@ -227,9 +227,18 @@ __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
   __half2 h = __floats2half2_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
-// saturating variant for gradient operands: +-inf would poison a whole accumulator column
+// max(x, 0) and the conversion in one instruction (F2FP.RELU.F16.F32.PACK_AB)
+__device__ __forceinline__ uint32_t pack_h2_relu(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+// saturating variant for gradient operands: +-inf would poison a whole accumulator column.  One instruction
+// (F2FP.SATFINITE.F16.F32.PACK_AB): out-of-range values go to +-65504, in-range values round to nearest as in pack_h2
 __device__ __forceinline__ uint32_t pack_h2_sat(float a, float b) {
-  return pack_h2(fminf(fmaxf(a, -65504.f), 65504.f), fminf(fmaxf(b, -65504.f), 65504.f));
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));      // first source operand = upper half
+  return r;
 }
 
 // ---- split precision (NP = 2, 3) ---------------------------------------------------------------------
@@ -249,11 +258,13 @@ __device__ __forceinline__ uint32_t bf16x2_rn(float a, float b) {
 }
 // one pair of operand elements -> w[0] (the fp16 pair, or the leading bf16 pair), w[1], w[2] (the lower bf16 pieces);
 // SAT clamps to the finite range first (gradient operands: +-inf would poison a whole accumulator column)
-template <int NP, bool SAT = false>
+// RELU: max(x, 0) folded into the conversion (F2FP.RELU), for the hidden-layer epilogues
+template <int NP, bool SAT = false, bool RELU = false>
 __device__ __forceinline__ void pack_pair(float a, float b, uint32_t (&w)[3]) {
   if (NP == 1) {
-    w[0] = SAT ? pack_h2_sat(a, b) : pack_h2(a, b);
+    w[0] = SAT ? pack_h2_sat(a, b) : (RELU ? pack_h2_relu(a, b) : pack_h2(a, b));
   } else {
+    if (RELU) { a = fmaxf(a, 0.f); b = fmaxf(b, 0.f); }
     if (SAT) { a = fminf(fmaxf(a, -3.0e38f), 3.0e38f); b = fminf(fmaxf(b, -3.0e38f), 3.0e38f); }
 #pragma unroll
     for (int p = 0; p < NP; ++p) {
@@ -263,11 +274,11 @@ __device__ __forceinline__ void pack_pair(float a, float b, uint32_t (&w)[3]) {
   }
 }
 // eight consecutive K elements of row `row` (= the 16-byte chunk kc) of an R-row operand; piece p at buf + p * piece_bytes
-template <int NP, int R, bool SAT = false>
+template <int NP, int R, bool SAT = false, bool RELU = false>
 __device__ __forceinline__ void store_chunk(uint8_t* buf, uint32_t piece_bytes, int row, int kc, const float (&x)[8]) {
   uint32_t w[4][3];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) pack_pair<NP, SAT>(x[2 * q], x[2 * q + 1], w[q]);
+  for (int q = 0; q < 4; ++q) pack_pair<NP, SAT, RELU>(x[2 * q], x[2 * q + 1], w[q]);
 #pragma unroll
   for (int p = 0; p < NP; ++p)
     *reinterpret_cast<uint4*>(buf + p * piece_bytes + chunk_off<R>(row, kc)) = make_uint4(w[0][p], w[1][p], w[2][p], w[3][p]);
