@@ -1,4 +1,5 @@
 cd $GRAFT_REPO_ROOT
-timeout 300 python tools/kernel_times.py 262144 fwd+bwd fast 3 fp16 2>&1 | tail -1
-timeout 300 python tools/kernel_times.py 262144 fwd+bwd exact 3 split 2>&1 | tail -1
-timeout 1500 python -m pytest tests -m gpu -q -x 2>&1 | tail -2
+for sc in 1.0 1000.0; do
+  echo "== table scale $sc"
+  timeout 300 python tools/diag_table_grad.py 30000 $sc 2>&1 | grep -v "^max" | grep "split\|level\|non-zero" | head -24
+done

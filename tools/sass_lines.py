@@ -21,7 +21,7 @@ for f in sorted(os.listdir(tmp)):
         if m and cur and kname in cur:
             if group:
                 cand = [g for g in group if own is None or g[0] == own]
-                outer = cand[-1] if cand else group[-1]
+                outer = group[0] if os.environ.get("INNER") else (cand[-1] if cand else group[-1])
                 group = []
             cnt.setdefault(cur, collections.Counter())[outer] += 1
         elif m:
