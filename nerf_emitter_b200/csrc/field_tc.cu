@@ -37,6 +37,24 @@ constexpr uint32_t kAPieceCols = 32;            // A in tensor memory: 64 K-elem
 #define NEMIT_SPLIT_ATM 1                       // split-operand mode: A operand in tensor memory (0: in shared memory, two groups)
 #endif
 constexpr bool kSplitAtm = NEMIT_SPLIT_ATM != 0;
+#ifndef NEMIT_FP16_FWD_ATM
+#define NEMIT_FP16_FWD_ATM 1                    // fp16 forward (MODE 0): A operand in tensor memory too, five CTAs per SM instead of four
+#endif
+constexpr bool kFp16FwdAtm = NEMIT_FP16_FWD_ATM != 0;
+#ifndef NEMIT_FP16_SEED_ATM
+#define NEMIT_FP16_SEED_ATM 1                   // the same for the fp16 seed pass (MODE 1; stays at four CTAs per SM: 128 registers)
+#endif
+constexpr bool kFp16SeedAtm = NEMIT_FP16_SEED_ATM != 0;
+template <int MODE, int NP>
+struct FwdCfg {
+  static constexpr bool kAtm = (NP > 1 && kSplitAtm) || (NP == 1 && (MODE == 0 ? kFp16FwdAtm : kFp16SeedAtm));
+  // fp16 operands: four CTAs of one group per SM (shared memory: weights + A operand = 47 KB each); with A in tensor
+  // memory 31 KB and 64 + 32 TMEM columns each: five
+#ifndef NEMIT_SEED_CTAS
+#define NEMIT_SEED_CTAS 4
+#endif
+  static constexpr int kCtasPerSm = NP == 1 ? (kAtm ? (MODE == 0 ? 5 : NEMIT_SEED_CTAS) : 4) : 1;
+};
 constexpr int kSplitGroups = kSplitAtm ? 3 : 2;
 template <int NP, int NG, bool ATM>
 struct TcSmem {
@@ -59,6 +77,7 @@ struct TcSmem {
   float bias_b0[64], bias_b1[16], bias_h0[64], bias_h1[64], bias_h2[4];
   float app_tmp[kApp];
   uint32_t tmem_slot;
+  uint32_t tmem_slot_a;                        // fp16 operands with A in tensor memory: the A operand's own allocation (32 columns)
   int seed_max_bits;                           // adjoint-seed mode: max seed magnitude of this CTA (float bits)
 };
 
@@ -141,8 +160,9 @@ __device__ __forceinline__ uint2 epilogue_hidden(uint32_t taddr, const float* __
 
 // make this thread's A-operand writes visible to the tensor core, then let one thread of the group issue the layer
 template <int N, int K, int NP, int NG, bool ATM>
-__device__ __forceinline__ void run_layer(typename TcSmem<NP, NG, ATM>::Group* G, const uint8_t* b, uint32_t tmem, uint32_t& phase,
-                                          int gt, int grp, uint8_t* keep = nullptr, uint32_t keep_bytes = 0, uint64_t policy = 0) {
+__device__ __forceinline__ void run_layer(typename TcSmem<NP, NG, ATM>::Group* G, const uint8_t* b, uint32_t tmem, uint32_t a_tmem,
+                                          uint32_t& phase, int gt, int grp, uint8_t* keep = nullptr, uint32_t keep_bytes = 0,
+                                          uint64_t policy = 0) {
   if (ATM) {
     // the rows were written with tcgen05.st: complete them, order them before the barrier; D = columns [0, 64), A pieces
     // from column 64 (the kept pieces went out from the registers, AOut::put)
@@ -151,7 +171,7 @@ __device__ __forceinline__ void run_layer(typename TcSmem<NP, NG, ATM>::Group* G
     group_sync<NG>(grp);
     if (gt == 0) {
       tc::tc_fence_after();
-      tc::mma_chain_np_ts<NP>(tmem, tmem + 64, kAPieceCols, tc::op_kmajor(b, N), N * K * 2, tc::idesc_f16(128, N), K / 16, false);
+      tc::mma_chain_np_ts<NP>(tmem, a_tmem, kAPieceCols, tc::op_kmajor(b, N), N * K * 2, tc::idesc_f16(128, N), K / 16, false);
       tc::mma_commit(&G->mbar);
     }
     tc::mbar_wait(&G->mbar, phase);
@@ -183,12 +203,13 @@ __device__ __forceinline__ void run_layer(typename TcSmem<NP, NG, ATM>::Group* G
 
 // MODE 0: forward.  MODE 1: first pass of the backward (same forward, then the per-ray composite adjoint).
 template <int MODE, int NP, int NG>
-__global__ void __launch_bounds__(128 * NG)
+__global__ void __launch_bounds__(128 * NG, FwdCfg<MODE, NP>::kCtasPerSm)
 k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ FieldArgs A) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  constexpr bool ATM = NP > 1 && kSplitAtm;    // A operand in tensor memory
+  constexpr bool ATM = FwdCfg<MODE, NP>::kAtm;  // A operand in tensor memory
+  constexpr bool kTwoAllocs = ATM && NP == 1;  // accumulator (64 columns) and A operand (32) as two power-of-two allocations
   constexpr int kGroupCols = ATM ? 64 + NP * (int)kAPieceCols : 64;
-  constexpr int kAllocCols = NG * kGroupCols <= 64 ? 64 : (NG * kGroupCols <= 128 ? 128 : (NG * kGroupCols <= 256 ? 256 : 512));
+  constexpr int kAllocCols = kTwoAllocs ? 64 : (NG * kGroupCols <= 64 ? 64 : (NG * kGroupCols <= 128 ? 128 : (NG * kGroupCols <= 256 ? 256 : 512)));
   static_assert(NG * kGroupCols <= 512, "tensor memory of one SM");
   using Smem = TcSmem<NP, NG, ATM>;
   Smem* sm = reinterpret_cast<Smem*>(smem_raw);
@@ -213,7 +234,15 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   if (tid == 0) sm->seed_max_bits = 0;
   if (gt == 0) tc::fence_mbar_init();
   float seed_max = 0.f;
-  if (tid < 32) tc::tmem_alloc<kAllocCols>(&sm->tmem_slot);
+  if (tid < 32) {
+    if (kTwoAllocs) {
+      tc::tmem_alloc_only<64>(&sm->tmem_slot);
+      tc::tmem_alloc_only<32>(&sm->tmem_slot_a);
+      tc::tmem_relinquish();
+    } else {
+      tc::tmem_alloc<kAllocCols>(&sm->tmem_slot);
+    }
+  }
   __syncthreads();
   for (int n = tid; n < 64; n += kThreads) {
     float b = A.P.head_b0[n];
@@ -223,7 +252,8 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
-  const uint32_t tmem = sm->tmem_slot + (uint32_t)grp * kGroupCols;   // this group's columns: accumulator, then A pieces
+  const uint32_t tmem = sm->tmem_slot + (kTwoAllocs ? 0u : (uint32_t)grp * kGroupCols);   // this group's columns: accumulator, then A pieces
+  const uint32_t a_tmem = kTwoAllocs ? sm->tmem_slot_a : tmem + 64;
   const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16);     // this warp's 32 TMEM lanes
   uint32_t phase = 0;
   const uint64_t policy = MODE == 1 ? tc::l2_evict_first_policy() : 0;
@@ -256,7 +286,7 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       rot_sample(A.rot, &G->ray_o[rr * 3], &G->ray_d[rr * 3], tsum, x, dirq);      // Rotater.apply_frustums when set for this stage
       const bool sel = contract_normalise(x, M, p) && rr < rays_here;
       const int64_t tile_id = g * (kGroupSamples / kTileM) + tile;
-      AOut<NP, ATM> aout{G->a, taddr + 64, gt, nullptr, 0};
+      AOut<NP, ATM> aout{G->a, a_tmem + ((uint32_t)(wq * 32) << 16), gt, nullptr, 0};
       // ---- hash encoding: 4 levels = 8 values = one 16-byte K-chunk of this thread's A row ------------
 #pragma unroll 1
       for (int l0 = 0; l0 < kMainLevels; l0 += 4) {
@@ -311,11 +341,11 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
       uint8_t* act = nullptr;
       if (MODE == 1 && A.act_tiles) act = A.act_tiles + tile_id * (SP * kActTileBytes);
       // ---- base MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32, NP, NG, ATM>(G, sm->b1, tmem, phase, gt, grp, act ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr, 8192, policy);
+      run_layer<64, 32, NP, NG, ATM>(G, sm->b1, tmem, a_tmem, phase, gt, grp, act ? A.enc_tiles + tile_id * (SP * kEncTileBytes) : nullptr, 8192, policy);
       aout.keep = ATM ? act : nullptr;
       aout.keep_bytes = 16384;
       epilogue_hidden<NP, ATM>(taddr, sm->bias_b0, aout);
-      run_layer<16, 64, NP, NG, ATM>(G, sm->b2, tmem, phase, gt, grp, act, 16384, policy);
+      run_layer<16, 64, NP, NG, ATM>(G, sm->b2, tmem, a_tmem, phase, gt, grp, act, 16384, policy);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
@@ -347,14 +377,14 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
         aout.keep = nullptr;
       }
       // ---- head MLP ------------------------------------------------------------------------------------
-      run_layer<64, 32, NP, NG, ATM>(G, sm->b3, tmem, phase, gt, grp, act ? act + SP * 16384 : nullptr, 8192, policy);
+      run_layer<64, 32, NP, NG, ATM>(G, sm->b3, tmem, a_tmem, phase, gt, grp, act ? act + SP * 16384 : nullptr, 8192, policy);
       const uint2 m2 = epilogue_hidden<NP, ATM>(taddr, sm->bias_h0, aout);
       // H2 / H3 are not kept: the backward recomputes them from IN (kernels.h); with split operands its recompute has
       // 16 significant bits where this pass has 24, so the ReLU masks decided HERE are handed over
-      run_layer<64, 64, NP, NG, ATM>(G, sm->b4, tmem, phase, gt, grp);
+      run_layer<64, 64, NP, NG, ATM>(G, sm->b4, tmem, a_tmem, phase, gt, grp);
       const uint2 m3 = epilogue_hidden<NP, ATM>(taddr, sm->bias_h1, aout);
       if (MODE == 1 && NP > 1 && A.masks4) __stcs(A.masks4 + tile_id * 128 + gt, make_uint4(m2.x, m2.y, m3.x, m3.y));
-      run_layer<16, 64, NP, NG, ATM>(G, sm->b5, tmem, phase, gt, grp);
+      run_layer<16, 64, NP, NG, ATM>(G, sm->b5, tmem, a_tmem, phase, gt, grp);
       {
         float v[16];
         tc::tmem_ld16(taddr, v);
@@ -420,14 +450,17 @@ k_field_forward_tc(const __grid_constant__ ModelDev M, const __grid_constant__ F
   tc::tc_fence_before();
   __syncthreads();
   if (MODE == 1 && A.g_absmax && tid == 0) atomicMax(reinterpret_cast<int*>(A.g_absmax), sm->seed_max_bits);
-  if (tid < 32) tc::tmem_dealloc<kAllocCols>(sm->tmem_slot);
+  if (tid < 32) {
+    tc::tmem_dealloc<kAllocCols>(sm->tmem_slot);
+    if (kTwoAllocs) tc::tmem_dealloc<32>(sm->tmem_slot_a);
+  }
 }
 
 template <int MODE, int NP, int NG>
 static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStream_t stream) {
   if (A.n <= 0) return cudaSuccess;
   static DeviceOnce attr_once;      // cudaFuncSetAttribute is per device
-  size_t smem = sizeof(TcSmem<NP, NG, (NP > 1 && kSplitAtm)>) + 128;
+  size_t smem = sizeof(TcSmem<NP, NG, FwdCfg<MODE, NP>::kAtm>) + 128;
   if (attr_once.need()) {
     cudaError_t e = cudaFuncSetAttribute(k_field_forward_tc<MODE, NP, NG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -435,7 +468,7 @@ static cudaError_t launch_tc_mode(const ModelDev& M, const FieldArgs& A, cudaStr
   const int64_t groups = (A.n + kRaysPerGroup - 1) / kRaysPerGroup;
   // persistent: the groups of an SM (4 CTAs of one with fp16 operands, one CTA of two with split operands) share its
   // tensor core
-  const int64_t want = (groups + NG - 1) / NG, cap = 148 * (NP == 1 ? 4 : 1);
+  const int64_t want = (groups + NG - 1) / NG, cap = 148 * FwdCfg<MODE, NP>::kCtasPerSm;
   k_field_forward_tc<MODE, NP, NG><<<(unsigned)(want < cap ? want : cap), 128 * NG, smem, stream>>>(M, A);
   return cudaGetLastError();
 }

@@ -1,5 +1,6 @@
 cd $GRAFT_REPO_ROOT
-for sc in 1.0 1000.0; do
-  echo "== table scale $sc"
-  timeout 300 python tools/diag_table_grad.py 30000 $sc 2>&1 | grep -v "^max" | grep "split\|level\|non-zero" | head -24
+for v in "" seed5; do
+  lib=""; [ -n "$v" ] && lib=nerf_emitter_b200/libnerfemitter_$v.so
+  echo "== lib: ${v:-default}"
+  NEMIT_LIB=$lib timeout 300 python tools/kernel_times.py 262144 fwd+bwd fast 3 fp16 2>&1 | tail -1
 done
